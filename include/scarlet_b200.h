@@ -1,0 +1,124 @@
+/* scarlet_b200 -- C ABI of the B200-native deblending hot path.
+ *
+ * This is the drop-in boundary for the reference's native module
+ * `scarlet.operators_pybind11` (/root/reference/scarlet/operators_pybind11.cc:72-91,
+ * built by setup.py:66-77) widened to the whole `Blend.fit` loop
+ * (/root/reference/scarlet/blend.py:65-102).  Plain pointers and sizes only; every
+ * function returns 0 on success or a negative SCL_E_* code (scl_last_error() gives
+ * the message).  No exception crosses the boundary and there is no CPU fallback:
+ * without a CUDA device every compute entry point returns SCL_E_CUDA.
+ *
+ * Unless a parameter says "device", pointers are HOST pointers; the library does the
+ * host<->device copies on `stream` (a cudaStream_t passed as void*, NULL = default).
+ */
+#ifndef SCARLET_B200_H
+#define SCARLET_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SCL_OK 0
+#define SCL_E_ARG (-1)      /* bad argument (maps to ValueError)      */
+#define SCL_E_CUDA (-2)     /* CUDA runtime error (maps to RuntimeError) */
+#define SCL_E_LIMIT (-3)    /* shape outside the compiled limits (NotImplementedError) */
+
+#define SCL_FFT_EDGE 128    /* convolution FFT edge; needs Ny + ky/2 <= 128, Nx + kx/2 <= 128 */
+#define SCL_SPEC_COLS 65    /* columns of a kernel spectrum: rfft2 layout [128][65] complex64 */
+
+/* component flags */
+#define SCL_SYMMETRIC 1u    /* source.symmetric (source.py:427) */
+#define SCL_MONOTONIC 2u    /* source.monotonic (source.py:435) */
+#define SCL_FIX_SED 4u      /* component.fix_sed (blend.py:91) */
+#define SCL_FIX_MORPH 8u    /* component.fix_morph (blend.py:94) */
+#define SCL_KSPACE 16u      /* owner has `.shift`: k-space symmetry; else soft symmetry, strength 1 (operator.py:337-339) */
+#define SCL_CONSTRAINED 32u /* owner runs PointSource.update (source.py:402-440); plain Component.update is a no-op */
+
+int scl_version(void);
+const char* scl_last_error(void);
+int scl_device_count(void);
+
+/* ---- operator tables --------------------------------------------------------------
+ * Monotonicity weights depend only on the pixel's offset from the peak (plus the image
+ * border).  The host builds them once per image shape with the reference's formula
+ * (operator.py:540-621) and registers them here:
+ *   wtab  float32 [(2Ny-1)*(2Nx-1)*8]  normalised weights of an interior pixel
+ *   ctab  float64 [(2Ny-1)*(2Nx-1)*8]  un-normalised cosines, 0 where the tap is not strictly closer
+ * indexed by ((Y+Ny-1)*(2Nx-1) + (X+Nx-1))*8 + tap, (Y,X) = pixel - peak. */
+int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab);
+
+/* ---- array-level operators (host arrays, updated in place) -------------------------
+ * n images of shape [Ny][Nx]; centers int32 [n][2] = (y, x) of the peak. */
+
+/* operators_pybind11.prox_weighted_monotonic, f32 / f64 overloads (operators_pybind11.cc:27-50,82-85)
+ * with the weights, offsets and radius ordering of operator.prox_strict_monotonic(use_nearest=False)
+ * (operator.py:116-122) generated on the device. */
+int scl_prox_weighted_monotonic_f32(float* x, int n, int Ny, int Nx, const int32_t* centers, float thresh, void* stream);
+int scl_prox_weighted_monotonic_f64(double* x, int n, int Ny, int Nx, const int32_t* centers, double thresh, void* stream);
+/* operators_pybind11.prox_monotonic (operators_pybind11.cc:11-25), f64 only, nearest-neighbour reference
+ * pixels of operator.prox_strict_monotonic(use_nearest=True) (operator.py:105-115). */
+int scl_prox_monotonic_f64(double* x, int n, int Ny, int Nx, const int32_t* centers, double thresh, void* stream);
+/* operator.prox_uncentered_symmetry (operator.py:291-350).  mode 0 = "kspace" (shifts float64 [n][2] = (dy,dx),
+ * operator.py:253-288), 1 = "soft" (strength), 2 = "sdss".  The window of operator.uncentered_operator
+ * (operator.py:175-228) with fill=None is applied on the device. */
+int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* centers, const double* shifts,
+                          int mode, float strength, void* stream);
+/* measurement.max_pixel (measurement.py:3-29) and/or measurement.psf_weighted_centroid (measurement.py:32-94).
+ * centers in/out; shifts out (float64 [n][2]); psf float32 [ph][pw]. */
+int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, double* shifts,
+                    const float* psf, int ph, int pw, int do_max_pixel, int do_centroid, void* stream);
+/* Observation.render (observation.py:203-220): out = convolve(model, diff kernel) per band.
+ * model/out float32 [n][C][Ny][Nx]; spec complex64 [n_ker][128][65] (rfft2 of the truncated difference kernel
+ * with its centre tap at index 0); ker_idx int32 [n*C] (-1 = identity).  adjoint != 0 applies the transpose. */
+int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int Nx, const float* spec, int n_ker,
+                     const int32_t* ker_idx, int adjoint, void* stream);
+/* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
+ * exported for symbol parity, returns SCL_E_LIMIT. */
+int scl_apply_filter_f32(void);
+
+/* ---- Blend.fit on a batch of independent blends ------------------------------------ */
+typedef struct scl_batch scl_batch;
+
+typedef struct {
+    int32_t n_blends, n_comp;       /* B, Ktot */
+    int32_t C, Ny, Nx;              /* frame shape shared by the batch */
+    const int32_t* comp_off;        /* [B+1] component range of each blend */
+    const float* sed;               /* [Ktot][C] */
+    const float* morph;             /* [Ktot][Ny*Nx] */
+    const uint32_t* cflags;         /* [Ktot] SCL_* flags */
+    const int32_t* center;          /* [Ktot][2] pixel_center (y, x) */
+    const double* shift;            /* [Ktot][2] (dy, dx) */
+    const int32_t* conv;            /* [Ktot] BlendFlag bits (component.py:32-36) */
+    const float* images;            /* [B][C][Ny*Nx] */
+    const float* weights;           /* [B][C][Ny*Nx] or NULL (weights = 1, observation.py:148-151) */
+    int32_t n_ker;                  /* number of distinct kernel spectra */
+    const float* kernel_spec;       /* complex64 [n_ker][128][65] */
+    const int32_t* ker_idx;         /* [B*C] index into kernel_spec, -1 = identical PSFs (observation.py:191-194) */
+    int32_t n_cw, ph, pw;           /* centroid weight images (source.py:389-397) */
+    const float* cw;                /* [n_cw][ph][pw] */
+    const int32_t* cw_idx;          /* [B] */
+    const int32_t* it0;             /* [B] Blend.it before this fit (len(mse)) */
+    const double* prev_loss;        /* [B] mse[-1] before this fit (ignored where it0 == 0) */
+} scl_batch_desc;
+
+/* Allocate device state for `desc`'s sizes and upload it. */
+int scl_batch_create(const scl_batch_desc* desc, scl_batch** out, void* stream);
+/* Re-upload inputs of identical sizes into an existing batch (no allocation). */
+int scl_batch_upload(scl_batch* batch, const scl_batch_desc* desc, void* stream);
+/* Blend.fit(max_iter, e_rel, approximate_L) (blend.py:65-102) for every blend of the batch.
+ * check_every: how often (iterations) the host polls the device-side active count to stop early.
+ * device_ms (optional): device time of the whole loop by CUDA events on `stream`.
+ * k1_ms (optional): summed device time of the fused render/convolve/residual/adjoint kernel and
+ * k1_launches its launch count (only measured when profile != 0; adds event overhead). */
+int scl_batch_fit(scl_batch* batch, int max_iter, double e_rel, int approximate_L, int check_every,
+                  int profile, float* device_ms, float* k1_ms, int* k1_launches, int* launches, void* stream);
+/* Copy results back.  Any pointer may be NULL.  logL: [B][max_iter of the last fit] (Blend.mse entries appended
+ * by that fit; n_iter[b] of them valid); active[b] == 0 <=> blend b converged. */
+int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* center, double* shift, int32_t* conv,
+                       int32_t* n_iter, int32_t* active, double* logL, float* lipschitz, void* stream);
+void scl_batch_destroy(scl_batch* batch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

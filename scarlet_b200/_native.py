@@ -1,0 +1,355 @@
+"""ctypes binding of libscarlet_b200.so (include/scarlet_b200.h) and the small
+host-side tables the kernels consume.  There is no CPU fallback: every compute
+entry point raises when the library or a CUDA device is missing.
+"""
+import ctypes
+import os
+import threading
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libscarlet_b200.so")
+
+FFT_EDGE = 128
+SPEC_COLS = 65
+
+F_SYMMETRIC, F_MONOTONIC, F_FIX_SED, F_FIX_MORPH, F_KSPACE, F_CONSTRAINED = 1, 2, 4, 8, 16, 32
+
+_lib = None
+_lock = threading.Lock()
+
+c_int, c_float, c_double, c_void_p = ctypes.c_int, ctypes.c_float, ctypes.c_double, ctypes.c_void_p
+
+
+class BatchDesc(ctypes.Structure):
+    _fields_ = [
+        ("n_blends", ctypes.c_int32), ("n_comp", ctypes.c_int32),
+        ("C", ctypes.c_int32), ("Ny", ctypes.c_int32), ("Nx", ctypes.c_int32),
+        ("comp_off", c_void_p), ("sed", c_void_p), ("morph", c_void_p), ("cflags", c_void_p),
+        ("center", c_void_p), ("shift", c_void_p), ("conv", c_void_p),
+        ("images", c_void_p), ("weights", c_void_p),
+        ("n_ker", ctypes.c_int32), ("kernel_spec", c_void_p), ("ker_idx", c_void_p),
+        ("n_cw", ctypes.c_int32), ("ph", ctypes.c_int32), ("pw", ctypes.c_int32),
+        ("cw", c_void_p), ("cw_idx", c_void_p),
+        ("it0", c_void_p), ("prev_loss", c_void_p),
+    ]
+
+
+def lib():
+    """Load the CUDA library; fail loudly if it has not been built."""
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                raise RuntimeError("libscarlet_b200.so is not built (run `python -m scarlet_b200.build`); "
+                                   "scarlet_b200 has no CPU fallback")
+            L = ctypes.CDLL(LIB_PATH)
+            L.scl_last_error.restype = ctypes.c_char_p
+            L.scl_batch_destroy.restype = None
+            _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc == 0:
+        return
+    msg = lib().scl_last_error().decode()
+    if rc == -1:
+        raise ValueError(msg)
+    if rc == -3:
+        raise NotImplementedError(msg)
+    raise RuntimeError(msg)
+
+
+def require_device():
+    if lib().scl_device_count() < 1:
+        raise RuntimeError("scarlet_b200 needs a CUDA device (no CPU fallback)")
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(c_void_p)
+
+
+# --------------------------------------------------------------------------- host tables
+def next_fast_len(target):
+    """Smallest 5-smooth integer >= target (what scipy.fftpack.next_fast_len returns, fft.py:99)."""
+    target = int(target)
+    if target <= 6:
+        return target
+    best = None
+    p5 = 1
+    while p5 < 2 * target:
+        p35 = p5
+        while p35 < 2 * target:
+            n = p35
+            while n < target:
+                n *= 2
+            best = n if best is None or n < best else best
+            p35 *= 3
+        p5 *= 5
+    return best
+
+
+def conv_fft_shape(n_img, n_ker, last):
+    """The reference's FFT length for one axis of fft.convolve (fft.py:68-106, padding 3)."""
+    f = next_fast_len(n_img + n_ker + 3)
+    if last:
+        while f % 2:
+            f = next_fast_len(f + 1)
+    return f
+
+
+_COORDS = [(-1, -1), (-1, 0), (-1, 1), (0, -1), (0, 1), (1, -1), (1, 0), (1, 1)]
+_tables = {}
+_registered = set()
+
+
+def monotonic_tables(Ny, Nx):
+    """Build (once per shape) and register the monotonicity tables with the CUDA library."""
+    key = (int(Ny), int(Nx))
+    if key not in _registered:
+        wtab, ctab = monotonic_tables_host(Ny, Nx)
+        _check(lib().scl_set_monotonic_tables(c_int(Ny), c_int(Nx), _p(wtab), _p(ctab)))
+        _registered.add(key)
+    return _tables[key]
+
+
+def monotonic_tables_host(Ny, Nx):
+    """Offset-indexed weight tables of the radial monotonicity operator.
+
+    Same arithmetic as getRadialMonotonicWeights (operator.py:540-621) evaluated for
+    every offset (Y, X) = pixel - peak instead of for one peak position:
+      ctab[Y, X, i]  cos(theta_p - phi_i) if neighbour i is strictly closer to the peak, else 0
+      wtab[Y, X, i]  ctab normalised over the 8 taps, rounded to float32 (interior pixels)
+    The device renormalises ctab for pixels on the image border.
+    """
+    key = (int(Ny), int(Nx))
+    if key in _tables:
+        return _tables[key]
+    Y, X = np.meshgrid(np.arange(-(Ny - 1), Ny), np.arange(-(Nx - 1), Nx), indexing="ij")
+    inf = X == 0
+    tX = X.copy()
+    tX[inf] = 1
+    ang = np.arctan2(-Y, -tX)
+    sel = inf & (Y != 0)
+    ang[sel] = 0.5 * np.pi * np.sign(ang[sel])
+    ctab = np.zeros(Y.shape + (8,), dtype=np.float64)
+    for i, (oy, ox) in enumerate(_COORDS):
+        dy = np.full(Y.shape, float(oy))
+        dx = np.full(Y.shape, float(ox))
+        infn = dx == 0
+        dx[infn] = 1
+        rel = np.arctan2(dy, dx)
+        s = infn & (dy != 0)
+        rel[s] = 0.5 * np.pi * np.sign(rel[s])
+        w = np.cos(ang - rel)
+        closer = (Y + oy) ** 2 + (X + ox) ** 2 < Y ** 2 + X ** 2
+        w[~closer] = 0
+        ctab[..., i] = w
+    norm = np.zeros(Y.shape)
+    for i in range(8):                      # sequential tap-order sum, like np.sum(axis=0) on (8, N)
+        norm = norm + ctab[..., i]
+    norm[norm == 0] = 1
+    wtab = (ctab / norm[..., None]).astype(np.float32)
+    ctab = np.ascontiguousarray(ctab)
+    wtab = np.ascontiguousarray(wtab)
+    _tables[key] = (wtab, ctab)
+    return _tables[key]
+
+
+def kernel_spectrum(kernels, Ny, Nx):
+    """rfft2 of real-space difference kernels [n, ky, kx] on the 128x128 periodic grid.
+
+    Tap j of an axis lands on grid index j + off with off = (F-k+1)//2 - F//2, F the
+    reference's FFT length for that axis (fft.py:60-65,193-211) -- for odd kernels this is
+    simply the centre tap at index 0.  Returns complex64 [n, 128, 65].
+    """
+    kernels = np.asarray(kernels)
+    n, ky, kx = kernels.shape
+    Fy, Fx = conv_fft_shape(Ny, ky, False), conv_fft_shape(Nx, kx, True)
+    offy = (Fy - ky + 1) // 2 - Fy // 2
+    offx = (Fx - kx + 1) // 2 - Fx // 2
+    if Ny - offy > FFT_EDGE or Ny + ky - 1 + offy > FFT_EDGE or Nx - offx > FFT_EDGE or Nx + kx - 1 + offx > FFT_EDGE:
+        raise NotImplementedError("frame + PSF half-width exceeds the 128x128 convolution tile")
+    grid = np.zeros((n, FFT_EDGE, FFT_EDGE), dtype=np.float64)
+    iy = (np.arange(ky) + offy) % FFT_EDGE
+    ix = (np.arange(kx) + offx) % FFT_EDGE
+    grid[:, iy[:, None], ix[None, :]] = kernels
+    return np.ascontiguousarray(np.fft.rfft2(grid).astype(np.complex64))
+
+
+# --------------------------------------------------------------------------- operators
+def _centers(centers, n):
+    c = np.ascontiguousarray(np.asarray(centers, dtype=np.int32).reshape(n, 2))
+    return c
+
+
+def prox_weighted_monotonic(x, centers, thresh=0.0):
+    """In place on x [n, Ny, Nx] (float32 or float64, C-contiguous)."""
+    require_device()
+    n, Ny, Nx = x.shape
+    monotonic_tables(Ny, Nx)
+    c = _centers(centers, n)
+    if x.dtype == np.float32:
+        _check(lib().scl_prox_weighted_monotonic_f32(_p(x), n, Ny, Nx, _p(c), c_float(thresh), None))
+    elif x.dtype == np.float64:
+        _check(lib().scl_prox_weighted_monotonic_f64(_p(x), n, Ny, Nx, _p(c), c_double(thresh), None))
+    else:
+        raise TypeError("prox_weighted_monotonic: float32 or float64 arrays only")
+    return x
+
+
+def prox_monotonic_nearest(x, centers, thresh=0.0):
+    require_device()
+    if x.dtype != np.float64:
+        raise TypeError("prox_monotonic: float64 arrays only")
+    n, Ny, Nx = x.shape
+    monotonic_tables(Ny, Nx)
+    _check(lib().scl_prox_monotonic_f64(_p(x), n, Ny, Nx, _p(_centers(centers, n)), c_double(thresh), None))
+    return x
+
+
+def prox_symmetry(x, centers, shifts=None, mode="kspace", strength=1.0):
+    require_device()
+    if x.dtype != np.float32:
+        raise TypeError("prox_symmetry: float32 arrays only")
+    n, Ny, Nx = x.shape
+    m = {"kspace": 0, "soft": 1, "sdss": 2}[mode]
+    sh = None if shifts is None else np.ascontiguousarray(np.asarray(shifts, dtype=np.float64).reshape(n, 2))
+    _check(lib().scl_prox_symmetry_f32(_p(x), n, Ny, Nx, _p(_centers(centers, n)), _p(sh), m, c_float(strength), None))
+    return x
+
+
+def measure(x, centers, psf=None, do_max=True, do_centroid=True):
+    """max_pixel and/or psf_weighted_centroid for x [n, Ny, Nx] float32.
+    Returns (centers int32 [n,2], shifts float64 [n,2])."""
+    require_device()
+    n, Ny, Nx = x.shape
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    c = _centers(centers, n).copy()
+    s = np.zeros((n, 2), dtype=np.float64)
+    ph = pw = 0
+    if psf is not None:
+        psf = np.ascontiguousarray(psf, dtype=np.float32)
+        ph, pw = psf.shape
+    _check(lib().scl_measure_f32(_p(x), n, Ny, Nx, _p(c), _p(s), _p(psf), ph, pw, int(do_max), int(do_centroid), None))
+    return c, s
+
+
+def convolve(model, spec, ker_idx, adjoint=False):
+    """model float32 [n, C, Ny, Nx]; spec complex64 [n_ker,128,65]; ker_idx int32 [n*C]."""
+    require_device()
+    model = np.ascontiguousarray(model, dtype=np.float32)
+    n, C, Ny, Nx = model.shape
+    out = np.empty_like(model)
+    ker_idx = np.ascontiguousarray(ker_idx, dtype=np.int32).reshape(-1)
+    n_ker = 0 if spec is None else len(spec)
+    if spec is not None:
+        spec = np.ascontiguousarray(spec, dtype=np.complex64)
+    _check(lib().scl_convolve_f32(_p(model), _p(out), n, C, Ny, Nx, _p(spec), n_ker, _p(ker_idx), int(adjoint), None))
+    return out
+
+
+# --------------------------------------------------------------------------- batch fit
+class Batch:
+    """Device-resident state of B independent blends sharing one frame shape
+    (thin owner of a `scl_batch*`)."""
+
+    def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
+                 kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, stream=None):
+        require_device()
+        monotonic_tables(Ny, Nx)
+        self.C, self.Ny, self.Nx = int(C), int(Ny), int(Nx)
+        self.stream = stream
+        self._h = c_void_p()
+        self._keep = None
+        self.max_iter = 0
+        desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
+                          cw, cw_idx, it0, prev_loss)
+        _check(lib().scl_batch_create(ctypes.byref(desc), ctypes.byref(self._h), c_void_p(self.stream)))
+
+    def _desc(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
+              cw, cw_idx, it0, prev_loss):
+        N = self.Ny * self.Nx
+        ca = np.ascontiguousarray
+        comp_off = ca(comp_off, dtype=np.int32)
+        B = len(comp_off) - 1
+        K = int(comp_off[-1]) if B > 0 else 0
+        a = dict(
+            comp_off=comp_off,
+            sed=ca(sed, dtype=np.float32).reshape(K, self.C),
+            morph=ca(morph, dtype=np.float32).reshape(K, N),
+            cflags=ca(cflags, dtype=np.uint32).reshape(K),
+            center=ca(center, dtype=np.int32).reshape(K, 2),
+            shift=ca(shift, dtype=np.float64).reshape(K, 2),
+            conv=ca(conv, dtype=np.int32).reshape(K),
+            images=ca(images, dtype=np.float32).reshape(B, self.C, N),
+            weights=None if weights is None else ca(weights, dtype=np.float32).reshape(B, self.C, N),
+            kernel_spec=None if kernel_spec is None else ca(kernel_spec, dtype=np.complex64),
+            ker_idx=ca(ker_idx, dtype=np.int32).reshape(B * self.C),
+            cw=None if cw is None else ca(cw, dtype=np.float32),
+            cw_idx=ca(cw_idx, dtype=np.int32).reshape(B),
+            it0=ca(np.zeros(B) if it0 is None else it0, dtype=np.int32).reshape(B),
+            prev_loss=None if prev_loss is None else ca(prev_loss, dtype=np.float64).reshape(B),
+        )
+        self._keep = a
+        self.B, self.K = B, K
+        d = BatchDesc()
+        d.n_blends, d.n_comp, d.C, d.Ny, d.Nx = B, K, self.C, self.Ny, self.Nx
+        for name in ("comp_off", "sed", "morph", "cflags", "center", "shift", "conv", "images", "weights",
+                     "kernel_spec", "ker_idx", "cw", "cw_idx", "it0", "prev_loss"):
+            setattr(d, name, _p(a[name]))
+        d.n_ker = 0 if a["kernel_spec"] is None else len(a["kernel_spec"])
+        if a["cw"] is None:
+            d.n_cw, d.ph, d.pw = 0, 0, 0
+        else:
+            d.n_cw, d.ph, d.pw = a["cw"].shape
+        self.h2d_bytes = sum(v.nbytes for v in a.values() if v is not None)
+        return d
+
+    def upload(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
+               cw, cw_idx, it0=None, prev_loss=None):
+        desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
+                          cw, cw_idx, it0, prev_loss)
+        _check(lib().scl_batch_upload(self._h, ctypes.byref(desc), c_void_p(self.stream)))
+
+    def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False):
+        """Returns dict(device_ms, k1_ms, k1_launches, launches)."""
+        ms, k1 = c_float(0), c_float(0)
+        nk1, nl = c_int(0), c_int(0)
+        _check(lib().scl_batch_fit(self._h, int(max_iter), c_double(e_rel), int(bool(approximate_L)), int(check_every),
+                                   int(bool(profile)), ctypes.byref(ms), ctypes.byref(k1), ctypes.byref(nk1),
+                                   ctypes.byref(nl), c_void_p(self.stream)))
+        self.max_iter = int(max_iter)
+        return dict(device_ms=ms.value, k1_ms=k1.value, k1_launches=nk1.value, launches=nl.value)
+
+    def download(self, morph=True):
+        N = self.Ny * self.Nx
+        out = dict(
+            sed=np.empty((self.K, self.C), np.float32),
+            morph=np.empty((self.K, self.Ny, self.Nx), np.float32) if morph else None,
+            center=np.empty((self.K, 2), np.int32),
+            shift=np.empty((self.K, 2), np.float64),
+            conv=np.empty(self.K, np.int32),
+            n_iter=np.empty(self.B, np.int32),
+            active=np.empty(self.B, np.int32),
+            logL=np.empty((self.B, self.max_iter), np.float64) if self.max_iter > 0 else None,
+            lipschitz=np.empty((self.B, 2), np.float32),
+        )
+        _check(lib().scl_batch_download(self._h, _p(out["sed"]), _p(out["morph"]), _p(out["center"]), _p(out["shift"]),
+                                        _p(out["conv"]), _p(out["n_iter"]), _p(out["active"]), _p(out["logL"]),
+                                        _p(out["lipschitz"]), c_void_p(self.stream)))
+        self.d2h_bytes = sum(v.nbytes for v in out.values() if v is not None)
+        return out
+
+    def close(self):
+        if self._h:
+            lib().scl_batch_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,282 @@
+// C ABI of libscarlet_b200.so (see include/scarlet_b200.h).  Single translation
+// unit: the kernels are included so that one nvcc invocation builds the library.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+#include <map>
+#include <vector>
+#include <utility>
+#include <mutex>
+
+#include "../../include/scarlet_b200.h"
+#include "k_forward.cu"
+#include "k_grad.cu"
+#include "k_prox.cu"
+
+static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
+static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
+              SCL_F_FIX_MORPH == SCL_FIX_MORPH && SCL_F_KSPACE == SCL_KSPACE && SCL_F_CONSTRAINED == SCL_CONSTRAINED,
+              "flag constants diverged");
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char* fmt, const char* a = "", const char* b = "") {
+    snprintf(g_err, sizeof(g_err), fmt, a, b);
+    return code;
+}
+
+#define CK(call)                                                                        \
+    do {                                                                                \
+        cudaError_t e_ = (call);                                                        \
+        if (e_ != cudaSuccess) return fail(SCL_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+constexpr size_t kFwdSmem = (size_t)(SCL_FFT * SCL_RS + 128) * sizeof(float2) + 32 * sizeof(double);
+
+int next_fast_len(int target) {     // smallest 2^a 3^b 5^c >= target (scipy.fftpack.next_fast_len, fft.py:99)
+    if (target <= 6) return target;
+    int best = 1 << 30;
+    for (long p5 = 1; p5 < 2L * target; p5 *= 5)
+        for (long p35 = p5; p35 < 2L * target; p35 *= 3) {
+            long n = p35;
+            while (n < target) n *= 2;
+            if (n < best) best = (int)n;
+        }
+    return best;
+}
+
+struct Tables {
+    float* wtab = nullptr;
+    double* ctab = nullptr;
+};
+std::mutex g_mu;
+std::map<std::pair<int, int>, Tables> g_tables;
+int* g_nfl = nullptr;        // device [1024]
+int* g_nfl_even = nullptr;   // device [1024]
+constexpr int kNflN = 1024;
+bool g_attr_done = false;
+
+int ensure_globals() {
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_nfl) {
+        std::vector<int> a(kNflN), b(kNflN);
+        for (int n = 0; n < kNflN; n++) {
+            a[n] = next_fast_len(n);
+            int e = a[n];
+            while (e % 2 != 0) e = next_fast_len(e + 1);      // fft.py:103-105
+            b[n] = e;
+        }
+        CK(cudaMalloc(&g_nfl, kNflN * sizeof(int)));
+        CK(cudaMalloc(&g_nfl_even, kNflN * sizeof(int)));
+        CK(cudaMemcpy(g_nfl, a.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(g_nfl_even, b.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
+    }
+    if (!g_attr_done) {
+        CK(cudaFuncSetAttribute(scl_k_forward_adjoint, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        const int big = 200 * 1024;
+        CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_symmetry, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_monotonic<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_monotonic<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_monotonic<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        g_attr_done = true;
+    }
+    return SCL_OK;
+}
+
+int get_tables(int Ny, int Nx, Tables* t) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_tables.find({Ny, Nx});
+    if (it == g_tables.end())
+        return fail(SCL_E_ARG, "no monotonic tables registered for this shape (call scl_set_monotonic_tables)%s%s");
+    *t = it->second;
+    return SCL_OK;
+}
+
+size_t prox_smem(int Ny, int Nx) {
+    int mx = Ny > Nx ? Ny : Nx;
+    return ((size_t)2 * Ny * Nx + 3 * (2 * mx - 1) + 2 * Nx + 8) * sizeof(float);
+}
+
+int check_shape(int Ny, int Nx) {
+    if (Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "empty image shape%s%s");
+    if (prox_smem(Ny, Nx) > 200 * 1024 || 2 * Ny + 10 >= kNflN || 2 * Nx + 10 >= kNflN)
+        return fail(SCL_E_LIMIT, "image shape exceeds the shared-memory resident limit%s%s");
+    return SCL_OK;
+}
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t n = 0;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t count) {
+        n = count;
+        return cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+    }
+    cudaError_t up(const T* h, cudaStream_t s) { return cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s); }
+    cudaError_t down(T* h, cudaStream_t s) const { return cudaMemcpyAsync(h, p, n * sizeof(T), cudaMemcpyDeviceToHost, s); }
+};
+
+template <typename T, bool NEAREST>
+static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T thresh, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || !centers || n < 0) return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = check_shape(Ny, Nx);
+    if (rc) return rc;
+    if ((rc = ensure_globals())) return rc;
+    for (int i = 0; i < n; i++)
+        if (centers[2 * i] < 0 || centers[2 * i] >= Ny || centers[2 * i + 1] < 0 || centers[2 * i + 1] >= Nx)
+            return fail(SCL_E_ARG, "center outside the image%s%s");
+    Tables t;
+    if ((rc = get_tables(Ny, Nx, &t))) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    size_t N = (size_t)Ny * Nx;
+    DevBuf<T> dx;
+    DevBuf<int> dc;
+    CK(dx.alloc(n * N));
+    CK(dc.alloc(2 * (size_t)n));
+    CK(dx.up(x, s));
+    CK(dc.up(centers, s));
+    scl_k_monotonic<T, NEAREST><<<n, SCL_THREADS, N * sizeof(T), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
+    CK(cudaGetLastError());
+    CK(dx.down(x, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int scl_version(void) { return 100; }
+const char* scl_last_error(void) { return g_err; }
+int scl_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) return 0;
+    return n;
+}
+
+int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab) {
+    int rc = check_shape(Ny, Nx);
+    if (rc) return rc;
+    if (!wtab || !ctab) return fail(SCL_E_ARG, "null table%s%s");
+    size_t n = (size_t)(2 * Ny - 1) * (2 * Nx - 1) * 8;
+    Tables t;
+    CK(cudaMalloc(&t.wtab, n * sizeof(float)));
+    CK(cudaMalloc(&t.ctab, n * sizeof(double)));
+    CK(cudaMemcpy(t.wtab, wtab, n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.ctab, ctab, n * sizeof(double), cudaMemcpyHostToDevice));
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_tables.find({Ny, Nx});
+    if (it != g_tables.end()) { cudaFree(it->second.wtab); cudaFree(it->second.ctab); }
+    g_tables[{Ny, Nx}] = t;
+    return SCL_OK;
+}
+
+int scl_prox_weighted_monotonic_f32(float* x, int n, int Ny, int Nx, const int32_t* c, float thresh, void* stream) {
+    return run_monotonic<float, false>(x, n, Ny, Nx, c, thresh, stream);
+}
+int scl_prox_weighted_monotonic_f64(double* x, int n, int Ny, int Nx, const int32_t* c, double thresh, void* stream) {
+    return run_monotonic<double, false>(x, n, Ny, Nx, c, thresh, stream);
+}
+int scl_prox_monotonic_f64(double* x, int n, int Ny, int Nx, const int32_t* c, double thresh, void* stream) {
+    return run_monotonic<double, true>(x, n, Ny, Nx, c, thresh, stream);
+}
+
+int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* centers, const double* shifts,
+                          int mode, float strength, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || !centers || n < 0 || mode < 0 || mode > 2) return fail(SCL_E_ARG, "bad argument%s%s");
+    if (mode == 0 && !shifts) return fail(SCL_E_ARG, "kspace symmetry needs shifts%s%s");
+    int rc = check_shape(Ny, Nx);
+    if (rc) return rc;
+    if ((rc = ensure_globals())) return rc;
+    for (int i = 0; i < n; i++)
+        if (centers[2 * i] < 0 || centers[2 * i] >= Ny || centers[2 * i + 1] < 0 || centers[2 * i + 1] >= Nx)
+            return fail(SCL_E_ARG, "center outside the image%s%s");
+    cudaStream_t s = (cudaStream_t)stream;
+    size_t N = (size_t)Ny * Nx;
+    DevBuf<float> dx;
+    DevBuf<int> dc;
+    DevBuf<double> ds;
+    CK(dx.alloc(n * N));
+    CK(dc.alloc(2 * (size_t)n));
+    CK(ds.alloc(2 * (size_t)n));
+    CK(dx.up(x, s));
+    CK(dc.up(centers, s));
+    if (shifts) CK(ds.up(shifts, s)); else CK(cudaMemsetAsync(ds.p, 0, 2 * (size_t)n * sizeof(double), s));
+    scl_k_symmetry<<<n, SCL_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl, g_nfl_even);
+    CK(cudaGetLastError());
+    CK(dx.down(x, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, double* shifts,
+                    const float* psf, int ph, int pw, int do_max, int do_centroid, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || !centers || !shifts || n < 0 || (do_centroid && (!psf || ph < 1 || pw < 1)))
+        return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = check_shape(Ny, Nx);
+    if (rc) return rc;
+    if ((rc = ensure_globals())) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    size_t N = (size_t)Ny * Nx;
+    DevBuf<float> dx, dp;
+    DevBuf<int> dc;
+    DevBuf<double> ds;
+    CK(dx.alloc(n * N));
+    CK(dp.alloc(psf ? (size_t)ph * pw : 1));
+    CK(dc.alloc(2 * (size_t)n));
+    CK(ds.alloc(2 * (size_t)n));
+    CK(cudaMemcpyAsync(dx.p, x, n * N * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (psf) CK(dp.up(psf, s));
+    CK(dc.up(centers, s));
+    scl_k_measure<<<n, SCL_THREADS, N * sizeof(float), s>>>(dx.p, dc.p, ds.p, Ny, Nx, dp.p, ph, pw, do_max, do_centroid);
+    CK(cudaGetLastError());
+    CK(dc.down(centers, s));
+    CK(ds.down(shifts, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int Nx, const float* spec, int n_ker,
+                     const int32_t* ker_idx, int adjoint, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!model || !out || !ker_idx || n < 0 || C < 1 || (n_ker > 0 && !spec)) return fail(SCL_E_ARG, "bad argument%s%s");
+    if (Ny > SCL_FFT || Nx > SCL_FFT) return fail(SCL_E_LIMIT, "frame larger than the 128x128 convolution tile%s%s");
+    for (int i = 0; i < n * C; i++)
+        if (ker_idx[i] >= n_ker) return fail(SCL_E_ARG, "ker_idx out of range%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    size_t tot = (size_t)n * C * Ny * Nx;
+    DevBuf<float> dm, dout;
+    DevBuf<float2> dspec;
+    DevBuf<int> dk;
+    CK(dm.alloc(tot));
+    CK(dout.alloc(tot));
+    CK(dspec.alloc((size_t)(n_ker > 0 ? n_ker : 1) * SCL_FFT * SCL_RS));
+    CK(dk.alloc((size_t)n * C));
+    CK(cudaMemcpyAsync(dm.p, model, tot * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (n_ker > 0) CK(cudaMemcpyAsync(dspec.p, spec, dspec.n * sizeof(float2), cudaMemcpyHostToDevice, s));
+    CK(dk.up(ker_idx, s));
+    scl_k_convolve<<<dim3(C, n), SCL_THREADS, kFwdSmem, s>>>(dm.p, dspec.p, dk.p, dout.p, C, Ny, Nx, adjoint);
+    CK(cudaGetLastError());
+    CK(dout.down(out, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_apply_filter_f32(void) {
+    return fail(SCL_E_LIMIT, "apply_filter has no caller in the reference (operators_pybind11.cc:52-70); not implemented%s%s");
+}
+
+}  // extern "C"
+
+#include "api_batch.inc"

@@ -1,0 +1,56 @@
+// Shared helpers for the scarlet_b200 CUDA kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SCL_MAX_BANDS 8          // C <= 8 spectral channels per frame
+#define SCL_FFT 128              // smem FFT edge (power of two); Ny+ky/2 <= 128, Nx+kx/2 <= 128
+#define SCL_RS 65                // complex row stride of the smem spectrum tile (odd: conflict-free columns)
+#define SCL_THREADS 256
+
+// component flags (host mirror: scarlet_b200/_native.py)
+#define SCL_F_SYMMETRIC 1u       // run the symmetry prox (source.py:427-432)
+#define SCL_F_MONOTONIC 2u       // run the monotonicity prox (source.py:435-436)
+#define SCL_F_FIX_SED   4u       // skip the SED gradient step (blend.py:91)
+#define SCL_F_FIX_MORPH 8u       // skip the morphology gradient step (blend.py:94)
+#define SCL_F_KSPACE    16u      // component owner has a `.shift` -> k-space symmetry; else soft, strength 1
+#define SCL_F_CONSTRAINED 32u    // run max_pixel / positive / normalized (PointSource.update); plain Components: no-op
+
+// BlendFlag bits (component.py:32-36)
+#define SCL_SED_NOT_CONVERGED 1
+#define SCL_MORPH_NOT_CONVERGED 2
+
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
+}
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) {   // a * conj(b)
+    return make_float2(a.x * b.x + a.y * b.y, a.y * b.x - a.x * b.y);
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cswap(float2 a) { return make_float2(a.y, a.x); }
+
+template <typename T>
+__device__ __forceinline__ T warp_sum(T v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// Block-wide sum (all threads get the result).  `red` holds >= 32 T.
+template <typename T>
+__device__ __forceinline__ T block_sum(T v, T* red) {
+    v = warp_sum(v);
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if (l == 0) red[w] = v;
+    __syncthreads();
+    T r = (l < nw) ? red[l] : T(0);
+    r = warp_sum(r);
+    return r;
+}

@@ -1,0 +1,223 @@
+// K3: the per-source constraint schedule + convergence norms, one CTA per
+// component with the morphology resident in shared memory.
+// K4: per-blend convergence decision.
+//
+// Replaces (reference file:line):
+//   PointSource.update / ExtendedSource.update   source.py:402-440
+//       max_pixel -> (it % 5 == 0) psf_weighted_centroid -> symmetric(kspace)
+//       -> monotonic(thresh=0) -> positive -> normalized(morph_max)
+//   update.symmetric / monotonic / positive / normalized   update.py:27-68,106-199
+//   Blend._check_convergence                     blend.py:141-184
+#include "prox_dev.cuh"
+
+struct SclProxArgs {
+    const float* A_step;      // [Ktot, C]  SEDs after the gradient step
+    const float* S_step;      // [Ktot, N]  morphologies after the gradient step
+    float* A;                 // [Ktot, C]  in: previous iterate; out: new iterate
+    float* S;                 // [Ktot, N]  in: previous iterate; out: new iterate
+    const int* comp_blend;    // [Ktot]
+    const unsigned* cflags;   // [Ktot]
+    int* center;              // [Ktot, 2]  (y, x) pixel_center, updated
+    double* shift;            // [Ktot, 2]  (dy, dx), updated every 5th iteration
+    int* conv;                // [Ktot]     BlendFlag bits, updated when it > 1
+    const int* active;        // [B]
+    const int* it0;           // [B]
+    const float* cw;          // [n_cw, ph, pw] centroid weights (model PSF image)
+    const int* cw_idx;        // [B]
+    const float* wtab;        // monotonic tables (see prox_dev.cuh)
+    const double* ctab;
+    const int* nfl;           // next_fast_len tables
+    const int* nfl_even;
+    int C, Ny, Nx, ph, pw, step;
+    double e_rel2;
+};
+
+// dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
+extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+scl_k_prox(SclProxArgs a)
+{
+    extern __shared__ __align__(16) float smem_f[];
+    const int k = blockIdx.x;
+    const int b = a.comp_blend[k];
+    if (!a.active[b]) return;
+    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
+    float* X = smem_f;
+    float* Z = X + N;
+    float* tab = Z + N;
+    __shared__ double red[32];
+    __shared__ int sc[2];
+    __shared__ double ss[2];
+    __shared__ float sm;
+    const unsigned fl = a.cflags[k];
+    const int it = a.it0[b] + a.step + 1;          // Blend.it seen by update() (len(mse))
+
+    const float* Sin = a.S_step + (size_t)k * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
+    if (threadIdx.x == 0) {
+        sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
+        ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
+    }
+    __syncthreads();
+
+    if (fl & SCL_F_CONSTRAINED) {
+        scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
+        __syncthreads();
+        if (fl & SCL_F_SYMMETRIC) {
+            if (it % 5 == 0) {
+                const float* psf = a.cw + (size_t)a.cw_idx[b] * a.ph * a.pw;
+                int cy = sc[0], cx = sc[1];
+                __syncthreads();
+                scl_centroid(X, Ny, Nx, psf, a.ph, a.pw, cy, cx, sc, ss, red);
+            }
+            SclWindow w = scl_window(Ny, Nx, sc[0], sc[1]);
+            if (fl & SCL_F_KSPACE) {
+                // update.symmetric discards the return value of the centred case (update.py:193-198)
+                if (!w.centered) scl_kspace_symmetry(X, Nx, w, ss[0], ss[1], Z, tab, a.nfl, a.nfl_even);
+            } else {
+                scl_flip_symmetry(X, Nx, w, 0, 1.0f);
+            }
+        }
+        if (fl & SCL_F_MONOTONIC) scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+        // positive (update.py:27-32) + morph_max (update.py:62-65)
+        float mx = -INFINITY;
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            float v = X[p];
+            if (v < 0.f) { v = 0.f; X[p] = 0.f; }
+            mx = fmaxf(mx, v);
+        }
+        mx = warp_max(mx);
+        __shared__ float smax[32];
+        if ((threadIdx.x & 31) == 0) smax[threadIdx.x >> 5] = mx;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            float v = (threadIdx.x < (blockDim.x >> 5)) ? smax[threadIdx.x] : -INFINITY;
+            v = warp_max(v);
+            if (threadIdx.x == 0) sm = v;
+        }
+        __syncthreads();
+    } else if (threadIdx.x == 0) {
+        sm = 1.f;
+    }
+    __syncthreads();
+    const float norm = sm;
+    const bool constrained = fl & SCL_F_CONSTRAINED;
+
+    // write back + convergence sums (blend.py:160-174)
+    double d2 = 0.0, n2 = 0.0;
+    float* Sout = a.S + (size_t)k * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        float v = constrained ? X[p] / norm : X[p];
+        float old = Sout[p];
+        double df = (double)old - (double)v;
+        d2 += df * df;
+        n2 += (double)v * (double)v;
+        Sout[p] = v;
+    }
+    d2 = block_sum<double>(d2, red);
+    n2 = block_sum<double>(n2, red);
+    if (threadIdx.x == 0) {
+        double ad2 = 0.0, an2 = 0.0;
+        for (int c = 0; c < C; c++) {
+            float v = a.A_step[(size_t)k * C + c];
+            if (constrained) {
+                if (v < 0.f) v = 0.f;
+                v = v * norm;
+            }
+            float old = a.A[(size_t)k * C + c];
+            double df = (double)old - (double)v;
+            ad2 += df * df;
+            an2 += (double)v * (double)v;
+            a.A[(size_t)k * C + c] = v;
+        }
+        if (it > 1) {
+            int f = 0;
+            if (!(ad2 <= a.e_rel2 * an2)) f |= SCL_SED_NOT_CONVERGED;
+            if (!(d2 <= a.e_rel2 * n2)) f |= SCL_MORPH_NOT_CONVERGED;
+            a.conv[k] = f;
+        }
+        a.center[2 * k] = sc[0]; a.center[2 * k + 1] = sc[1];
+        a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
+    }
+}
+
+// K4: one thread per blend.  blend.py:157-176: never converged before it > 1.
+extern "C" __global__ void scl_k_converge(const int* __restrict__ comp_off, const int* __restrict__ conv,
+                                          const int* __restrict__ it0, int* __restrict__ active,
+                                          int* __restrict__ n_iter, int* __restrict__ n_active,
+                                          int B, int step)
+{
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B || !active[b]) return;
+    n_iter[b] = step + 1;
+    int it = it0[b] + step + 1;
+    bool done = it > 1;
+    for (int k = comp_off[b]; k < comp_off[b + 1]; k++) done = done && (conv[k] == 0);
+    if (done) {
+        active[b] = 0;
+        atomicSub(n_active, 1);
+    }
+}
+
+// ---------------------------------------------------------------- standalone operators
+// (drop-in device paths for scarlet.operator.prox_* / operators_pybind11.*)
+// one CTA per image; images [n, Ny, Nx] float32 in global memory, updated in place.
+template <typename T, bool NEAREST>
+__global__ void __launch_bounds__(SCL_THREADS)
+scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, int Nx, T thresh,
+                const float* __restrict__ wtab, const double* __restrict__ ctab)
+{
+    extern __shared__ __align__(16) unsigned char smem_b[];
+    const int N = Ny * Nx;
+    T* X = reinterpret_cast<T*>(smem_b);
+    T* g = imgs + (size_t)blockIdx.x * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
+    __syncthreads();
+    scl_monotonic<T, NEAREST>(X, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
+    for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
+}
+template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*);
+template __global__ void scl_k_monotonic<double, false>(double*, const int*, int, int, double, const float*, const double*);
+template __global__ void scl_k_monotonic<double, true>(double*, const int*, int, int, double, const float*, const double*);
+
+// mode: 0 = kspace (shift required), 1 = soft(strength), 2 = sdss
+extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+scl_k_symmetry(float* __restrict__ imgs, const int* __restrict__ centers, const double* __restrict__ shifts,
+               int Ny, int Nx, int mode, float strength, const int* __restrict__ nfl,
+               const int* __restrict__ nfl_even)
+{
+    extern __shared__ __align__(16) float smem_f[];
+    const int N = Ny * Nx;
+    float* X = smem_f;
+    float* Z = X + N;
+    float* tab = Z + N;
+    float* g = imgs + (size_t)blockIdx.x * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
+    __syncthreads();
+    SclWindow w = scl_window(Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1]);
+    if (mode == 0) scl_kspace_symmetry(X, Nx, w, shifts[2 * blockIdx.x], shifts[2 * blockIdx.x + 1], Z, tab, nfl, nfl_even);
+    else scl_flip_symmetry(X, Nx, w, mode == 2, strength);
+    for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
+}
+
+// max_pixel + psf_weighted_centroid for a stack of images (measurement.py)
+extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+scl_k_measure(const float* __restrict__ imgs, int* __restrict__ centers, double* __restrict__ shifts,
+              int Ny, int Nx, const float* __restrict__ psf, int ph, int pw, int do_max, int do_centroid)
+{
+    extern __shared__ __align__(16) float smem_f[];
+    __shared__ double red[32];
+    __shared__ int sc[2];
+    __shared__ double ss[2];
+    const int N = Ny * Nx;
+    float* X = smem_f;
+    const float* g = imgs + (size_t)blockIdx.x * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
+    if (threadIdx.x == 0) { sc[0] = centers[2 * blockIdx.x]; sc[1] = centers[2 * blockIdx.x + 1]; ss[0] = ss[1] = 0.0; }
+    __syncthreads();
+    if (do_max) { scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc); __syncthreads(); }
+    if (do_centroid) { int cy = sc[0], cx = sc[1]; __syncthreads(); scl_centroid(X, Ny, Nx, psf, ph, pw, cy, cx, sc, ss, red); }
+    if (threadIdx.x == 0) {
+        centers[2 * blockIdx.x] = sc[0]; centers[2 * blockIdx.x + 1] = sc[1];
+        shifts[2 * blockIdx.x] = ss[0]; shifts[2 * blockIdx.x + 1] = ss[1];
+    }
+}

@@ -1,0 +1,334 @@
+// Device building blocks of the constraint chain run on one morphology image
+// held in shared memory (row-major [Ny][Nx] floats) by one CTA.
+//
+// Reference (file:line):
+//   max_pixel                 measurement.py:3-29
+//   psf_weighted_centroid     measurement.py:32-94
+//   uncentered_operator       operator.py:175-228 (window geometry)
+//   prox_kspace_symmetry      operator.py:253-288, interpolation.mk_shifter interpolation.py:302-340
+//   prox_soft_symmetry        operator.py:242-251;  prox_sdss_symmetry operator.py:231-239
+//   prox_weighted_monotonic   operators_pybind11.cc:27-50 with weights of operator.py:540-621
+#pragma once
+#include "common.cuh"
+
+struct SclWindow { int y0, x0, ny, nx; bool centered; };
+
+// operator.py:197-220: largest window in which (py,px) is the //2 centre
+__device__ __forceinline__ SclWindow scl_window(int Ny, int Nx, int py, int px) {
+    SclWindow w;
+    int cy = Ny / 2, cx = Nx / 2;
+    w.centered = (py == cy && px == cx);
+    int dy = 2 * (py - cy) + ((Ny & 1) ? 0 : 1);
+    int dx = 2 * (px - cx) + ((Nx & 1) ? 0 : 1);
+    if (w.centered) { dy = 0; dx = 0; }
+    if (dy < 0) { w.y0 = 0; w.ny = Ny + dy; } else { w.y0 = dy; w.ny = Ny - dy; }
+    if (dx < 0) { w.x0 = 0; w.nx = Nx + dx; } else { w.x0 = dx; w.nx = Nx - dx; }
+    return w;
+}
+
+// ---------------------------------------------------------------- max_pixel
+// first row-major argmax of the 5x5 window around (cy,cx); executed by warp 0,
+// result broadcast through `out` (shared int[2]); caller syncs.
+__device__ __forceinline__ void scl_max_pixel(const float* X, int Ny, int Nx, int cy, int cx, int* out) {
+    if (threadIdx.x < 32) {
+        int l = threadIdx.x;
+        int ys = max(cy - 2, 0), ye = min(cy + 3, Ny), xs = max(cx - 2, 0), xe = min(cx + 3, Nx);
+        int wy = ye - ys, wx = xe - xs;
+        float v = -INFINITY;
+        int idx = 0x7fffffff;
+        if (l < wy * wx) {
+            int y = ys + l / wx, x = xs + l % wx;
+            v = X[y * Nx + x];
+            idx = l;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            float v2 = __shfl_xor_sync(0xffffffffu, v, o);
+            int i2 = __shfl_xor_sync(0xffffffffu, idx, o);
+            if (v2 > v || (v2 == v && i2 < idx)) { v = v2; idx = i2; }
+        }
+        if (l == 0) {
+            if (idx == 0x7fffffff) { out[0] = cy; out[1] = cx; }
+            else { out[0] = ys + idx / wx; out[1] = xs + idx % wx; }
+        }
+    }
+}
+
+// ---------------------------------------------------------------- centroid
+// all threads call; results (new centre, shift) written by thread 0 into outc/outs (shared)
+__device__ __forceinline__ void scl_centroid(const float* X, int Ny, int Nx, const float* __restrict__ psf,
+                                             int ph, int pw, int cy, int cx, int* outc, double* outs, double* red) {
+    int rad = pw / 2;
+    int ry = min(min(cy, Ny - 1 - cy), rad), rx = min(min(cx, Nx - 1 - cx), rad);
+    int wy = 2 * ry + 1, wx = 2 * rx + 1;
+    double sw = 0.0, sy = 0.0, sx = 0.0;
+    for (int i = threadIdx.x; i < wy * wx; i += blockDim.x) {
+        int iy = i / wx, ix = i % wx;
+        float w = X[(cy - ry + iy) * Nx + (cx - rx + ix)] * psf[(rad - ry + iy) * pw + (rad - rx + ix)];
+        sw += (double)w;
+        sy += (double)iy * (double)w;
+        sx += (double)ix * (double)w;
+    }
+    sw = block_sum<double>(sw, red);
+    sy = block_sum<double>(sy, red);
+    sx = block_sum<double>(sx, red);
+    if (threadIdx.x == 0) {
+        double wsum = (double)(float)sw;         // the reference sums the f32 products in f32
+        double my = sy / wsum, mx = sx / wsum;
+        double wyr = rint(my), wxr = rint(mx);   // np.round: half to even
+        outs[0] = wyr - my;
+        outs[1] = wxr - mx;
+        outc[0] = (int)(wyr + (double)(cy - ry));
+        outc[1] = (int)(wxr + (double)(cx - rx));
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------- symmetry
+// Dirichlet-kernel tables of the k-space symmetry operator in real space
+// (DESIGN.md "symmetry"): T[m], H[m] for m = 0..2n-2 (index p_i + p_j - 2o).
+//   T = (1/F)[1 + 2 sum_{k=1}^{M} cos(k th)] (+ (-1)^m cos(pi a)/F on the rfft axis)
+//   H = (1/F)[ -2 sum_{k=1}^{M} sin(k th)]   (+ (-1)^m sin(pi a)/F on the rfft axis)
+// th = 2 pi (m + 2o - a)/F, a = 2*shift, M = (F-1)/2, o = (F-n+1)/2 - F/2.
+__device__ __forceinline__ void scl_dirichlet(float* T, float* H, int n, int F, double a, bool rfft_axis) {
+    int o = (F - n + 1) / 2 - F / 2;
+    int M = (F - 1) / 2;
+    for (int i = threadIdx.x; i < 2 * n - 1; i += blockDim.x) {
+        int m = i + 2 * o;
+        double th = 2.0 * M_PI * ((double)m - a) / (double)F;
+        double s2, c2;
+        sincos(0.5 * th, &s2, &c2);
+        double D, Ssum;
+        if (fabs(s2) < 1e-14) { D = 2.0 * M + 1.0; Ssum = 0.0; }
+        else {
+            double sm, cm;
+            sincos(((double)M + 0.5) * th, &sm, &cm);
+            D = sm / s2;
+            Ssum = (c2 - cm) / (2.0 * s2);
+        }
+        double t = D / F, h = -2.0 * Ssum / F;
+        if (rfft_axis && (F % 2 == 0)) {
+            double sg = (m & 1) ? -1.0 : 1.0;
+            double sa, ca;
+            sincospi(a, &sa, &ca);
+            t += sg * ca / F;
+            h += sg * sa / F;
+        }
+        T[i] = (float)t;
+        if (H) H[i] = (float)h;
+    }
+}
+
+// k-space symmetry on the window w of X (in place).  Z: scratch of ny*nx floats;
+// tab: scratch of >= 3*(2*max(ny,nx)-1) + 2*nx floats.  nfl: next_fast_len table
+// (nfl[n] = smallest 5-smooth >= n), nfl_even likewise but even.
+__device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, double dx,
+                                    float* Z, float* tab, const int* __restrict__ nfl,
+                                    const int* __restrict__ nfl_even) {
+    const int ny = w.ny, nx = w.nx;
+    const int Fy = nfl[2 * ny + 10], Fx = nfl_even[2 * nx + 10];
+    float* Ty = tab;
+    float* Tx = Ty + (2 * ny - 1);
+    float* Hx = Tx + (2 * nx - 1);
+    float* bvec = Hx + (2 * nx - 1);      // nx
+    float* vvec = bvec + nx;              // nx
+    scl_dirichlet(Ty, nullptr, ny, Fy, 2.0 * dy, false);
+    scl_dirichlet(Tx, Hx, nx, Fx, 2.0 * dx, true);
+    __syncthreads();
+    float* Xw = X + w.y0 * Nx + w.x0;
+    // Z[i][j] = sum_l Xw[i][l] Tx[j + l]      (4x4 register tiles)
+    const int ty4 = (ny + 3) / 4, tx4 = (nx + 3) / 4;
+    for (int tile = threadIdx.x; tile < ty4 * tx4; tile += blockDim.x) {
+        int i0 = (tile / tx4) * 4, j0 = (tile % tx4) * 4;
+        float acc[4][4] = {};
+        for (int l = 0; l < nx; l++) {
+            float xv[4], tv[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) xv[r] = (i0 + r < ny) ? Xw[(i0 + r) * Nx + l] : 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; c++) tv[c] = (j0 + c < nx) ? Tx[j0 + c + l] : 0.f;
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[r][c] += xv[r] * tv[c];
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++)
+                if (i0 + r < ny && j0 + c < nx) Z[(i0 + r) * nx + j0 + c] = acc[r][c];
+    }
+    const bool nyq = (Fy % 2 == 0);
+    const int oy = (Fy - ny + 1) / 2 - Fy / 2;
+    if (nyq) {
+        // b[l] = sum_i (-1)^{p_i} Xw[i][l]
+        for (int l = threadIdx.x; l < nx; l += blockDim.x) {
+            float s = 0.f;
+            for (int i = 0; i < ny; i++) s += (((i + oy) & 1) ? -1.f : 1.f) * Xw[i * Nx + l];
+            bvec[l] = s;
+        }
+    }
+    __syncthreads();
+    if (nyq) {
+        double sphi, cphi;
+        sincospi(2.0 * dy, &sphi, &cphi);
+        float cf = (float)(cphi / Fy), sf = (float)(sphi / Fy);
+        for (int j = threadIdx.x; j < nx; j += blockDim.x) {
+            float s1 = 0.f, s2 = 0.f;
+            for (int l = 0; l < nx; l++) { s1 += Tx[j + l] * bvec[l]; s2 += Hx[j + l] * bvec[l]; }
+            vvec[j] = cf * s1 + sf * s2;
+        }
+        __syncthreads();
+    }
+    // Y[i][j] = sum_l Ty[i + l] Z[l][j];  X <- (X <= 0) ? 0 : (X + Y)/2
+    for (int tile = threadIdx.x; tile < ty4 * tx4; tile += blockDim.x) {
+        int i0 = (tile / tx4) * 4, j0 = (tile % tx4) * 4;
+        float acc[4][4] = {};
+        for (int l = 0; l < ny; l++) {
+            float tv[4], zv[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) tv[r] = (i0 + r < ny) ? Ty[i0 + r + l] : 0.f;
+#pragma unroll
+            for (int c = 0; c < 4; c++) zv[c] = (j0 + c < nx) ? Z[l * nx + j0 + c] : 0.f;
+#pragma unroll
+            for (int r = 0; r < 4; r++)
+#pragma unroll
+                for (int c = 0; c < 4; c++) acc[r][c] += tv[r] * zv[c];
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                int i = i0 + r, j = j0 + c;
+                if (i < ny && j < nx) {
+                    float y = acc[r][c];
+                    if (nyq) y += (((i + oy) & 1) ? -1.f : 1.f) * vvec[j];
+                    float x = Xw[i * Nx + j];
+                    Xw[i * Nx + j] = (x <= 0.f) ? 0.f : 0.5f * (x + y);
+                }
+            }
+    }
+    __syncthreads();
+}
+
+// soft (strength s) or sdss symmetry on window w, in place.  Pairs (p, flip(p)).
+__device__ __forceinline__ void scl_flip_symmetry(float* X, int Nx, SclWindow w, int sdss, float strength) {
+    int n = w.ny * w.nx;
+    float* Xw = X + w.y0 * Nx + w.x0;
+    for (int i = threadIdx.x; i < (n + 1) / 2; i += blockDim.x) {
+        int j = n - 1 - i;
+        int iy = i / w.nx, ix = i % w.nx, jy = j / w.nx, jx = j % w.nx;
+        float a = Xw[iy * Nx + ix], b = Xw[jy * Nx + jx];
+        float na, nb;
+        if (sdss) { na = fminf(a, b); nb = na; }
+        else {
+            na = 0.5f * strength * (a + b) + (1.f - strength) * a;
+            nb = 0.5f * strength * (b + a) + (1.f - strength) * b;
+        }
+        Xw[iy * Nx + ix] = na;
+        Xw[jy * Nx + jx] = nb;
+    }
+    __syncthreads();
+}
+
+// ---------------------------------------------------------------- monotonicity
+// Radius-ordered wavefront of the sequential sweep of operators_pybind11.cc:27-50.
+// Pixel at offset (Y,X) from the peak only reads strictly closer 8-neighbours
+// (operator.py:569-571), all of which lie on a lower level
+//     level(Y,X) = 2 max(|Y|,|X|) + min(|Y|,|X|) - 1,
+// so processing level by level (any order inside a level) reproduces the
+// radius-sorted sequential result bit for bit (tests/test_wavefront_order.py).
+//
+// Weights: wtab  f32 [(2Ny-1)(2Nx-1)][8]  normalised weights of an interior pixel
+//          ctab  f64 [(2Ny-1)(2Nx-1)][8]  un-normalised cosines (0 where the tap is not
+//                                          strictly closer), for pixels on the image border
+// both indexed by (Y + Ny-1, X + Nx-1) and built on the host with the reference's
+// own formula (scarlet_b200/operator.py:monotonic_tables).
+__device__ __forceinline__ float scl_mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double scl_mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float scl_add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double scl_add_rn(double a, double b) { return __dadd_rn(a, b); }
+
+// T = float: the f32 overload (weights rounded to f32 first, operators_pybind11.cc:82-83);
+// T = double: the f64 overload.  NEAREST: prox_monotonic (operators_pybind11.cc:11-25) with
+// the single best-aligned closer neighbour as reference (operator.py:602-611).
+template <typename T, bool NEAREST>
+__device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
+                                               const float* __restrict__ wtab, const double* __restrict__ ctab,
+                                               T one_minus_thresh) {
+    const int ti = ((Yo + Ny - 1) * (2 * Nx - 1) + (Xo + Nx - 1)) * 8;
+    T w[8];
+    const bool border = (y == 0) | (y == Ny - 1) | (x == 0) | (x == Nx - 1);
+    if (sizeof(T) == 4 && !NEAREST && !border) {
+        const float4 w0 = *reinterpret_cast<const float4*>(wtab + ti);
+        const float4 w1 = *reinterpret_cast<const float4*>(wtab + ti + 4);
+        w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w;
+        w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+    } else {
+        double c[8], s = 0.0;
+        int best = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+            int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
+            bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
+            c[i] = in ? ctab[ti + i] : 0.0;
+            s = s + c[i];
+            if (c[i] > c[best]) best = i;
+        }
+        if (NEAREST) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) w[i] = (i == best) ? (T)1 : (T)0;
+        } else {
+            if (s == 0.0) s = 1.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) w[i] = (T)(c[i] / s);
+        }
+    }
+    T ref = 0;
+    const int p = y * Nx + x;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+        int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
+        if (w[i] > (T)0) {
+            if (NEAREST) ref = X[p + oy * Nx + ox];
+            else ref = scl_add_rn(ref, scl_mul_rn(X[p + oy * Nx + ox], w[i]));
+        }
+    }
+    T r = scl_mul_rn(ref, one_minus_thresh);
+    T cur = X[p];
+    X[p] = (r < cur) ? r : cur;
+}
+
+template <typename T, bool NEAREST>
+__device__ void scl_monotonic(T* X, int Ny, int Nx, int cy, int cx,
+                              const float* __restrict__ wtab, const double* __restrict__ ctab, T thresh) {
+    const T omt = (T)1 - thresh;
+    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
+    const int vmax = 2 * max(ay, ax) + min(ay, ax);       // v = level + 1 = 2a + b
+    const int slot = threadIdx.x >> 3, oct = threadIdx.x & 7;
+    const int nslot = blockDim.x >> 3;
+    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
+    __syncthreads();
+    if (NEAREST && threadIdx.x == 0) {
+        // the peak refers to itself (operator.py:641-647): x = min(x, x (1 - thresh))
+        T cur = X[cy * Nx + cx], r = scl_mul_rn(cur, omt);
+        X[cy * Nx + cx] = (r < cur) ? r : cur;
+    }
+    __syncthreads();
+    for (int v = 1; v <= vmax; v++) {
+        const int amin = (v + 2) / 3, amax = v / 2;
+        for (int a = amin + slot; a <= amax; a += nslot) {
+            const int bb = v - 2 * a;
+            // drop duplicate images of the same pixel
+            if ((bb == 0 && sb) || (a == bb && sw)) continue;
+            const int pa = sa ? -a : a, pb = sb ? -bb : bb;
+            const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
+            const int y = cy + Yo, x = cx + Xo;
+            if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
+            scl_mono_pixel<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
+        }
+        __syncthreads();
+    }
+}

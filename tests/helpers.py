@@ -1,0 +1,127 @@
+"""Shared test helpers: pack an oracle Blend into the arrays of scarlet_b200._native.Batch."""
+import os
+import numpy as np
+
+from oracle import ref_blend as rb
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def npz_blend(tag, dtype=np.float32):
+    """Oracle scene for configs 1 ("hsc") and 2 ("sim"), built from the input fixtures."""
+    fn = {"hsc": "hsc_cosmos_inputs.npz", "sim": "psf_unmatched_sim_inputs.npz"}[tag]
+    d = np.load(os.path.join(GOLD, fn))
+    images, psfs = d["images"], d["psfs"]
+    mpsf = rb.generate_psf_image(rb.gaussian, psfs[0].shape, sigma=.9)
+    frame = rb.Frame(images.shape, psfs=mpsf[None], dtype=dtype)
+    obs = rb.Observation(images, psfs=psfs).match(frame)
+    bg = np.ones(len(images), dtype=images.dtype) * float(d["bg_rms"])
+    srcs = []
+    for (y, x), star in zip(d["coords"], d["is_star"]):
+        if star:
+            srcs.append(rb.PointSource(frame, (y, x), obs, fix_morph=True))
+        else:
+            srcs.append(rb.ExtendedSource(frame, (y, x), obs, bg))
+    return frame, obs, srcs, rb.Blend(srcs, obs)
+
+
+def synthetic_blend(seed, C=5, Ny=64, Nx=64, kmin=2, kmax=8, psf_size=41, dtype=np.float32, _cache={}):
+    """One synthetic blend of BASELINE config 3, oracle objects."""
+    rng = np.random.default_rng(20260411 + seed)
+    key = (C, psf_size)
+    if key not in _cache:
+        mpsf = rb.generate_psf_image(rb.gaussian, (psf_size, psf_size), sigma=.9)
+        psfs = np.array([rb.generate_psf_image(rb.gaussian, (psf_size, psf_size), sigma=1.2 + .15 * b)
+                         for b in range(C)])
+        _cache[key] = (mpsf, psfs)
+    mpsf, psfs = _cache[key]
+    K = int(rng.integers(kmin, kmax + 1))
+    centers = []
+    while len(centers) < K:
+        c = rng.uniform(12, min(Ny, Nx) - 12, 2)
+        if all(np.hypot(*(c - o)) >= 6 for o in centers):
+            centers.append(c)
+    yy, xx = np.indices((Ny, Nx))
+    images = np.zeros((C, Ny, Nx))
+    for c in centers:
+        re, n = rng.uniform(1.5, 5), rng.uniform(.7, 2.5)
+        q, pa = rng.uniform(.5, 1), rng.uniform(0, np.pi)
+        dy, dx = yy - c[0], xx - c[1]
+        u = dx * np.cos(pa) + dy * np.sin(pa)
+        v = (-dx * np.sin(pa) + dy * np.cos(pa)) / q
+        morph = np.exp(-(np.hypot(u, v) / re) ** (1 / n))
+        sed = rng.dirichlet(np.ones(C)) * 10 ** rng.uniform(np.log10(50), np.log10(5000))
+        from scipy.signal import fftconvolve
+        for b in range(C):
+            images[b] += sed[b] * fftconvolve(morph, psfs[b], mode="same")
+    images += rng.normal(0, 1, images.shape)
+    images = images.astype(dtype)
+    weights = np.ones(images.shape, dtype=dtype)
+    frame = rb.Frame(images.shape, psfs=mpsf[None], dtype=dtype)
+    obs = rb.Observation(images, psfs=psfs.astype(dtype), weights=weights).match(frame)
+    bg = np.ones(C, dtype=dtype)
+    srcs = []
+    for c in centers:
+        try:
+            srcs.append(rb.ExtendedSource(frame, (int(round(c[0])), int(round(c[1]))), obs, bg))
+        except rb.SourceInitError:
+            pass
+    return frame, obs, srcs, rb.Blend(srcs, obs)
+
+
+def pack(blends):
+    """Arrays for _native.Batch from oracle Blend objects sharing one frame shape."""
+    from scarlet_b200 import _native as nat
+    C, Ny, Nx = blends[0].frame.shape
+    comp_off, sed, morph, cflags, center, shift, conv = [0], [], [], [], [], [], []
+    images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
+    spec_cache, cw_cache = {}, {}
+    any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
+    for bl in blends:
+        obs = bl.observations[0]
+        for s in bl.sources:
+            for c in s.components:
+                f = 0
+                if isinstance(s, rb.PointSource):
+                    f |= nat.F_CONSTRAINED | nat.F_KSPACE
+                    if s.symmetric:
+                        f |= nat.F_SYMMETRIC
+                    if s.monotonic:
+                        f |= nat.F_MONOTONIC
+                if c.fix_sed:
+                    f |= nat.F_FIX_SED
+                if c.fix_morph:
+                    f |= nat.F_FIX_MORPH
+                cflags.append(f)
+                sed.append(c.sed)
+                morph.append(c.morph)
+                center.append(getattr(s, "pixel_center", (Ny // 2, Nx // 2)))
+                shift.append(getattr(s, "shift", (0., 0.)))
+                conv.append(c.flags)
+        comp_off.append(len(sed))
+        images.append(obs.images)
+        if any_w:
+            weights.append(obs.weights if isinstance(obs.weights, np.ndarray) else np.ones_like(obs.images))
+        if obs.diff_kernels is None:
+            ker_idx += [-1] * C
+        else:
+            key = obs.diff_kernels.tobytes()
+            if key not in spec_cache:
+                spec_cache[key] = len(specs)
+                specs.append(nat.kernel_spectrum(obs.diff_kernels, Ny, Nx))
+            base = spec_cache[key] * C
+            ker_idx += [base + c for c in range(C)]
+        cw = rb._centroid_weight(bl.frame).astype(np.float32)
+        key = cw.tobytes()
+        if key not in cw_cache:
+            cw_cache[key] = len(cws)
+            cws.append(cw)
+        cw_idx.append(cw_cache[key])
+        it0.append(bl.it)
+        prev.append(bl.mse[-1] if bl.mse else 0.)
+    return dict(C=C, Ny=Ny, Nx=Nx, comp_off=np.array(comp_off), sed=np.array(sed), morph=np.array(morph),
+                cflags=np.array(cflags), center=np.array(center), shift=np.array(shift, dtype=np.float64),
+                conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
+                kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
+                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev))

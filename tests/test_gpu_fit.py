@@ -1,0 +1,156 @@
+"""GPU parity of the fused Blend.fit loop (through the C ABI) against the oracle."""
+import copy
+import numpy as np
+import pytest
+from numpy.testing import assert_array_equal, assert_allclose
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+
+REL = 1e-5      # north_star tolerance on per-iteration logL and on the model (fp32)
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from scarlet_b200 import _native
+    _native.require_device()
+    return _native
+
+
+def _model(out, k0, k1):
+    return np.einsum("kc,kyx->cyx", out["sed"][k0:k1].astype(np.float64), out["morph"][k0:k1].astype(np.float64))
+
+
+def _lockstep(nat, blend, n_steps, e_rel=1e-2):
+    """Each iteration: start the GPU from the oracle's state, run one iteration on both,
+    compare everything the iteration produces."""
+    for step in range(n_steps):
+        p = helpers.pack([blend])
+        bt = nat.Batch(**p)
+        bt.fit(1, e_rel)
+        out = bt.download()
+        bt.close()
+        conv = blend.step(e_rel)
+        assert_allclose(out["logL"][0, 0], blend.mse[-1], rtol=REL)
+        assert_allclose(out["lipschitz"][0], [blend.L_sed, blend.L_morph], rtol=2e-6)
+        ref_c = np.array([getattr(s, "pixel_center", (0, 0)) for s in blend.sources for _ in s.components])
+        con = np.array([isinstance(s, helpers.rb.PointSource) for s in blend.sources for _ in s.components])
+        assert_array_equal(out["center"][con], ref_c[con])                      # index work: exact
+        ref_s = np.array([getattr(s, "shift", (0, 0)) for s in blend.sources for _ in s.components], dtype=np.float64)
+        assert_allclose(out["shift"][con], ref_s[con], rtol=0, atol=5e-6)
+        sed = np.array([c.sed for c in blend.components])
+        morph = np.array([c.morph for c in blend.components])
+        assert_allclose(out["sed"], sed, rtol=0, atol=REL * np.abs(sed).max())
+        assert_allclose(out["morph"], morph, rtol=0, atol=REL)
+        assert_array_equal(out["conv"], [c.flags for c in blend.components])
+        assert out["active"][0] == (0 if conv else 1)
+        if conv:
+            break
+
+
+@pytest.mark.parametrize("tag", ["hsc", "sim"])
+def test_lockstep_npz(nat, tag):
+    """configs 1 and 2, every iteration until the oracle converges"""
+    _, _, _, blend = helpers.npz_blend(tag)
+    _lockstep(nat, blend, 60)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_lockstep_synthetic(nat, seed):
+    _, _, _, blend = helpers.synthetic_blend(seed)
+    _lockstep(nat, blend, 12)
+
+
+@pytest.mark.parametrize("tag", ["hsc", "sim"])
+def test_free_running_vs_reference(nat, golden, tag):
+    """Whole fit on the GPU vs the reference's own run (tests/golden): iteration count, per-iteration
+    logL, centres and the final model."""
+    _, _, _, blend = helpers.npz_blend(tag)
+    bt = nat.Batch(**helpers.pack([blend]))
+    bt.fit(200, 1e-2)
+    out = bt.download()
+    bt.close()
+    ref = golden[tag + "_mse"]
+    assert out["n_iter"][0] == len(ref)
+    assert out["active"][0] == 0
+    assert_allclose(out["logL"][0, :len(ref)], ref, rtol=5 * REL)
+    assert_array_equal(out["center"], golden[tag + "_centers"])
+    model = _model(out, 0, len(out["sed"]))
+    assert_allclose(model, golden[tag + "_model"], rtol=0, atol=5 * REL * np.abs(golden[tag + "_model"]).max())
+
+
+def test_batch_matches_single(nat):
+    """A heterogeneous batch (different K) gives the same answers as blend-by-blend runs, and blends that
+    converge early stop being updated."""
+    blends = [helpers.synthetic_blend(s)[3] for s in range(6)]
+    packs = helpers.pack(blends)
+    bt = nat.Batch(**packs)
+    info = bt.fit(40, 1e-2, check_every=4)
+    out = bt.download()
+    bt.close()
+    assert info["launches"] > 0
+    off = packs["comp_off"]
+    for i, bl in enumerate(blends):
+        b1 = nat.Batch(**helpers.pack([bl]))
+        b1.fit(40, 1e-2)
+        o1 = b1.download()
+        b1.close()
+        n = o1["n_iter"][0]
+        assert out["n_iter"][i] == n
+        assert_array_equal(out["logL"][i, :n], o1["logL"][0, :n])
+        assert_array_equal(out["morph"][off[i]:off[i + 1]], o1["morph"])
+        assert_array_equal(out["sed"][off[i]:off[i + 1]], o1["sed"])
+
+
+def test_free_running_synthetic_vs_oracle(nat):
+    blends = [helpers.synthetic_blend(s)[3] for s in range(4)]
+    packs = helpers.pack(blends)
+    bt = nat.Batch(**packs)
+    bt.fit(25, 0.0)            # e_rel = 0: fixed iteration count
+    out = bt.download()
+    bt.close()
+    off = packs["comp_off"]
+    for i, bl in enumerate(blends):
+        bl.fit(25, 0.0)
+        assert out["n_iter"][i] == 25
+        assert_allclose(out["logL"][i, :25], np.array(bl.mse, dtype=np.float64), rtol=20 * REL)
+        assert_array_equal(out["center"][off[i]:off[i + 1]], [s.pixel_center for s in bl.sources])
+
+
+def test_continue_fit_and_approximate_L(nat):
+    """fit() called twice continues (blend.py:79, it = len(mse)); approximate_L path (blend.py:189-202)."""
+    _, _, _, blend = helpers.npz_blend("hsc")
+    ref = copy.deepcopy(blend)
+    bt = nat.Batch(**helpers.pack([blend]))
+    bt.fit(3, 1e-2, approximate_L=True)
+    o = bt.download()
+    bt.close()
+    ref.fit(3, 1e-2, approximate_L=True)
+    assert_allclose(o["logL"][0, :3], np.array(ref.mse, dtype=np.float64), rtol=REL)
+    # second call starts from it0 = 3: centroid schedule keyed on the absolute iteration
+    p = helpers.pack([ref])
+    assert p["it0"][0] == 3
+    bt = nat.Batch(**p)
+    bt.fit(4, 1e-2)
+    o = bt.download()
+    bt.close()
+    ref.fit(4, 1e-2)
+    assert_allclose(o["logL"][0, :o["n_iter"][0]], np.array(ref.mse[3:], dtype=np.float64), rtol=REL)
+    assert_array_equal(o["center"], [s.pixel_center for s in ref.sources])
+
+
+def test_empty_and_errors(nat):
+    _, _, _, blend = helpers.npz_blend("sim")
+    p = helpers.pack([blend])
+    bad = dict(p)
+    bad["center"] = p["center"].copy()
+    bad["center"][0] = (999, 0)
+    with pytest.raises(ValueError):
+        nat.Batch(**bad)
+    bt = nat.Batch(**p)
+    bt.fit(0)
+    out = bt.download()
+    assert out["n_iter"][0] == 0
+    assert_array_equal(out["morph"], p["morph"].astype(np.float32))
+    bt.close()

@@ -1,0 +1,147 @@
+"""GPU parity of the array-level operators, called through the C ABI, against
+the oracle and the reference fixtures."""
+import numpy as np
+import pytest
+from numpy.testing import assert_array_equal, assert_allclose
+
+from oracle import ref_prox, ref_fft, ref_blend
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def nat():
+    from scarlet_b200 import _native
+    _native.require_device()
+    return _native
+
+
+def test_monotonic_kat(nat):
+    """reference tests/test_operator.py:30-56 through the CUDA wavefront (f64 and f32)."""
+    X = np.arange(25).reshape(1, 5, 5).astype(np.float64)
+    Y = X.copy()
+    nat.prox_weighted_monotonic(Y, [(2, 2)], 0.25)
+    gold = X[0].copy()
+    ref_prox.build_monotonic((5, 5), None, .25)(gold)
+    assert_array_equal(Y[0], gold)
+    Y = X.copy()
+    nat.prox_monotonic_nearest(Y, [(2, 2)], 0.0)
+    assert_array_equal(Y[0], [[0, 1, 2, 3, 4], [5, 6, 7, 8, 9], [10, 11, 12, 12, 12],
+                              [11, 12, 12, 12, 12], [12, 12, 12, 12, 12]])
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_monotonic_vs_reference_fixture(nat, golden, tag):
+    shape = tuple(golden["mono_%s_shape" % tag])
+    center = tuple(golden["mono_%s_center" % tag])
+    for dt in ("float32", "float64"):
+        for th, t in ((0, 0), (.1, 1)):
+            x = golden["mono_%s_in_%s" % (tag, dt)].copy()[None]
+            nat.prox_weighted_monotonic(x, [center], th)
+            assert_array_equal(x[0], golden["mono_%s_out_%s_t%d" % (tag, dt, t)])   # bit-exact
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (69, 57), (40, 59), (7, 100)])
+def test_monotonic_random_centres_bit_exact(nat, shape):
+    rng = np.random.default_rng(3)
+    n = 24
+    centers = np.stack([rng.integers(0, shape[0], n), rng.integers(0, shape[1], n)], axis=1)
+    centers[0] = (0, 0)
+    centers[1] = (shape[0] - 1, shape[1] - 1)
+    centers[2] = (shape[0] // 2, shape[1] // 2)
+    for dt in (np.float32, np.float64):
+        x = (rng.random((n,) + shape) - .2).astype(dt)
+        y = x.copy()
+        nat.prox_weighted_monotonic(y, centers, 0.1 if dt == np.float64 else 0.0)
+        for i in range(n):
+            g = x[i].copy()
+            ref_prox.build_monotonic(shape, tuple(centers[i]), 0.1 if dt == np.float64 else 0.0)(g)
+            assert_array_equal(y[i], g)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d", "e"])
+def test_symmetry_vs_reference_fixture(nat, golden, tag):
+    x64 = golden["sym_%s_in" % tag]
+    c = tuple(golden["sym_%s_center" % tag])
+    shift = tuple(golden["sym_%s_shift" % tag])
+    x = x64.astype(np.float32)[None]
+    for mode, key in (("soft", "soft"), ("sdss", "sdss")):
+        y = x.copy()
+        nat.prox_symmetry(y, [c], None, mode, 1.0)
+        assert_array_equal(y[0], golden["sym_%s_%s" % (tag, key)].astype(np.float32))
+    y = x.copy()
+    nat.prox_symmetry(y, [c], [shift], "kspace")
+    gold = x64.astype(np.float32).astype(np.float64)
+    sl = ref_prox.uncentered_slices(gold.shape, c)
+    if sl is None:
+        gold = ref_prox.prox_kspace_symmetry(gold, 0, shift)     # what a caller of the operator gets
+    else:
+        gold[sl] = ref_prox.prox_kspace_symmetry(gold[sl], 0, shift)
+    assert_allclose(y[0], gold, rtol=0, atol=2e-6 * np.abs(gold).max())
+
+
+def test_symmetry_random(nat):
+    rng = np.random.default_rng(5)
+    shape, n = (64, 64), 16
+    x = rng.random((n,) + shape).astype(np.float32)
+    x[rng.random(x.shape) < .2] = 0
+    centers = np.stack([rng.integers(3, 61, n), rng.integers(3, 61, n)], axis=1)
+    shifts = rng.uniform(-.5, .5, (n, 2))
+    y = x.copy()
+    nat.prox_symmetry(y, centers, shifts, "kspace")
+    for i in range(n):
+        g = x[i].astype(np.float64)
+        ref_prox.prox_uncentered_symmetry(g, 0, tuple(centers[i]), "kspace", None, tuple(shifts[i]))
+        assert_allclose(y[i], g, rtol=0, atol=3e-6)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_measure_vs_reference_fixture(nat, golden, tag):
+    m = golden["meas_%s_in" % tag][None]
+    c = tuple(golden["meas_%s_center" % tag])
+    cc, _ = nat.measure(m, [c], None, True, False)
+    assert_array_equal(cc[0], golden["meas_%s_maxpix" % tag])
+    cc, ss = nat.measure(m, [c], golden["psf_target_41"].astype(np.float32), False, True)
+    assert_array_equal(cc[0], golden["meas_%s_centroid" % tag])
+    assert_allclose(ss[0], golden["meas_%s_shift" % tag], rtol=0, atol=2e-6)
+
+
+def test_convolve_vs_oracle(nat, golden):
+    """Observation.render on the reference's test_blend scene (tests/test_blend.py:56-73), f32."""
+    rng = np.random.default_rng(7)
+    dk = golden["tb_diff_kernels"].astype(np.float32)
+    C, Ny, Nx = 6, 31, 55
+    model = rng.random((2, C, Ny, Nx)).astype(np.float32)
+    spec = nat.kernel_spectrum(dk, Ny, Nx)
+    idx = np.tile(np.arange(C), 2)
+    out = nat.convolve(model, spec, idx)
+    adj = nat.convolve(model, spec, idx, adjoint=True)
+    for i in range(2):
+        ref = ref_fft.convolve(model[i].astype(np.float64), dk.astype(np.float64), axes=(1, 2))
+        assert_allclose(out[i], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+        ref = ref_fft.correlate(model[i].astype(np.float64), dk.astype(np.float64), axes=(1, 2))
+        assert_allclose(adj[i], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+    out = nat.convolve(model, None, -np.ones(2 * C))
+    assert_array_equal(out, model)
+
+
+def test_convolve_shapes(nat):
+    rng = np.random.default_rng(8)
+    for (Ny, Nx, k) in [(64, 64, 41), (69, 57, 41), (40, 59, 31), (3, 5, 7), (64, 64, 16)]:
+        ker = rng.random((1, k, k))
+        model = rng.random((1, 1, Ny, Nx)).astype(np.float32)
+        out = nat.convolve(model, nat.kernel_spectrum(ker, Ny, Nx), [0])
+        ref = ref_fft.convolve(model[0].astype(np.float64), ker, axes=(1, 2))
+        assert_allclose(out[0], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+
+
+def test_errors(nat):
+    x = np.zeros((1, 5, 5), np.float32)
+    with pytest.raises(ValueError):
+        nat.prox_weighted_monotonic(x, [(7, 0)])
+    with pytest.raises(TypeError):
+        nat.prox_weighted_monotonic(x.astype(np.int32), [(2, 2)])
+    with pytest.raises(NotImplementedError):
+        nat.kernel_spectrum(np.zeros((1, 41, 41)), 120, 64)
+    y = np.zeros((0, 5, 5), np.float32)
+    nat.prox_weighted_monotonic(y, np.zeros((0, 2)))          # empty batch is a no-op
