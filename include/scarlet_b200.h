@@ -60,7 +60,7 @@ int scl_prox_weighted_monotonic_f64(double* x, int n, int Ny, int Nx, const int3
 int scl_prox_monotonic_f64(double* x, int n, int Ny, int Nx, const int32_t* centers, double thresh, void* stream);
 /* operator.prox_uncentered_symmetry (operator.py:291-350).  mode 0 = "kspace" (shifts float64 [n][2] = (dy,dx),
  * operator.py:253-288), 1 = "soft" (strength), 2 = "sdss".  The window of operator.uncentered_operator
- * (operator.py:175-228) with fill=None is applied on the device. */
+ * (operator.py:175-228) with fill=None is applied on the device; a center of (-1,-1) selects the whole array. */
 int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* centers, const double* shifts,
                           int mode, float strength, void* stream);
 /* measurement.max_pixel (measurement.py:3-29) and/or measurement.psf_weighted_centroid (measurement.py:32-94).
@@ -112,6 +112,9 @@ int scl_batch_upload(scl_batch* batch, const scl_batch_desc* desc, void* stream)
  * k1_launches its launch count (only measured when profile != 0; adds event overhead). */
 int scl_batch_fit(scl_batch* batch, int max_iter, double e_rel, int approximate_L, int check_every,
                   int profile, float* device_ms, float* k1_ms, int* k1_launches, int* launches, void* stream);
+/* The constraint pass every source runs once at construction (`self.update()` with it = 0, source.py:400,492):
+ * max_pixel, centroid + shift, symmetry, monotonicity, positivity, normalisation on the batch's current state. */
+int scl_batch_constrain(scl_batch* batch, void* stream);
 /* Copy results back.  Any pointer may be NULL.  logL: [B][max_iter of the last fit] (Blend.mse entries appended
  * by that fit; n_iter[b] of them valid); active[b] == 0 <=> blend b converged. */
 int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* center, double* shift, int32_t* conv,

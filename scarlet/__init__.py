@@ -1,0 +1,8 @@
+"""`import scarlet` alias: the reference package name, served by scarlet_b200."""
+import sys
+import scarlet_b200
+from scarlet_b200 import *  # noqa: F401,F403
+from scarlet_b200 import fft, psf, operator, update, measurement, observation, component, source, blend  # noqa: F401
+
+for _n in ("fft", "psf", "operator", "update", "measurement", "observation", "component", "source", "blend"):
+    sys.modules["scarlet." + _n] = getattr(scarlet_b200, _n)

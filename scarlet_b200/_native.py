@@ -324,6 +324,10 @@ class Batch:
         self.max_iter = int(max_iter)
         return dict(device_ms=ms.value, k1_ms=k1.value, k1_launches=nk1.value, launches=nl.value)
 
+    def constrain(self):
+        """One `update()` pass with it = 0 on every component (what sources run at construction)."""
+        _check(lib().scl_batch_constrain(self._h, c_void_p(self.stream)))
+
     def download(self, morph=True):
         N = self.Ny * self.Nx
         out = dict(

@@ -1,0 +1,163 @@
+"""Blend: the scene and its fit (mirrors scarlet/blend.py).
+
+`Blend.fit` packs the components and observations into device buffers, runs the
+whole proximal-gradient loop (blend.py:65-102 of the reference) as CUDA kernels
+through the C ABI, and writes SEDs, morphologies, centres, flags and the loss
+history back.  `fit_many` does the same for any number of independent blends in
+one batched launch sequence (the reference has no batch notion; Blend.fit is a
+batch of one).
+"""
+import logging
+
+import numpy as np
+
+from .component import ComponentTree, Component, BlendFlag
+from .observation import LowResObservation
+from . import _native
+from .source import PointSource, component_flags, _centroid_weight
+
+logger = logging.getLogger("scarlet.blend")
+
+
+def _owner_of(blend):
+    """(source, component) pairs in component order."""
+    pairs = []
+    for s in blend.sources:
+        comps = s.components if isinstance(s, ComponentTree) else [s]
+        for c in comps:
+            if not any(c is p[1] for p in pairs):
+                pairs.append((s, c))
+    return pairs
+
+
+def pack_blends(blends):
+    """Arrays for _native.Batch from Blend objects that share one frame shape."""
+    C, Ny, Nx = blends[0].frame.shape
+    comp_off, sed, morph, cflags, center, shift, conv = [0], [], [], [], [], [], []
+    images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
+    spec_ids, cw_ids = {}, {}
+    any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
+    for bl in blends:
+        if bl.frame.shape != (C, Ny, Nx):
+            raise ValueError("all blends of a batch must share the frame shape")
+        if bl.frame.dtype != np.float32:
+            raise NotImplementedError("the CUDA loop computes in float32; use Frame(dtype=np.float32)")
+        if len(bl.observations) != 1:
+            raise NotImplementedError("multiple observations per blend are not implemented in scarlet_b200 yet")
+        obs = bl.observations[0]
+        if isinstance(obs, LowResObservation) or obs._band_slice != slice(None):
+            raise NotImplementedError("band-sliced / multi-resolution observations are not implemented yet")
+        for s, c in _owner_of(bl):
+            if c.prior is not None:
+                raise NotImplementedError("Prior callbacks cannot run inside the CUDA loop")
+            if isinstance(s, ComponentTree) and not isinstance(s, Component):
+                raise NotImplementedError("multi-component sources are not implemented in scarlet_b200 yet")
+            if not isinstance(s, PointSource) and type(s).update is not Component.update:
+                raise NotImplementedError("custom Python update() overrides cannot run inside the CUDA loop")
+            cflags.append(component_flags(s, c))
+            sed.append(c._sed)
+            morph.append(c._morph)
+            center.append(getattr(s, "pixel_center", (Ny // 2, Nx // 2)))
+            shift.append(getattr(s, "shift", (0., 0.)))
+            conv.append(c.flags.value & 3)
+        comp_off.append(len(sed))
+        images.append(obs.images)
+        if any_w:
+            weights.append(obs.weights if isinstance(obs.weights, np.ndarray)
+                           else np.ones(obs.images.shape, np.float32) * obs.weights)
+        spec = obs.kernel_spectrum()
+        if spec is None:
+            ker_idx += [-1] * C
+        else:
+            key = id(obs._diff_kernels.image) if len(blends) > 64 else obs._diff_kernels.image.tobytes()
+            if key not in spec_ids:
+                spec_ids[key] = len(specs)
+                specs.append(spec)
+            base = spec_ids[key] * C
+            ker_idx += [base + c for c in range(C)]
+        cw = np.asarray(_centroid_weight(bl.frame), dtype=np.float32)
+        key = id(bl.frame.psfs) if len(blends) > 64 else cw.tobytes()
+        if key not in cw_ids:
+            cw_ids[key] = len(cws)
+            cws.append(cw)
+        cw_idx.append(cw_ids[key])
+        it0.append(bl.it)
+        prev.append(float(bl.mse[-1]) if bl.mse else 0.)
+    return dict(C=C, Ny=Ny, Nx=Nx, comp_off=np.array(comp_off), sed=np.array(sed), morph=np.array(morph),
+                cflags=np.array(cflags), center=np.array(center), shift=np.array(shift, dtype=np.float64),
+                conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
+                kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
+                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev))
+
+
+def unpack_blends(blends, packed, out):
+    """Write the device results back into the Python objects."""
+    off = packed["comp_off"]
+    for i, bl in enumerate(blends):
+        n = int(out["n_iter"][i])
+        if out["logL"] is not None:
+            bl.mse.extend(float(v) for v in out["logL"][i, :n])
+        if n > 0:
+            bl.L_sed, bl.L_morph = float(out["lipschitz"][i, 0]), float(out["lipschitz"][i, 1])
+        for j, (s, c) in enumerate(_owner_of(bl)):
+            k = off[i] + j
+            c._sed = out["sed"][k].copy()
+            c._morph = out["morph"][k].copy()
+            if n > 0:
+                c._last_sed, c._last_morph = c._sed.copy(), c._morph.copy()      # blend.py:180-182
+            c.flags = (c.flags & ~(BlendFlag.SED_NOT_CONVERGED | BlendFlag.MORPH_NOT_CONVERGED)) | BlendFlag(int(out["conv"][k]))
+            c.L_sed, c.L_morph = getattr(bl, "L_sed", 1), getattr(bl, "L_morph", 1)
+            if isinstance(s, PointSource):
+                s.pixel_center = (int(out["center"][k, 0]), int(out["center"][k, 1]))
+                if s.symmetric:
+                    s.shift = (float(out["shift"][k, 0]), float(out["shift"][k, 1]))
+
+
+def fit_many(blends, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, stream=None):
+    """`Blend.fit` for a list of independent blends, batched on one GPU.
+    Returns the list of timing dicts (one per frame-shape group)."""
+    groups = {}
+    for bl in blends:
+        groups.setdefault(bl.frame.shape, []).append(bl)
+    infos = []
+    for shape, group in groups.items():
+        packed = pack_blends(group)
+        bt = _native.Batch(stream=stream, **packed)
+        try:
+            info = bt.fit(max_iter, e_rel, approximate_L, check_every)
+            out = bt.download()
+        finally:
+            bt.close()
+        unpack_blends(group, packed, out)
+        info.update(n_blends=len(group), shape=shape)
+        infos.append(info)
+    return infos
+
+
+class Blend(ComponentTree):
+    """The blended scene (blend.py:11-223)."""
+
+    def __init__(self, sources, observations):
+        ComponentTree.__init__(self, sources)
+        try:
+            iter(observations)
+        except TypeError:
+            observations = (observations,)
+        self.observations = observations
+        self.mse = []
+
+    @property
+    def it(self):
+        """Number of iterations run in the `fit` method"""
+        return len(self.mse)
+
+    @property
+    def converged(self):
+        for c in self.components:
+            if (c.flags & (BlendFlag.SED_NOT_CONVERGED | BlendFlag.MORPH_NOT_CONVERGED)).value > 0:
+                return False
+        return True
+
+    def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False):
+        """Fit the model for each source to the data (blend.py:65-102), on the GPU."""
+        fit_many([self], max_iter, e_rel, approximate_L)

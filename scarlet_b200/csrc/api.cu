@@ -196,9 +196,11 @@ int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* center
     int rc = check_shape(Ny, Nx);
     if (rc) return rc;
     if ((rc = ensure_globals())) return rc;
-    for (int i = 0; i < n; i++)
+    for (int i = 0; i < n; i++) {
+        if (centers[2 * i] == -1 && centers[2 * i + 1] == -1) continue;      // whole-array window
         if (centers[2 * i] < 0 || centers[2 * i] >= Ny || centers[2 * i + 1] < 0 || centers[2 * i + 1] >= Nx)
             return fail(SCL_E_ARG, "center outside the image%s%s");
+    }
     cudaStream_t s = (cudaStream_t)stream;
     size_t N = (size_t)Ny * Nx;
     DevBuf<float> dx;

@@ -29,6 +29,7 @@ struct SclProxArgs {
     const int* nfl;           // next_fast_len tables
     const int* nfl_even;
     int C, Ny, Nx, ph, pw, step;
+    int it_override;          // >= 0: the iteration number update() sees (0 = source construction)
     double e_rel2;
 };
 
@@ -49,7 +50,7 @@ scl_k_prox(SclProxArgs a)
     __shared__ double ss[2];
     __shared__ float sm;
     const unsigned fl = a.cflags[k];
-    const int it = a.it0[b] + a.step + 1;          // Blend.it seen by update() (len(mse))
+    const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
     const float* Sin = a.S_step + (size_t)k * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
@@ -193,7 +194,9 @@ scl_k_symmetry(float* __restrict__ imgs, const int* __restrict__ centers, const 
     float* g = imgs + (size_t)blockIdx.x * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
-    SclWindow w = scl_window(Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1]);
+    SclWindow w;
+    if (centers[2 * blockIdx.x] < 0) { w.y0 = 0; w.x0 = 0; w.ny = Ny; w.nx = Nx; w.centered = false; }   // whole array
+    else w = scl_window(Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1]);
     if (mode == 0) scl_kspace_symmetry(X, Nx, w, shifts[2 * blockIdx.x], shifts[2 * blockIdx.x + 1], Z, tab, nfl, nfl_even);
     else scl_flip_symmetry(X, Nx, w, mode == 2, strength);
     for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];

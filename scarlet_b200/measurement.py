@@ -1,0 +1,23 @@
+"""Centre measurement (mirrors scarlet/measurement.py:3-94), evaluated on the device."""
+import numpy as np
+
+from . import _native
+
+
+def max_pixel(morph, center=None, window=None):
+    """Pixel with the maximum flux in the 5x5 window around `center` (measurement.py:3-29)."""
+    if window is not None:
+        raise NotImplementedError("max_pixel: only the default 5x5 window runs on the device")
+    if center is None:
+        center = (morph.shape[0] // 2, morph.shape[1] // 2)
+    c, _ = _native.measure(np.asarray(morph, dtype=np.float32)[None], [(int(center[0]), int(center[1]))],
+                           None, True, False)
+    return (int(c[0, 0]), int(c[0, 1]))
+
+
+def psf_weighted_centroid(morph, psf, pixel_center):
+    """PSF-weighted first moments around `pixel_center` (measurement.py:32-94).
+    Returns (rounded centre, (dy, dx))."""
+    c, s = _native.measure(np.asarray(morph, dtype=np.float32)[None],
+                           [(int(pixel_center[0]), int(pixel_center[1]))], psf, False, True)
+    return (int(c[0, 0]), int(c[0, 1])), (float(s[0, 0]), float(s[0, 1]))
