@@ -1,0 +1,352 @@
+#!/usr/bin/env python
+"""bench.py -- blends/sec of `Blend.fit` on BASELINE config 3 (synthetic 5-band 64x64 blends, 2-8 ExtendedSources).
+
+One "step" = Blend.fit(max_iter=200, e_rel=1e-2) (the reference's defaults, blend.py:65) over the whole batch of
+blends resident on one GPU.  Ranks own disjoint blends (weak scaling: --blends per GPU), no collective inside the
+step; per-blend result records are all-gathered over NCCL after the step.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--blends B] [--impl b200|reference]
+
+Prints ONE JSON line (rank 0).  `value` = blends/s with inputs resident in HBM; `e2e` = the same through the
+C ABI with host buffers (upload + fit + download per step); `roofline` = the dominant kernel against the
+measured HBM peak; `cpu_baseline` = the CPU oracle (restatement of the reference, oracle/) on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "blends_per_sec"
+UNIT = "blends/s"
+WORKLOAD = "config3: synthetic 5-band 64x64 blends, 2-8 ExtendedSources, 41x41 PSFs, Blend.fit(200, e_rel=1e-2)"
+C, NY, NX, PSF = 5, 64, 64, 41
+MAX_ITER, E_REL = 200, 1e-2
+
+
+# ------------------------------------------------------------------------------------------ CPU side (oracle)
+def _cpu_worker(args):
+    """Fit a list of blends with the CPU oracle; returns (n_blends, n_iters, seconds in fit)."""
+    os.environ["OMP_NUM_THREADS"] = "1"
+    images, weights, psfs, mpsf, centers, max_iter, e_rel = args
+    from oracle import ref_blend as rb
+    tot_it, tot_t, nb = 0, 0.0, 0
+    for b in range(len(images)):
+        frame = rb.Frame(images[b].shape, psfs=mpsf, dtype=np.float32)
+        obs = rb.Observation(images[b], psfs=psfs, weights=weights[b]).match(frame)
+        bg = np.ones(images.shape[1], np.float32)
+        srcs = []
+        for (y, x) in centers[b]:
+            try:
+                srcs.append(rb.ExtendedSource(frame, (int(y), int(x)), obs, bg))
+            except rb.SourceInitError:
+                pass
+        if not srcs:
+            continue
+        blend = rb.Blend(srcs, obs)
+        t0 = time.perf_counter()
+        blend.fit(max_iter, e_rel)
+        tot_t += time.perf_counter() - t0
+        tot_it += blend.it
+        nb += 1
+    return nb, tot_it, tot_t
+
+
+def cpu_baseline(per_worker=6, max_workers=32, first_index=0):
+    """Oracle Blend.fit on a bounded sample of the same workload, one process per host core."""
+    import multiprocessing as mp
+    from scarlet_b200 import synth
+    subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle")])
+    cores = min(max_workers, len(os.sched_getaffinity(0)))
+    n = cores * per_worker
+    data = synth.make_blends(range(first_index, first_index + n), C, NY, NX, psf_size=PSF, device="cpu")
+    jobs = []
+    for w in range(cores):
+        sl = slice(w * per_worker, (w + 1) * per_worker)
+        jobs.append((data["images"][sl], data["weights"][sl], data["psfs"], data["model_psf"], data["centers"][sl],
+                     MAX_ITER, E_REL))
+    ctx = mp.get_context("spawn")
+    t0 = time.perf_counter()
+    with ctx.Pool(cores) as pool:
+        res = pool.map(_cpu_worker, jobs)
+    wall = time.perf_counter() - t0
+    nb = sum(r[0] for r in res)
+    its = sum(r[1] for r in res)
+    tmax = max(r[2] for r in res)
+    return dict(value=nb / tmax, unit=UNIT, cores=cores, kind="port",
+                sample="%d blends of the same generator (indices %d..%d), %d per process; %.1f s of fit time on the "
+                       "slowest process (pool wall %.1f s incl. source init); %.1f iterations/blend"
+                       % (nb, first_index, first_index + n - 1, per_worker, tmax, wall, its / max(nb, 1)),
+                iters_per_sec=its / tmax, single_core_blends_per_sec=nb / sum(r[2] for r in res))
+
+
+# ------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi -lms 200 during the timed region (profiling recipe's clocks line)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([f.strip() for f in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=["nvidia-smi unavailable"])
+        self.proc.terminate()
+        self.th.join(timeout=2)
+        sm, mx, reasons, pw = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1])); pw.append(float(r[2]))
+            except (ValueError, IndexError):
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    power_w_max=max(pw) if pw else None, samples=len(sm), reasons=sorted(reasons))
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+def alg_bytes(comp_off, n_iter=None):
+    """Algorithmic bytes per launch of each kernel, summed over the blends of one batch.
+    With n_iter: summed over the iterations each blend actually ran (launches differ in active blends)."""
+    K = np.diff(comp_off).astype(np.float64)
+    N = NY * NX
+    w = np.ones_like(K) if n_iter is None else n_iter.astype(np.float64)
+    k1 = 4 * N * (K + 3 * C) + 4 * C * PSF * PSF + 4 * K * C          # S, images, weights in; G out; diff kernel; A
+    k2 = 4 * N * (K + C) + 4 * N * K + 8 * K * C                      # S, G in; stepped S out; A in/out
+    k3 = 8 * N * K + 8 * K * C                                        # stepped S in, S out; A in/out
+    it = 4 * N * (2 * K + 2 * C) + 4 * C * PSF * PSF + 8 * K * C      # fused-iteration figure B_iter
+    return [float((k1 * w).sum()), float((k2 * w).sum()), float((k3 * w).sum())], float((it * w).sum())
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak, peak_src = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks \
+        else (6650.0, "fallback (B200_PROFILING.md)")
+
+    import __graft_entry__
+    if rank == 0:
+        __graft_entry__.build()
+    if world > 1:
+        dist.barrier()
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_baseline()
+
+    # ---- inputs: rank r owns blend indices [r*B, (r+1)*B)
+    B = args.blends
+    t0 = time.perf_counter()
+    data = synth.make_blends(range(rank * B, (rank + 1) * B), C, NY, NX, psf_size=PSF)
+    t_gen = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    bb = BlendBatch(data["images"], data["psfs"], data["model_psf"], data["centers"], data["bg_rms"],
+                    weights=data["weights"])
+    t_init = time.perf_counter() - t0
+    bb.snapshot()
+    comp_off = bb.host["comp_off"]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def allmax(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- device-resident throughput: restore the initial state, run the loop
+    for _ in range(args.warmup):
+        bb.restore()
+        bb.fit_device(MAX_ITER, E_REL, check_every=args.check_every)
+    sampler = ClockSampler(local) if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kms = np.zeros(4)
+    launches = steps_run = 0
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        bb.restore()
+        info = bb.fit_device(MAX_ITER, E_REL, check_every=args.check_every, profile=True)
+        kms += info["kernel_ms"]
+        launches += info["launches"]
+        steps_run += info["steps"]
+    ev1.record()
+    barrier()
+    ms = allmax(ev0.elapsed_time(ev1))
+    clocks = sampler.stop() if sampler else None
+    out = bb.download(morph=False)
+    n_iter = out["n_iter"]
+    blends_total = allsum(float(bb.B))
+    iters_total = allsum(float(n_iter.sum()))
+    value = blends_total * args.steps / (ms / 1e3)
+
+    # ---- end to end through the C ABI with page-locked host buffers: upload + fit + download (+ gather)
+    cudart = torch.cuda.cudart()
+    res = bb._dev.alloc_results(MAX_ITER, morph=True)
+    for a in list(bb.host.values()) + list(res.values()):
+        if isinstance(a, np.ndarray) and a.nbytes >= 4096:
+            cudart.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+    rec = torch.empty((bb.B, 3), dtype=torch.float32, device="cuda")
+
+    def e2e_step():
+        bb.upload()
+        bb.fit_device(MAX_ITER, E_REL, check_every=args.check_every)
+        o = bb.download(morph=True, out=res)
+        if world > 1:       # per-blend result records gathered over NCCL (north_star: NCCL only for results)
+            n = o["n_iter"]
+            rec.copy_(torch.from_numpy(np.stack([n, o["active"], o["logL"][np.arange(bb.B), np.maximum(n - 1, 0)]], 1)
+                                       .astype(np.float32)))
+            allrec = [torch.empty_like(rec) for _ in range(world)]
+            dist.all_gather(allrec, rec)
+        return o
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    barrier()
+    e2e_s = allmax(time.perf_counter() - t0)
+    e2e = dict(value=blends_total * args.steps / e2e_s, unit=UNIT, h2d_bytes_per_step=int(allsum(float(bb.h2d_bytes))),
+               d2h_bytes_per_step=int(allsum(float(bb.d2h_bytes))), ms_per_step=e2e_s * 1e3 / args.steps)
+
+    # ---- roofline of each kernel: fixed-iteration pass (e_rel = 0: every blend active in every launch)
+    bb.restore()
+    bb.fit_device(8, 0.0, check_every=1000)
+    bb.restore()
+    fx = bb.fit_device(args.roofline_iters, 0.0, check_every=1000, profile=True)
+    per_launch, it_bytes = alg_bytes(comp_off)
+    names = ["scl_k_forward_adjoint", "scl_k_grad_step", "scl_k_prox", "scl_k_converge"]
+    kernels = []
+    for j in range(3):
+        t = fx["kernel_ms"][j] / fx["steps"]
+        gbs = per_launch[j] / (t * 1e-3) / 1e9
+        kernels.append(dict(name=names[j], ms_per_launch=t, alg_bytes_per_launch=per_launch[j], gbs=gbs,
+                            frac=gbs / hbm_peak, share=fx["kernel_ms"][j] / sum(fx["kernel_ms"])))
+    top = max(range(3), key=lambda j: fx["kernel_ms"][j])
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(names[top])
+    except (OSError, ValueError):
+        pass
+    roofline = dict(bound="hbm", kernel=names[top], achieved=kernels[top]["gbs"], peak=hbm_peak, unit="GB/s",
+                    frac=kernels[top]["frac"], traffic=traffic, peak_source=peak_src,
+                    how="CUDA events around each launch, %d fixed iterations with every blend active (e_rel=0); "
+                        "algorithmic bytes per launch per DESIGN.md" % fx["steps"],
+                    iteration=dict(ms=fx["device_ms"] / fx["steps"], alg_bytes=it_bytes,
+                                   gbs=it_bytes / (fx["device_ms"] / fx["steps"] * 1e-3) / 1e9,
+                                   frac=it_bytes / (fx["device_ms"] / fx["steps"] * 1e-3) / 1e9 / hbm_peak),
+                    timed_region_share={names[j]: kms[j] / max(kms.sum(), 1e-9) for j in range(4)},
+                    kernels=kernels)
+    if rank == 0:
+        line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                    ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                    dtype="f32", data="synthetic",
+                    config=dict(workload=WORKLOAD, blends_per_gpu=int(bb.B), components_per_gpu=int(bb.K),
+                                max_iter=MAX_ITER, e_rel=E_REL, mean_iters_per_blend=iters_total / blends_total,
+                                l2="inputs per GPU (%.1f GB) exceed the 126 MB L2" % (bb.h2d_bytes / 1e9),
+                                sharding="blend-parallel, rank r owns blends [r*B,(r+1)*B), no data-path collective",
+                                input_gen_s=t_gen, source_init_s=t_init, failed_sources=bb.n_failed),
+                    pgm_iters_per_sec=iters_total * args.steps / (ms / 1e3),
+                    e2e=e2e, gpu_launches=int(launches), roofline=roofline, clocks=clocks)
+        if cpu is not None:
+            line["cpu_baseline"] = cpu
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's algorithm on the host cores: the CPU oracle (the reference itself cannot be imported or built
+    here: autograd, proxmin and Eigen are absent -- DESIGN.md)."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    vals = []
+    cpu = None
+    for i in range(args.warmup + args.steps):
+        r = cpu_baseline(per_worker=args.ref_per_worker, first_index=0)
+        if i >= args.warmup:
+            vals.append(r)
+        cpu = r
+    v = float(np.mean([r["value"] for r in vals]))
+    cpu = dict(cpu, value=v)
+    n = int(os.environ.get("WORLD_SIZE", 1))
+    print(json.dumps(dict(metric=METRIC, value=v, unit=UNIT, impl="reference", n_gpus=n, steps=args.steps,
+                          warmup=args.warmup, ms_per_step=None, higher_is_better=True, scaling="weak", vs_baseline=None,
+                          dtype="f32", data="synthetic", config=dict(workload=WORKLOAD, max_iter=MAX_ITER, e_rel=E_REL),
+                          cpu_baseline=cpu,
+                          e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--blends", type=int, default=10000, help="blends per GPU")
+    ap.add_argument("--check-every", type=int, default=8)
+    ap.add_argument("--roofline-iters", type=int, default=40)
+    ap.add_argument("--ref-per-worker", type=int, default=6)
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if args.steps > 2:
+            args.steps = 2          # each step is a bounded CPU sample; keep the run within minutes
+        args.warmup = min(args.warmup, 1)
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

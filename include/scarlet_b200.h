@@ -108,10 +108,12 @@ int scl_batch_upload(scl_batch* batch, const scl_batch_desc* desc, void* stream)
 /* Blend.fit(max_iter, e_rel, approximate_L) (blend.py:65-102) for every blend of the batch.
  * check_every: how often (iterations) the host polls the device-side active count to stop early.
  * device_ms (optional): device time of the whole loop by CUDA events on `stream`.
- * k1_ms (optional): summed device time of the fused render/convolve/residual/adjoint kernel and
- * k1_launches its launch count (only measured when profile != 0; adds event overhead). */
+ * kernel_ms (optional, float[4]): summed device time of each of the four kernels of an iteration
+ *   [0] render/convolve/residual/adjoint  [1] gradients + Lipschitz + step  [2] constraint chain  [3] convergence
+ * by CUDA events between the launches (only measured when profile != 0); steps_run: iterations launched
+ * (= launches of each kernel); launches: total kernel launches. */
 int scl_batch_fit(scl_batch* batch, int max_iter, double e_rel, int approximate_L, int check_every,
-                  int profile, float* device_ms, float* k1_ms, int* k1_launches, int* launches, void* stream);
+                  int profile, float* device_ms, float* kernel_ms, int* steps_run, int* launches, void* stream);
 /* The constraint pass every source runs once at construction (`self.update()` with it = 0, source.py:400,492):
  * max_pixel, centroid + shift, symmetry, monotonicity, positivity, normalisation on the batch's current state. */
 int scl_batch_constrain(scl_batch* batch, void* stream);
@@ -119,6 +121,10 @@ int scl_batch_constrain(scl_batch* batch, void* stream);
  * by that fit; n_iter[b] of them valid); active[b] == 0 <=> blend b converged. */
 int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* center, double* shift, int32_t* conv,
                        int32_t* n_iter, int32_t* active, double* logL, float* lipschitz, void* stream);
+/* Keep / bring back a device-side copy of the model state (sed, morph, center, shift, flags), so that a fit can be
+ * repeated from the same starting point without another host upload (stream-ordered device-to-device copies). */
+int scl_batch_snapshot(scl_batch* batch, void* stream);
+int scl_batch_restore(scl_batch* batch, void* stream);
 void scl_batch_destroy(scl_batch* batch);
 
 #ifdef __cplusplus

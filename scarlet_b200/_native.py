@@ -315,22 +315,28 @@ class Batch:
         _check(lib().scl_batch_upload(self._h, ctypes.byref(desc), c_void_p(self.stream)))
 
     def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False):
-        """Returns dict(device_ms, k1_ms, k1_launches, launches)."""
-        ms, k1 = c_float(0), c_float(0)
+        """Returns dict(device_ms, kernel_ms[4], steps, launches)."""
+        ms, k1 = c_float(0), (c_float * 4)()
         nk1, nl = c_int(0), c_int(0)
         _check(lib().scl_batch_fit(self._h, int(max_iter), c_double(e_rel), int(bool(approximate_L)), int(check_every),
-                                   int(bool(profile)), ctypes.byref(ms), ctypes.byref(k1), ctypes.byref(nk1),
+                                   int(bool(profile)), ctypes.byref(ms), k1, ctypes.byref(nk1),
                                    ctypes.byref(nl), c_void_p(self.stream)))
         self.max_iter = int(max_iter)
-        return dict(device_ms=ms.value, k1_ms=k1.value, k1_launches=nk1.value, launches=nl.value)
+        return dict(device_ms=ms.value, kernel_ms=[float(v) for v in k1], steps=nk1.value, launches=nl.value)
 
     def constrain(self):
         """One `update()` pass with it = 0 on every component (what sources run at construction)."""
         _check(lib().scl_batch_constrain(self._h, c_void_p(self.stream)))
 
-    def download(self, morph=True):
-        N = self.Ny * self.Nx
-        out = dict(
+    def snapshot(self):
+        _check(lib().scl_batch_snapshot(self._h, c_void_p(self.stream)))
+
+    def restore(self):
+        _check(lib().scl_batch_restore(self._h, c_void_p(self.stream)))
+
+    def alloc_results(self, max_iter, morph=True):
+        """Host arrays `download` fills (allocate once and pass as `out=` to reuse, e.g. page-locked)."""
+        return dict(
             sed=np.empty((self.K, self.C), np.float32),
             morph=np.empty((self.K, self.Ny, self.Nx), np.float32) if morph else None,
             center=np.empty((self.K, 2), np.int32),
@@ -338,9 +344,15 @@ class Batch:
             conv=np.empty(self.K, np.int32),
             n_iter=np.empty(self.B, np.int32),
             active=np.empty(self.B, np.int32),
-            logL=np.empty((self.B, self.max_iter), np.float64) if self.max_iter > 0 else None,
+            logL=np.empty((self.B, max_iter), np.float64) if max_iter > 0 else None,
             lipschitz=np.empty((self.B, 2), np.float32),
         )
+
+    def download(self, morph=True, out=None):
+        if out is None:
+            out = self.alloc_results(self.max_iter, morph)
+        elif out["logL"] is not None and out["logL"].shape != (self.B, self.max_iter):
+            raise ValueError("out['logL'] must be [B, max_iter of the last fit]")
         _check(lib().scl_batch_download(self._h, _p(out["sed"]), _p(out["morph"]), _p(out["center"]), _p(out["shift"]),
                                         _p(out["conv"]), _p(out["n_iter"]), _p(out["active"]), _p(out["logL"]),
                                         _p(out["lipschitz"]), c_void_p(self.stream)))

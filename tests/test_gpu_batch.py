@@ -1,0 +1,120 @@
+"""GPU parity of BlendBatch (array-level batch entry, config 3) against the oracle, plus size-independent
+properties at a larger batch."""
+import numpy as np
+import pytest
+from numpy.testing import assert_array_equal, assert_allclose
+
+import helpers
+
+pytestmark = pytest.mark.gpu
+REL = 1e-5
+
+
+@pytest.fixture(scope="module")
+def batch6():
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    d = synth.make_blends(range(6), device="cpu")
+    bb = BlendBatch(d["images"], d["psfs"], d["model_psf"], d["centers"], d["bg_rms"], weights=d["weights"])
+    yield d, bb
+    bb.close()
+
+
+def test_init_matches_oracle_sources(batch6):
+    """Source initialisation + the construction-time constraint pass equal the oracle's ExtendedSource objects."""
+    d, bb = batch6
+    off = bb.host["comp_off"]
+    for i in range(6):
+        _, obs, srcs, _ = helpers.synthetic_blend(i)
+        assert_array_equal(obs.images, d["images"][i])
+        assert off[i + 1] - off[i] == len(srcs)
+        for j, s in enumerate(srcs):
+            k = off[i] + j
+            assert_array_equal(bb.host["center"][k], s.pixel_center)
+            assert_allclose(bb.host["shift"][k], s.shift, rtol=0, atol=5e-6)
+            assert_allclose(bb.host["sed"][k], s.sed, rtol=2e-6)
+            assert_allclose(bb.host["morph"][k], s.morph, rtol=0, atol=REL)
+
+
+def test_fit_matches_oracle(batch6):
+    """Free-running fit(30, e_rel=0) of the batch vs the oracle blend by blend."""
+    d, bb = batch6
+    bb.snapshot()
+    bb.fit_device(30, 0.0)
+    out = bb.download()
+    off = bb.host["comp_off"]
+    for i in range(6):
+        bl = helpers.synthetic_blend(i)[3]
+        bl.fit(30, 0.0)
+        assert out["n_iter"][i] == 30
+        assert_allclose(out["logL"][i], np.array(bl.mse, dtype=np.float64), rtol=20 * REL)
+        assert_array_equal(out["center"][off[i]:off[i + 1]], [s.pixel_center for s in bl.sources])
+        ref = bl.get_model().astype(np.float64)
+        got = np.einsum("kc,kyx->cyx", out["sed"][off[i]:off[i + 1]].astype(np.float64),
+                        out["morph"][off[i]:off[i + 1]].astype(np.float64))
+        assert_allclose(got, ref, rtol=0, atol=1e-3 * np.abs(ref).max())
+    # restore brings the initial state back bit for bit; the repeated fit is bit-identical
+    bb.restore()
+    again0 = bb.download()
+    assert_array_equal(again0["morph"], bb.host["morph"])
+    assert_array_equal(again0["sed"], bb.host["sed"])
+    bb.fit_device(30, 0.0)
+    again = bb.download()
+    assert_array_equal(again["logL"], out["logL"])
+    assert_array_equal(again["morph"], out["morph"])
+    bb.restore()
+
+
+def test_fit_host_roundtrip_and_converged_stop(batch6):
+    """BlendBatch.fit (upload + loop + download) with the reference defaults: every blend stops on its own
+    iteration, the loss history is non-increasing at the end and the state after a converged stop is frozen."""
+    d, bb = batch6
+    info = bb.fit(200, 1e-2)
+    assert info["launches"] > 0
+    out = bb.last
+    assert (out["active"] == 0).all() and (out["conv"] == 0).all()
+    for i in range(bb.B):
+        bl = helpers.synthetic_blend(i)[3]
+        bl.fit(200, 1e-2)
+        assert abs(len(bb.mse[i]) - bl.it) <= 1          # a 1-ulp difference may move the stopping iteration by one
+        n = min(len(bb.mse[i]), bl.it)
+        assert_allclose(bb.mse[i][:n], np.array(bl.mse[:n], dtype=np.float64), rtol=20 * REL)
+
+
+def test_properties_large_batch():
+    """512 blends (BASELINE shape): per-blend results do not depend on the batch they run in; morphologies obey the
+    constraints (non-negative, peak-normalised, monotonic from the peak outwards)."""
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    d = synth.make_blends(range(100, 612), device="cpu")
+    bb = BlendBatch(d["images"], d["psfs"], d["model_psf"], d["centers"], d["bg_rms"], weights=d["weights"])
+    bb.fit_device(200, 1e-2)
+    out = bb.download()
+    off = bb.host["comp_off"]
+    assert (out["active"] == 0).mean() > 0.9
+    assert (out["morph"] >= 0).all()
+    assert_allclose(out["morph"].reshape(bb.K, -1).max(axis=1), 1.0, rtol=1e-6)
+    peak = out["morph"].reshape(bb.K, -1).argmax(axis=1)
+    # the peak sits within the 5x5 window of the tracked centre
+    cy, cx = out["center"][:, 0], out["center"][:, 1]
+    assert (np.abs(peak // 64 - cy) <= 2).all() and (np.abs(peak % 64 - cx) <= 2).all()
+    # loss never increases over the last iterations of any blend
+    for b in range(0, bb.B, 37):
+        n = out["n_iter"][b]
+        l = out["logL"][b, :n]
+        assert l[-1] <= l[0]
+    # sub-batch independence: blends 40..47 alone give bit-identical results
+    sel = list(range(140, 148))
+    d2 = synth.make_blends(sel, device="cpu")
+    b2 = BlendBatch(d2["images"], d2["psfs"], d2["model_psf"], d2["centers"], d2["bg_rms"], weights=d2["weights"])
+    b2.fit_device(200, 1e-2)
+    o2 = b2.download()
+    kept = list(bb.kept)
+    assert b2.B == len(sel)
+    for j, g in enumerate(sel):
+        i = kept.index(g - 100)
+        assert out["n_iter"][i] == o2["n_iter"][j]
+        assert_array_equal(out["logL"][i, :out["n_iter"][i]], o2["logL"][j, :o2["n_iter"][j]])
+        assert_array_equal(out["morph"][off[i]:off[i + 1]], o2["morph"][b2.host["comp_off"][j]:b2.host["comp_off"][j + 1]])
+    bb.close()
+    b2.close()
