@@ -42,8 +42,9 @@ int scl_device_count(void);
  * Monotonicity weights depend only on the pixel's offset from the peak (plus the image
  * border).  The host builds them once per image shape with the reference's formula
  * (operator.py:540-621) and registers them here:
- *   wtab  float32 [(2Ny-1)*(2Nx-1)*8]  normalised weights of an interior pixel
- *   ctab  float64 [(2Ny-1)*(2Nx-1)*8]  un-normalised cosines, 0 where the tap is not strictly closer
+ *   wtab  float32 [9][(2Ny-1)*(2Nx-1)*8]  normalised weights per border type bt = by*3+bx (0 = interior pixel,
+ *                                          by/bx: 1 = first row/column, 2 = last): taps leaving the image dropped
+ *   ctab  float64 [(2Ny-1)*(2Nx-1)*8]     un-normalised cosines, 0 where the tap is not strictly closer
  * indexed by ((Y+Ny-1)*(2Nx-1) + (X+Nx-1))*8 + tap, (Y,X) = pixel - peak. */
 int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab);
 

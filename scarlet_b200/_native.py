@@ -121,8 +121,9 @@ def monotonic_tables_host(Ny, Nx):
     Same arithmetic as getRadialMonotonicWeights (operator.py:540-621) evaluated for
     every offset (Y, X) = pixel - peak instead of for one peak position:
       ctab[Y, X, i]  cos(theta_p - phi_i) if neighbour i is strictly closer to the peak, else 0
-      wtab[Y, X, i]  ctab normalised over the 8 taps, rounded to float32 (interior pixels)
-    The device renormalises ctab for pixels on the image border.
+      wt9[bt, Y, X, i]  ctab normalised over the taps that stay inside the image for a pixel of border type bt
+                        (0 = interior), rounded to float32 -- what the f32 overload multiplies with
+    ctab is kept for the float64 / nearest variants, which renormalise on the device.
     """
     key = (int(Ny), int(Nx))
     if key in _tables:
@@ -147,14 +148,22 @@ def monotonic_tables_host(Ny, Nx):
         closer = (Y + oy) ** 2 + (X + ox) ** 2 < Y ** 2 + X ** 2
         w[~closer] = 0
         ctab[..., i] = w
-    norm = np.zeros(Y.shape)
-    for i in range(8):                      # sequential tap-order sum, like np.sum(axis=0) on (8, N)
-        norm = norm + ctab[..., i]
-    norm[norm == 0] = 1
-    wtab = (ctab / norm[..., None]).astype(np.float32)
+    # border types: bt = by*3 + bx, by/bx = 0 interior, 1 first row/column, 2 last row/column; taps that leave the
+    # image are dropped before the normalisation (operator.py:505-520,614-617)
+    wt9 = np.zeros((9,) + Y.shape + (8,), dtype=np.float32)
+    for by in range(3):
+        for bx in range(3):
+            keep = np.array([not ((by == 1 and oy == -1) or (by == 2 and oy == 1) or
+                                  (bx == 1 and ox == -1) or (bx == 2 and ox == 1)) for oy, ox in _COORDS])
+            c = ctab * keep
+            norm = np.zeros(Y.shape)
+            for i in range(8):                      # sequential tap-order sum, like np.sum(axis=0) on (8, N)
+                norm = norm + c[..., i]
+            norm[norm == 0] = 1
+            wt9[by * 3 + bx] = (c / norm[..., None]).astype(np.float32)
     ctab = np.ascontiguousarray(ctab)
-    wtab = np.ascontiguousarray(wtab)
-    _tables[key] = (wtab, ctab)
+    wt9 = np.ascontiguousarray(wt9)
+    _tables[key] = (wt9, ctab)
     return _tables[key]
 
 

@@ -142,7 +142,7 @@ static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T 
     CK(dc.alloc(2 * (size_t)n));
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
-    scl_k_monotonic<T, NEAREST><<<n, SCL_THREADS, N * sizeof(T), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
+    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
     CK(cudaGetLastError());
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));
@@ -167,9 +167,9 @@ int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ct
     if (!wtab || !ctab) return fail(SCL_E_ARG, "null table%s%s");
     size_t n = (size_t)(2 * Ny - 1) * (2 * Nx - 1) * 8;
     Tables t;
-    CK(cudaMalloc(&t.wtab, n * sizeof(float)));
+    CK(cudaMalloc(&t.wtab, 9 * n * sizeof(float)));
     CK(cudaMalloc(&t.ctab, n * sizeof(double)));
-    CK(cudaMemcpy(t.wtab, wtab, n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(t.wtab, wtab, 9 * n * sizeof(float), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(t.ctab, ctab, n * sizeof(double), cudaMemcpyHostToDevice));
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_tables.find({Ny, Nx});

@@ -4,9 +4,11 @@
 #include <stdint.h>
 
 #define SCL_MAX_BANDS 8          // C <= 8 spectral channels per frame
+#define SCL_MAX_COMP 8           // K <= 8 components per blend (register accumulators, 8x8 Gram)
 #define SCL_FFT 128              // smem FFT edge (power of two); Ny+ky/2 <= 128, Nx+kx/2 <= 128
 #define SCL_RS 65                // complex row stride of the smem spectrum tile (odd: conflict-free columns)
 #define SCL_THREADS 256
+#define SCL_PROX_THREADS 128     // constraint kernel: one CTA of 4 warps per component
 
 // component flags (host mirror: scarlet_b200/_native.py)
 #define SCL_F_SYMMETRIC 1u       // run the symmetry prox (source.py:427-432)

@@ -146,6 +146,8 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const int* __restrict__ active,     // [B]
                       float* __restrict__ G,              // [B, C, N]
                       double* __restrict__ loss_part,     // [B, C]
+                      float* __restrict__ dA,             // [Ktot, C]  sum_p G[c,p] S[k,p]   (K <= 8)
+                      double* __restrict__ gram,          // [B, 8, 8]  rows r = c, c+C, .. of S S^T
                       int C, int Ny, int Nx)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -153,6 +155,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     float2* tw = buf + F * RS;
     double* red = reinterpret_cast<double*>(tw + 128);
     __shared__ float sA[64];
+    __shared__ double sred[SCL_THREADS / 32][2 * SCL_MAX_COMP];
 
     const int c = blockIdx.x, b = blockIdx.y;
     if (!active[b]) return;
@@ -173,6 +176,9 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     __syncthreads();
 
     double loss = 0.0;
+    float accA[SCL_MAX_COMP];            // this thread's share of dA[k, c]
+#pragma unroll
+    for (int k = 0; k < SCL_MAX_COMP; k++) accA[k] = 0.f;
 
     if (kid < 0) {
         // identical PSFs: R = M, G = W^2 (M - I)   (observation.py:216-220)
@@ -182,7 +188,11 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
             float w = wgt ? wgt[p] : 1.f;
             float d = w * (m - img[p]);
             loss += (double)d * (double)d;
-            gout[p] = w * d;
+            const float g = w * d;
+            gout[p] = g;
+#pragma unroll
+            for (int k = 0; k < SCL_MAX_COMP; k++)
+                if (k < K) accA[k] += g * S[(size_t)(k0 + k) * N + p];
         }
     } else {
         // ---- phase A: render rows, row FFT, untangle
@@ -256,14 +266,62 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                 int y0 = 2 * j, y1 = 2 * j + 1;
                 for (int x = t; x < Nx; x += 16) {
                     float2 z = line[x];
-                    gout[y0 * Nx + x] = z.y * inv;
-                    if (y1 < Ny) gout[y1 * Nx + x] = z.x * inv;
+                    const float g0 = z.y * inv, g1 = (y1 < Ny) ? z.x * inv : 0.f;
+                    const int p0 = y0 * Nx + x, p1 = (y1 < Ny) ? y1 * Nx + x : p0;
+                    gout[p0] = g0;
+                    if (y1 < Ny) gout[p1] = g1;
+#pragma unroll
+                    for (int k = 0; k < SCL_MAX_COMP; k++)
+                        if (k < K) {
+                            const float* Sk = S + (size_t)(k0 + k) * N;
+                            accA[k] += g0 * Sk[p0] + g1 * Sk[p1];
+                        }
                 }
             }
         }
     }
     double tot = block_sum<double>(loss, red);
     if (threadIdx.x == 0) loss_part[b * C + c] = 0.5 * tot;
+
+    // ---- SED gradient of this band: dA[k, c]
+    {
+#pragma unroll
+        for (int k = 0; k < SCL_MAX_COMP; k++) {
+            double v = warp_sum<double>((double)accA[k]);
+            if (lane == 0) sred[warp][k] = v;
+        }
+        __syncthreads();
+        if (threadIdx.x < K) {
+            double v = 0.0;
+            for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
+            dA[(size_t)(k0 + threadIdx.x) * C + c] = (float)v;
+        }
+    }
+    // ---- rows r = c, c + C, ... of the Gram matrix S S^T (Blend._set_lipschitz, blend.py:205-217)
+    for (int r = c; r < K; r += C) {
+        float acc[SCL_MAX_COMP];
+#pragma unroll
+        for (int l = 0; l < SCL_MAX_COMP; l++) acc[l] = 0.f;
+        const float* Sr = S + (size_t)(k0 + r) * N;
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            const float sr = Sr[p];
+#pragma unroll
+            for (int l = 0; l < SCL_MAX_COMP; l++)
+                if (l < K) acc[l] += sr * S[(size_t)(k0 + l) * N + p];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int l = 0; l < SCL_MAX_COMP; l++) {
+            double v = warp_sum<double>((double)acc[l]);
+            if (lane == 0) sred[warp][l] = v;
+        }
+        __syncthreads();
+        if (threadIdx.x < K) {
+            double v = 0.0;
+            for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
+            gram[(size_t)b * 64 + r * 8 + threadIdx.x] = v;
+        }
+    }
 }
 
 // Standalone render: observation.render(model) for host callers (drop-in

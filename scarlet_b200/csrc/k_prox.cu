@@ -11,8 +11,9 @@
 #include "prox_dev.cuh"
 
 struct SclProxArgs {
-    const float* A_step;      // [Ktot, C]  SEDs after the gradient step
-    const float* S_step;      // [Ktot, N]  morphologies after the gradient step
+    const float* A_step;      // [Ktot, C]  SEDs after the gradient step (K2)
+    const float* G;           // [B, C, N]  d loss / d model (K1); nullptr: no morphology step (construction pass)
+    const float* lips;        // [B, 2]     (L_sed, L_morph) (K2)
     float* A;                 // [Ktot, C]  in: previous iterate; out: new iterate
     float* S;                 // [Ktot, N]  in: previous iterate; out: new iterate
     const int* comp_blend;    // [Ktot]
@@ -34,7 +35,8 @@ struct SclProxArgs {
 };
 
 // dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
-extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+// block: SCL_PROX_THREADS
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
 scl_k_prox(SclProxArgs a)
 {
     extern __shared__ __align__(16) float smem_f[];
@@ -52,8 +54,26 @@ scl_k_prox(SclProxArgs a)
     const unsigned fl = a.cflags[k];
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
-    const float* Sin = a.S_step + (size_t)k * N;
-    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
+    // morphology gradient step (blend.py:94-96): S[k] -= (1/L_morph) sum_c A[k,c] G[c]
+    {
+        const float* Sin = a.S + (size_t)k * N;
+        if (a.G && !(fl & SCL_F_FIX_MORPH)) {
+            const float step_morph = 1.0f / a.lips[2 * b + 1];
+            const float* Gb = a.G + (size_t)b * C * N;
+            float ak[SCL_MAX_BANDS];
+#pragma unroll
+            for (int c = 0; c < SCL_MAX_BANDS; c++) ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f;
+            for (int p = threadIdx.x; p < N; p += blockDim.x) {
+                float d = 0.f;
+#pragma unroll
+                for (int c = 0; c < SCL_MAX_BANDS; c++)
+                    if (c < C) d += ak[c] * Gb[(size_t)c * N + p];
+                X[p] = Sin[p] - step_morph * d;
+            }
+        } else {
+            for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
+        }
+    }
     if (threadIdx.x == 0) {
         sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
         ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
@@ -78,7 +98,10 @@ scl_k_prox(SclProxArgs a)
                 scl_flip_symmetry(X, Nx, w, 0, 1.0f);
             }
         }
-        if (fl & SCL_F_MONOTONIC) scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+        if (fl & SCL_F_MONOTONIC) {
+            if (Ny >= 2 && Nx >= 2) scl_monotonic_f32<SCL_PROX_THREADS>(X, Ny, Nx, sc[0], sc[1], a.wtab, 0.f);
+            else scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+        }
         // positive (update.py:27-32) + morph_max (update.py:62-65)
         float mx = -INFINITY;
         for (int p = threadIdx.x; p < N; p += blockDim.x) {
@@ -173,7 +196,11 @@ scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, i
     T* g = imgs + (size_t)blockIdx.x * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
-    scl_monotonic<T, NEAREST>(X, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
+    if (sizeof(T) == 4 && !NEAREST && Ny >= 2 && Nx >= 2 && blockDim.x == SCL_PROX_THREADS)
+        scl_monotonic_f32<SCL_PROX_THREADS>(reinterpret_cast<float*>(X), Ny, Nx, centers[2 * blockIdx.x],
+                                            centers[2 * blockIdx.x + 1], wtab, (float)thresh);
+    else
+        scl_monotonic<T, NEAREST>(X, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
     for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
 }
 template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*);

@@ -301,6 +301,86 @@ __device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int 
     X[p] = (r < cur) ? r : cur;
 }
 
+// ---- fast f32 wavefront (the in-loop path) ---------------------------------
+// wt9: f32 [9][(2Ny-1)(2Nx-1)][8] normalised weights per border type
+//   bt = by*3 + bx, by = 0 interior / 1 first row / 2 last row (bx likewise), built on the host in f64 with the
+//   reference's formula and rounded to f32 (operators_pybind11.cc:82-83) -- no arithmetic on weights here.
+// NT threads (tid = 0..NT-1, all of them must call) sweep the levels; `sync` separates levels.
+struct SclMonoLoc { int p; int ti; bool ok; };
+
+__device__ __forceinline__ SclMonoLoc scl_mono_locate(int v, int a, int amax, int oct, int Ny, int Nx, int cy, int cx) {
+    SclMonoLoc r;
+    r.ok = false; r.p = 0; r.ti = 0;
+    if (a > amax) return r;
+    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
+    const int bb = v - 2 * a;
+    if ((bb == 0 && sb) || (a == bb && sw)) return r;      // duplicate images of the same pixel
+    const int pa = sa ? -a : a, pb = sb ? -bb : bb;
+    const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
+    const int y = cy + Yo, x = cx + Xo;
+    if (y < 0 || y >= Ny || x < 0 || x >= Nx) return r;
+    const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
+    const int W2 = 2 * Nx - 1;
+    r.ti = (((by * 3 + bx) * (2 * Ny - 1) + (Yo + Ny - 1)) * W2 + (Xo + Nx - 1)) * 8;
+    r.p = y * Nx + x;
+    r.ok = true;
+    return r;
+}
+
+__device__ __forceinline__ void scl_mono_apply(float* X, int Nx, int p, const float4& w0, const float4& w1, float omt) {
+    float ref = 0.f;
+    if (w0.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx - 1], w0.x));
+    if (w0.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx], w0.y));
+    if (w0.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx + 1], w0.z));
+    if (w0.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - 1], w0.w));
+    if (w1.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + 1], w1.x));
+    if (w1.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx - 1], w1.y));
+    if (w1.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx], w1.z));
+    if (w1.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx + 1], w1.w));
+    const float r = __fmul_rn(ref, omt), cur = X[p];
+    X[p] = (r < cur) ? r : cur;
+}
+
+template <int NT>
+__device__ __forceinline__ void scl_mono_sync() {
+    if (NT == 32) __syncwarp();
+    else __syncthreads();
+}
+
+// Requires Ny, Nx >= 2 and blockDim.x == NT.
+template <int NT>
+__device__ void scl_monotonic_f32(float* X, int Ny, int Nx, int cy, int cx, const float* __restrict__ wt9, float thresh) {
+    const float omt = 1.f - thresh;
+    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
+    const int vmax = 2 * max(ay, ax) + min(ay, ax);
+    const int tid = threadIdx.x, slot = tid >> 3, oct = tid & 7;
+    constexpr int NSLOT = NT / 8;
+    scl_mono_sync<NT>();
+    // weights of the first pass of level v are fetched while level v-1 is being processed
+    SclMonoLoc nx = scl_mono_locate(1, 1 + slot, 0, oct, Ny, Nx, cy, cx);
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0;
+    if (nx.ok) { n0 = *reinterpret_cast<const float4*>(wt9 + nx.ti); n1 = *reinterpret_cast<const float4*>(wt9 + nx.ti + 4); }
+    for (int v = 1; v <= vmax; v++) {
+        const SclMonoLoc cur = nx;
+        const float4 c0 = n0, c1 = n1;
+        const int amin = (v + 2) / 3, amax = v / 2;
+        if (v < vmax) {
+            nx = scl_mono_locate(v + 1, (v + 3) / 3 + slot, (v + 1) / 2, oct, Ny, Nx, cy, cx);
+            if (nx.ok) { n0 = *reinterpret_cast<const float4*>(wt9 + nx.ti); n1 = *reinterpret_cast<const float4*>(wt9 + nx.ti + 4); }
+        }
+        if (cur.ok) scl_mono_apply(X, Nx, cur.p, c0, c1, omt);
+        for (int a = amin + slot + NSLOT; a <= amax; a += NSLOT) {
+            const SclMonoLoc e = scl_mono_locate(v, a, amax, oct, Ny, Nx, cy, cx);
+            if (e.ok) {
+                const float4 e0 = *reinterpret_cast<const float4*>(wt9 + e.ti);
+                const float4 e1 = *reinterpret_cast<const float4*>(wt9 + e.ti + 4);
+                scl_mono_apply(X, Nx, e.p, e0, e1, omt);
+            }
+        }
+        scl_mono_sync<NT>();
+    }
+}
+
 template <typename T, bool NEAREST>
 __device__ void scl_monotonic(T* X, int Ny, int Nx, int cy, int cx,
                               const float* __restrict__ wtab, const double* __restrict__ ctab, T thresh) {

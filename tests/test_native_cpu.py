@@ -34,27 +34,26 @@ def test_no_device_is_loud():
 
 @pytest.mark.parametrize("shape,center", [((9, 7), (2, 5)), ((16, 13), (3, 3)), ((12, 12), (0, 11)), ((5, 5), (2, 2))])
 def test_offset_tables_reproduce_reference_weights(shape, center):
-    """wtab/ctab (offset-indexed) reproduce getRadialMonotonicWeights bit for bit when evaluated the way the
-    kernel does (interior: wtab; border: ctab renormalised in tap order)."""
+    """wt9/ctab (offset-indexed) reproduce getRadialMonotonicWeights bit for bit when evaluated the way the
+    kernels do (f32 path: wt9[border type]; f64 path: ctab renormalised in tap order)."""
     from scarlet_b200 import _native
-    wtab, ctab = _native.monotonic_tables_host(*shape)
+    wt9, ctab = _native.monotonic_tables_host(*shape)
     H, W = shape
     ref = ref_prox.monotonic_weights(shape, center)
     for y in range(H):
         for x in range(W):
             Y, X = y - center[0] + H - 1, x - center[1] + W - 1
-            if 0 < y < H - 1 and 0 < x < W - 1:
-                w = wtab[Y, X]
-            else:
-                c = ctab[Y, X].copy()
-                for i, (oy, ox) in enumerate(ref_prox.COORDS):
-                    if not (0 <= y + oy < H and 0 <= x + ox < W):
-                        c[i] = 0
-                s = 0.0
-                for i in range(8):
-                    s = s + c[i]
-                w = (c / (s if s != 0 else 1)).astype(np.float32)
-            assert_array_equal(w, ref[:, y * W + x].astype(np.float32))
+            by = 1 if y == 0 else (2 if y == H - 1 else 0)
+            bx = 1 if x == 0 else (2 if x == W - 1 else 0)
+            assert_array_equal(wt9[by * 3 + bx, Y, X], ref[:, y * W + x].astype(np.float32))
+            c = ctab[Y, X].copy()
+            for i, (oy, ox) in enumerate(ref_prox.COORDS):
+                if not (0 <= y + oy < H and 0 <= x + ox < W):
+                    c[i] = 0
+            s = 0.0
+            for i in range(8):
+                s = s + c[i]
+            assert_array_equal(c / (s if s != 0 else 1), ref[:, y * W + x])
 
 
 def test_wavefront_levels_are_a_topological_order():
