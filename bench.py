@@ -135,9 +135,9 @@ def alg_bytes(comp_off, n_iter=None):
     K = np.diff(comp_off).astype(np.float64)
     N = NY * NX
     w = np.ones_like(K) if n_iter is None else n_iter.astype(np.float64)
-    k1 = 4 * N * (K + 3 * C) + 4 * C * PSF * PSF + 4 * K * C          # S, images, weights in; G out; diff kernel; A
-    k2 = 4 * N * (K + C) + 4 * N * K + 8 * K * C                      # S, G in; stepped S out; A in/out
-    k3 = 8 * N * K + 8 * K * C                                        # stepped S in, S out; A in/out
+    k1 = 4 * N * (K + 3 * C) + 4 * C * PSF * PSF + 8 * K * C          # S, images, weights in; G out; diff kernel; A, dA
+    k2 = 12 * K * C + 8 * K * K + 8 * C + 16                          # A, dA in; A out; Gram, loss parts in; logL, L out
+    k3 = 4 * N * (2 * K + C) + 8 * K * C                              # S in/out, G in; A in/out
     it = 4 * N * (2 * K + 2 * C) + 4 * C * PSF * PSF + 8 * K * C      # fused-iteration figure B_iter
     return [float((k1 * w).sum()), float((k2 * w).sum()), float((k3 * w).sum())], float((it * w).sum())
 
@@ -264,7 +264,7 @@ def run_b200(args):
     bb.restore()
     fx = bb.fit_device(args.roofline_iters, 0.0, check_every=1000, profile=True)
     per_launch, it_bytes = alg_bytes(comp_off)
-    names = ["scl_k_forward_adjoint", "scl_k_grad_step", "scl_k_prox", "scl_k_converge"]
+    names = ["scl_k_forward_adjoint", "scl_k_lipschitz", "scl_k_prox", "scl_k_converge"]
     kernels = []
     for j in range(3):
         t = fx["kernel_ms"][j] / fx["steps"]

@@ -134,7 +134,7 @@ __device__ __forceinline__ void column_phase(float2* buf, const float2* tw, cons
 
 }  // namespace
 
-// grid: (C, n_blends); block: SCL_THREADS; dynamic smem: (128*65 + 128) float2 + 32 doubles
+// grid: (C * n_listed_blends); block: SCL_THREADS; dynamic smem: (128*65 + 128) float2 + 32 doubles
 extern "C" __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const float* __restrict__ S,        // [Ktot, N]
@@ -144,6 +144,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const float2* __restrict__ Dhat,    // [n_ker, 128, 65]
                       const int* __restrict__ ker_idx,    // [B*C], -1 = identity (no PSF matching)
                       const int* __restrict__ active,     // [B]
+                      const int* __restrict__ blend_list, // [gridDim.x / C] blends to process (compacted active list)
                       float* __restrict__ G,              // [B, C, N]
                       double* __restrict__ loss_part,     // [B, C]
                       float* __restrict__ dA,             // [Ktot, C]  sum_p G[c,p] S[k,p]   (K <= 8)
@@ -157,7 +158,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     __shared__ float sA[64];
     __shared__ double sred[SCL_THREADS / 32][2 * SCL_MAX_COMP];
 
-    const int c = blockIdx.x, b = blockIdx.y;
+    const int c = blockIdx.x % C, b = blend_list[blockIdx.x / C];
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const int N = Ny * Nx;

@@ -90,15 +90,17 @@ scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
                 const double* __restrict__ gram,      // [B, 8, 8]  S S^T (K1), rows/cols >= K unspecified
                 const double* __restrict__ loss_part, // [B, C]
                 const int* __restrict__ active,       // [B]
+                const int* __restrict__ blend_list,   // [nB] compacted active list
                 const int* __restrict__ it0,          // [B] iterations done before this fit call
                 const double* __restrict__ prev_loss, // [B] last loss of an earlier fit call (if it0 > 0)
                 double* __restrict__ logL,            // [B, logL_cap] loss of step s of THIS fit call
                 float* __restrict__ lips,             // [B, 2] (L_sed, L_morph)
-                int B, int C, int step, int logL_cap, int n_obs, int approximate_L)
+                int nB, int C, int step, int logL_cap, int n_obs, int approximate_L)
 {
     const int gt = blockIdx.x * blockDim.x + threadIdx.x;
-    const int b = gt >> 1, which = gt & 1;
-    const bool live = b < B && active[b];
+    const int which = gt & 1;
+    const int b = (gt >> 1) < nB ? blend_list[gt >> 1] : -1;
+    const bool live = b >= 0 && active[b];
     const int k0 = live ? comp_off[b] : 0, K = live ? comp_off[b + 1] - k0 : 0;
     const int n = which ? C : K;
 

@@ -16,6 +16,7 @@ struct SclProxArgs {
     const float* lips;        // [B, 2]     (L_sed, L_morph) (K2)
     float* A;                 // [Ktot, C]  in: previous iterate; out: new iterate
     float* S;                 // [Ktot, N]  in: previous iterate; out: new iterate
+    const int* comp_list;     // [gridDim.x] components to process (compacted active list)
     const int* comp_blend;    // [Ktot]
     const unsigned* cflags;   // [Ktot]
     int* center;              // [Ktot, 2]  (y, x) pixel_center, updated
@@ -40,7 +41,7 @@ extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
 scl_k_prox(SclProxArgs a)
 {
     extern __shared__ __align__(16) float smem_f[];
-    const int k = blockIdx.x;
+    const int k = a.comp_list[blockIdx.x];
     const int b = a.comp_blend[k];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
@@ -164,22 +165,59 @@ scl_k_prox(SclProxArgs a)
     }
 }
 
-// K4: one thread per blend.  blend.py:157-176: never converged before it > 1.
+// K4: one thread per listed blend.  blend.py:157-176: never converged before it > 1.
 extern "C" __global__ void scl_k_converge(const int* __restrict__ comp_off, const int* __restrict__ conv,
                                           const int* __restrict__ it0, int* __restrict__ active,
-                                          int* __restrict__ n_iter, int* __restrict__ n_active,
-                                          int B, int step)
+                                          int* __restrict__ n_iter, const int* __restrict__ blend_list,
+                                          int nB, int step)
 {
-    int b = blockIdx.x * blockDim.x + threadIdx.x;
-    if (b >= B || !active[b]) return;
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nB) return;
+    const int b = blend_list[i];
+    if (!active[b]) return;
     n_iter[b] = step + 1;
     int it = it0[b] + step + 1;
     bool done = it > 1;
     for (int k = comp_off[b]; k < comp_off[b + 1]; k++) done = done && (conv[k] == 0);
-    if (done) {
-        active[b] = 0;
-        atomicSub(n_active, 1);
+    if (done) active[b] = 0;
+}
+
+// K5: ordered compaction of the active blends and of their components (one CTA of 1024 threads).
+// counts[0] = active blends, counts[1] = their components.  Lists keep ascending index order, so the
+// work a launch does never depends on scheduling.
+extern "C" __global__ void __launch_bounds__(1024)
+scl_k_compact(const int* __restrict__ active, const int* __restrict__ comp_off, int B,
+              int* __restrict__ blend_list, int* __restrict__ comp_list, int* __restrict__ counts)
+{
+    __shared__ int wsum[2][32];
+    __shared__ int base[2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) { base[0] = 0; base[1] = 0; }
+    __syncthreads();
+    for (int start = 0; start < B; start += blockDim.x) {
+        const int b = start + threadIdx.x;
+        const int flag = (b < B && active[b]) ? 1 : 0;
+        const int k0 = flag ? comp_off[b] : 0, nk = flag ? comp_off[b + 1] - k0 : 0;
+        int xb = flag, xk = nk;                          // inclusive warp scans
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int yb = __shfl_up_sync(0xffffffffu, xb, o), yk = __shfl_up_sync(0xffffffffu, xk, o);
+            if (lane >= o) { xb += yb; xk += yk; }
+        }
+        if (lane == 31) { wsum[0][warp] = xb; wsum[1][warp] = xk; }
+        __syncthreads();
+        int ob = base[0], ok = base[1];
+        for (int w = 0; w < warp; w++) { ob += wsum[0][w]; ok += wsum[1][w]; }
+        if (flag) {
+            blend_list[ob + xb - 1] = b;
+            int dst = ok + xk - nk;
+            for (int j = 0; j < nk; j++) comp_list[dst + j] = k0 + j;
+        }
+        __syncthreads();
+        if (threadIdx.x == blockDim.x - 1) { base[0] = ob + xb; base[1] = ok + xk; }
+        __syncthreads();
     }
+    if (threadIdx.x == 0) { counts[0] = base[0]; counts[1] = base[1]; }
 }
 
 // ---------------------------------------------------------------- standalone operators
