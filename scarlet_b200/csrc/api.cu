@@ -33,7 +33,7 @@ int fail(int code, const char* fmt, const char* a = "", const char* b = "") {
         if (e_ != cudaSuccess) return fail(SCL_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
     } while (0)
 
-constexpr size_t kFwdSmem = (size_t)(SCL_FFT * SCL_RS + 128) * sizeof(float2) + 32 * sizeof(double);
+constexpr size_t kFwdSmem = (size_t)(SCL_FFT * SCL_RS + 256 + 2 * SCL_RS) * sizeof(float2) + 32 * sizeof(double);
 
 int next_fast_len(int target) {     // smallest 2^a 3^b 5^c >= target (scipy.fftpack.next_fast_len, fft.py:99)
     if (target <= 6) return target;

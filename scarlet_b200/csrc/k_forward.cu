@@ -19,7 +19,7 @@
 // the DC and Nyquist columns packed as re/im of column 0; column FFTs follow.
 // Every step is owned by a half-warp per line, so the kernel needs only four
 // block barriers.
-#include "fft_smem.cuh"
+#include "fft_reg.cuh"
 
 namespace {
 
@@ -134,14 +134,149 @@ __device__ __forceinline__ void column_phase(float2* buf, const float2* tw, cons
 
 }  // namespace
 
-// grid: (C * n_listed_blends); block: SCL_THREADS; dynamic smem: (128*65 + 128) float2 + 32 doubles
-extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+// ---------------------------------------------------------------------------------------------
+// Register-FFT version of the fused kernel (fft_reg.cuh): 8 lanes per 128-point line, one exchange per
+// transform, conflict-free shared-memory access.
+namespace {
+
+// Row line (pair of image rows) and spectrum column owned by this thread's 8-lane group.  The two groups of
+// a half-warp get lines 4 apart (4 * LS = 8 mod 16 float2) and columns 8 apart: conflict-free 64-bit accesses.
+__device__ __forceinline__ int grp_row_line() {
+    const int g = threadIdx.x >> 3, w = g >> 2, a = g & 1, b = (g >> 1) & 1;
+    return ((w & 1) * 2 + b) + 4 * a + 8 * (w >> 1);
+}
+__device__ __forceinline__ int grp_column() {
+    const int g = threadIdx.x >> 3, w = g >> 2, a = g & 1, b = (g >> 1) & 1;
+    return ((w & 3) * 2 + b) + 8 * a + 16 * (w >> 2);
+}
+
+// freq-distributed spectrum Z of a packed row pair -> half spectra A (row0) and B (row1), columns 0..63,
+// with (DC, Nyquist) of each packed as re/im of column 0.
+__device__ __forceinline__ void untangle_store(const float2 (&v)[16], float2* row0, int t, bool live) {
+    float2 r[16];
+    fft128_partner<0, 4>(v, r, t);
+    if (!live) return;
+#pragma unroll
+    for (int s = 0; s < 2; s++)
+#pragma unroll
+        for (int k2 = 0; k2 < 4; k2++) {
+            const int k = t + 8 * s + 16 * k2;
+            const float2 z1 = v[8 * s + k2];
+            float2 z2 = r[8 * s + k2];
+            float2 A, B;
+            if (s == 0 && k2 == 0 && t == 0) {
+                z2 = v[4];                                    // Z[64]
+                A = make_float2(z1.x, z2.x);
+                B = make_float2(z1.y, z2.y);
+            } else {
+                A = make_float2(0.5f * (z1.x + z2.x), 0.5f * (z1.y - z2.y));
+                B = make_float2(0.5f * (z1.y + z2.y), 0.5f * (z2.x - z1.x));
+            }
+            row0[k] = A;
+            row0[RS + k] = B;
+        }
+}
+
+// inverse of untangle_store: rows hold swap(A'), swap(B') (the column phase leaves its result swapped);
+// returns swap(Z') freq-distributed, ready for fft128_f2t acting as the inverse transform.
+__device__ __forceinline__ void load_retangle(float2 (&v)[16], const float2* row0, int t, bool live) {
+    float2 w[16], r[16];
+    float2 z64 = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int s = 0; s < 2; s++)
+#pragma unroll
+        for (int k2 = 0; k2 < 4; k2++) {
+            const int k = t + 8 * s + 16 * k2;
+            float2 a = make_float2(0.f, 0.f), b = a;
+            if (live) { a = cswap(row0[k]); b = cswap(row0[RS + k]); }
+            if (s == 0 && k2 == 0 && t == 0) {
+                v[0] = make_float2(a.x, b.x);                 // Z[0]
+                z64 = make_float2(a.y, b.y);                  // Z[64]
+                w[0] = v[0];
+            } else {
+                v[8 * s + k2] = make_float2(a.x - b.y, a.y + b.x);      // A + iB
+                w[8 * s + k2] = make_float2(a.x + b.y, b.x - a.y);      // conj(A) + i conj(B) = Z[128 - k]
+            }
+        }
+#pragma unroll
+    for (int i = 0; i < 16; i++) if ((i & 7) >= 4) w[i] = make_float2(0.f, 0.f);
+    fft128_partner<4, 8>(w, r, t);
+#pragma unroll
+    for (int s = 0; s < 2; s++)
+#pragma unroll
+        for (int k2 = 4; k2 < 8; k2++) v[8 * s + k2] = r[8 * s + k2];
+    if (t == 0) v[4] = z64;
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = cswap(v[i]);
+}
+
+// forward column FFT, x D (or conj D), inverse column FFT; result left swapped in rows [0, NR).
+// Dt: transposed kernel spectrum [65][128] (Dt[kx*128 + ky]).
+template <bool CONJ>
+__device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, const float2* __restrict__ Dt, int NR) {
+    const int t = threadIdx.x & 7;
+#pragma unroll 1
+    for (int round = 0; round < 2; round++) {
+        const int kx = 32 * round + grp_column();
+        float2* col = buf + kx;
+        float2 v[16];
+#pragma unroll
+        for (int n1 = 0; n1 < 16; n1++) {
+            const int y = 8 * n1 + t;
+            v[n1] = (y < NR) ? col[y * RS] : make_float2(0.f, 0.f);
+        }
+        fft128_t2f(v, col, RS, t, tw);
+        if (kx > 0) {
+            const float2* Dc = Dt + kx * 128;
+#pragma unroll
+            for (int s = 0; s < 2; s++)
+#pragma unroll
+                for (int k2 = 0; k2 < 8; k2++) {
+                    const float2 d = Dc[t + 8 * s + 16 * k2];
+                    const float2 x = v[8 * s + k2];
+                    v[8 * s + k2] = cswap(CONJ ? cmulc(x, d) : cmul(x, d));
+                }
+        }
+        if (__any_sync(0xffffffffu, kx == 0)) {
+            // column 0 carries C = Col0 + i ColN (kx = 0 and kx = 64): split, multiply each, recombine
+            float2 r[16];
+            fft128_partner<0, 8>(v, r, t);
+            if (kx == 0) {
+#pragma unroll
+                for (int s = 0; s < 2; s++)
+#pragma unroll
+                    for (int k2 = 0; k2 < 8; k2++) {
+                        const int ky = t + 8 * s + 16 * k2;
+                        const float2 c1 = v[8 * s + k2], c2 = r[8 * s + k2];
+                        float2 p0 = make_float2(0.5f * (c1.x + c2.x), 0.5f * (c1.y - c2.y));
+                        float2 pn = make_float2(0.5f * (c1.y + c2.y), 0.5f * (c2.x - c1.x));
+                        const float2 d0 = Dt[ky], dn = Dt[64 * 128 + ky];
+                        p0 = CONJ ? cmulc(p0, d0) : cmul(p0, d0);
+                        pn = CONJ ? cmulc(pn, dn) : cmul(pn, dn);
+                        v[8 * s + k2] = cswap(make_float2(p0.x - pn.y, p0.y + pn.x));
+                    }
+            }
+        }
+        fft128_f2t(v, col, RS, t, tw);
+#pragma unroll
+        for (int n1 = 0; n1 < 16; n1++) {
+            const int y = 8 * n1 + t;
+            if (y < NR) col[y * RS] = v[n1];
+        }
+    }
+}
+
+}  // namespace
+
+// grid: (C * n_listed_blends); block: SCL_THREADS; dynamic smem: kFwdSmem (api.cu)
+//   buf [128][65] float2 | tw [256] float2 | dummy line [130] float2 | red [32] double
+extern "C" __global__ void __launch_bounds__(SCL_THREADS, 2)
 scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const float* __restrict__ S,        // [Ktot, N]
                       const int* __restrict__ comp_off,   // [B+1]
                       const float* __restrict__ images,   // [B, C, N]
                       const float* __restrict__ weights,  // [B, C, N] or nullptr (W = 1)
-                      const float2* __restrict__ Dhat,    // [n_ker, 128, 65]
+                      const float2* __restrict__ Dhat_t,  // [n_ker, 65, 128] transposed kernel spectra
                       const int* __restrict__ ker_idx,    // [B*C], -1 = identity (no PSF matching)
                       const int* __restrict__ active,     // [B]
                       const int* __restrict__ blend_list, // [gridDim.x / C] blends to process (compacted active list)
@@ -154,26 +289,27 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float2* buf = reinterpret_cast<float2*>(smem_raw);
     float2* tw = buf + F * RS;
-    double* red = reinterpret_cast<double*>(tw + 128);
-    __shared__ float sA[64];
+    float2* dummy = tw + 256;
+    double* red = reinterpret_cast<double*>(dummy + LS);
+    __shared__ float sA[SCL_MAX_COMP];
     __shared__ double sred[SCL_THREADS / 32][2 * SCL_MAX_COMP];
 
     const int c = blockIdx.x % C, b = blend_list[blockIdx.x / C];
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const int N = Ny * Nx;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = lane & 15, half = lane >> 4;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, t = threadIdx.x & 7;
     const int nwarp = blockDim.x >> 5;
     const int NR = (Ny + 1) & ~1, NP = NR >> 1;
     const float inv = 1.0f / (float)(F * F);
     const int kid = ker_idx[b * C + c];
-    const float2* D = Dhat + (size_t)(kid < 0 ? 0 : kid) * F * RS;
+    const float2* Dt = Dhat_t + (size_t)(kid < 0 ? 0 : kid) * RS * F;
     const float* img = images + ((size_t)b * C + c) * N;
     const float* wgt = weights ? weights + ((size_t)b * C + c) * N : nullptr;
     float* gout = G + ((size_t)b * C + c) * N;
 
-    fill_twiddles128(tw);
-    for (int k = threadIdx.x; k < K && k < 64; k += blockDim.x) sA[k] = A[(size_t)(k0 + k) * C + c];
+    fill_twiddles_reg(tw);
+    if (threadIdx.x < K) sA[threadIdx.x] = A[(size_t)(k0 + threadIdx.x) * C + c];
     __syncthreads();
 
     double loss = 0.0;
@@ -185,7 +321,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
         // identical PSFs: R = M, G = W^2 (M - I)   (observation.py:216-220)
         for (int p = threadIdx.x; p < N; p += blockDim.x) {
             float m = 0.f;
-            for (int k = 0; k < K; k++) m += A[(size_t)(k0 + k) * C + c] * S[(size_t)(k0 + k) * N + p];
+            for (int k = 0; k < K; k++) m += sA[k] * S[(size_t)(k0 + k) * N + p];
             float w = wgt ? wgt[p] : 1.f;
             float d = w * (m - img[p]);
             loss += (double)d * (double)d;
@@ -196,78 +332,85 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                 if (k < K) accA[k] += g * S[(size_t)(k0 + k) * N + p];
         }
     } else {
-        // ---- phase A: render rows, row FFT, untangle
-        for (int j0 = warp * 2; j0 < NP; j0 += nwarp * 2) {
-            int j = j0 + half;
-            bool live = j < NP;
-            float2* line = buf + j * LS;
-            if (live) {
-                int y0 = 2 * j, y1 = 2 * j + 1;
-                for (int x = t; x < Nx; x += 16) {
-                    float m0 = 0.f, m1 = 0.f;
+        const int jg = grp_row_line();
+        // ---- phase A: render row pairs (ComponentTree.get_model), row FFT, untangle
+        for (int j0 = 0; j0 < NP; j0 += 32) {
+            const int j = j0 + jg;
+            const bool live = j < NP;
+            float2* line = live ? buf + j * LS : dummy;
+            const int y0 = 2 * j, y1 = 2 * j + 1;
+            float2 v[16];
+#pragma unroll
+            for (int n1 = 0; n1 < 16; n1++) {
+                const int x = 8 * n1 + t;
+                float m0 = 0.f, m1 = 0.f;
+                if (live && x < Nx) {
                     for (int k = 0; k < K; k++) {
                         const float* Sk = S + (size_t)(k0 + k) * N;
-                        float a = (k < 64) ? sA[k] : A[(size_t)(k0 + k) * C + c];
+                        const float a = sA[k];
                         m0 += a * Sk[y0 * Nx + x];
                         if (y1 < Ny) m1 += a * Sk[y1 * Nx + x];
                     }
-                    line[x] = make_float2(m0, m1);
                 }
+                v[n1] = make_float2(m0, m1);
             }
-            __syncwarp();
-            fft_line16<128>(line, 1, t, tw, Nx, live);
-            untangle_line(line, t, live);
+            fft128_t2f(v, line, 1, t, tw);
+            untangle_store(v, line, t, live);
         }
         __syncthreads();
         // ---- phase B: columns, x D
-        column_phase<false>(buf, tw, D, NR);
+        column_phase_reg<false>(buf, tw, Dt, NR);
         __syncthreads();
-        // ---- phase C: inverse rows -> R; residual; forward rows of r
-        for (int j0 = warp * 2; j0 < NP; j0 += nwarp * 2) {
-            int j = j0 + half;
-            bool live = j < NP;
-            float2* line = buf + j * LS;
-            retangle_line(line, t, live);
-            fft_line16<128>(line, 1, t, tw, 128, live);
-            if (live) {
-                int y0 = 2 * j, y1 = 2 * j + 1;
-                for (int x = t; x < Nx; x += 16) {
-                    float2 z = line[x];                    // swapped: (im, re)
-                    float r0 = z.y * inv, r1 = z.x * inv;
-                    int p0 = y0 * Nx + x, p1 = y1 * Nx + x;
-                    float w0 = wgt ? wgt[p0] : 1.f;
-                    float d0 = w0 * (r0 - img[p0]);
+        // ---- phase C: inverse rows -> R; residual r = W^2 (R - I) and logL; forward rows of r
+        for (int j0 = 0; j0 < NP; j0 += 32) {
+            const int j = j0 + jg;
+            const bool live = j < NP;
+            float2* line = live ? buf + j * LS : dummy;
+            const int y0 = 2 * j, y1 = 2 * j + 1;
+            float2 v[16];
+            load_retangle(v, line, t, live);
+            fft128_f2t(v, line, 1, t, tw);
+#pragma unroll
+            for (int n1 = 0; n1 < 16; n1++) {
+                const int x = 8 * n1 + t;
+                float o0 = 0.f, o1 = 0.f;
+                if (live && x < Nx) {
+                    const float r0 = v[n1].y * inv, r1 = v[n1].x * inv;       // swapped: (im, re)
+                    const int p0 = y0 * Nx + x, p1 = y1 * Nx + x;
+                    const float w0 = wgt ? wgt[p0] : 1.f;
+                    const float d0 = w0 * (r0 - img[p0]);
                     loss += (double)d0 * (double)d0;
-                    float o0 = w0 * d0, o1 = 0.f;
+                    o0 = w0 * d0;
                     if (y1 < Ny) {
-                        float w1 = wgt ? wgt[p1] : 1.f;
-                        float d1 = w1 * (r1 - img[p1]);
+                        const float w1 = wgt ? wgt[p1] : 1.f;
+                        const float d1 = w1 * (r1 - img[p1]);
                         loss += (double)d1 * (double)d1;
                         o1 = w1 * d1;
                     }
-                    line[x] = make_float2(o0, o1);
                 }
+                v[n1] = make_float2(o0, o1);
             }
-            __syncwarp();
-            fft_line16<128>(line, 1, t, tw, Nx, live);
-            untangle_line(line, t, live);
+            fft128_t2f(v, line, 1, t, tw);
+            untangle_store(v, line, t, live);
         }
         __syncthreads();
         // ---- phase D: columns, x conj(D)
-        column_phase<true>(buf, tw, D, NR);
+        column_phase_reg<true>(buf, tw, Dt, NR);
         __syncthreads();
-        // ---- phase E: inverse rows -> G
-        for (int j0 = warp * 2; j0 < NP; j0 += nwarp * 2) {
-            int j = j0 + half;
-            bool live = j < NP;
-            float2* line = buf + j * LS;
-            retangle_line(line, t, live);
-            fft_line16<128>(line, 1, t, tw, 128, live);
-            if (live) {
-                int y0 = 2 * j, y1 = 2 * j + 1;
-                for (int x = t; x < Nx; x += 16) {
-                    float2 z = line[x];
-                    const float g0 = z.y * inv, g1 = (y1 < Ny) ? z.x * inv : 0.f;
+        // ---- phase E: inverse rows -> G, and this band's SED gradient
+        for (int j0 = 0; j0 < NP; j0 += 32) {
+            const int j = j0 + jg;
+            const bool live = j < NP;
+            float2* line = live ? buf + j * LS : dummy;
+            const int y0 = 2 * j, y1 = 2 * j + 1;
+            float2 v[16];
+            load_retangle(v, line, t, live);
+            fft128_f2t(v, line, 1, t, tw);
+#pragma unroll
+            for (int n1 = 0; n1 < 16; n1++) {
+                const int x = 8 * n1 + t;
+                if (live && x < Nx) {
+                    const float g0 = v[n1].y * inv, g1 = (y1 < Ny) ? v[n1].x * inv : 0.f;
                     const int p0 = y0 * Nx + x, p1 = (y1 < Ny) ? y1 * Nx + x : p0;
                     gout[p0] = g0;
                     if (y1 < Ny) gout[p1] = g1;
@@ -323,6 +466,12 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
             gram[(size_t)b * 64 + r * 8 + threadIdx.x] = v;
         }
     }
+}
+
+// [n][128][65] -> [n][65][128]; grid: n * 65 blocks of 128 threads
+extern "C" __global__ void scl_k_transpose_spec(const float2* __restrict__ in, float2* __restrict__ out) {
+    const int n = blockIdx.x / RS, kx = blockIdx.x % RS, ky = threadIdx.x;
+    out[((size_t)n * RS + kx) * F + ky] = in[((size_t)n * F + ky) * RS + kx];
 }
 
 // Standalone render: observation.render(model) for host callers (drop-in
