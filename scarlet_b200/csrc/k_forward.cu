@@ -282,7 +282,6 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const int* __restrict__ blend_list, // [gridDim.x / C] blends to process (compacted active list)
                       float* __restrict__ G,              // [B, C, N]
                       double* __restrict__ loss_part,     // [B, C]
-                      float* __restrict__ dA,             // [Ktot, C]  sum_p G[c,p] S[k,p]   (K <= 8)
                       double* __restrict__ gram,          // [B, 8, 8]  rows r = c, c+C, .. of S S^T
                       int C, int Ny, int Nx)
 {
@@ -309,13 +308,16 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     float* gout = G + ((size_t)b * C + c) * N;
 
     fill_twiddles_reg(tw);
-    if (threadIdx.x < K) sA[threadIdx.x] = A[(size_t)(k0 + threadIdx.x) * C + c];
+    if (threadIdx.x < SCL_MAX_COMP) sA[threadIdx.x] = (threadIdx.x < K) ? A[(size_t)(k0 + threadIdx.x) * C + c] : 0.f;
     __syncthreads();
 
     double loss = 0.0;
-    float accA[SCL_MAX_COMP];            // this thread's share of dA[k, c]
+    // Gram rows r0 = c and r1 = c + C of S S^T (Blend._set_lipschitz, blend.py:205-217) ride on the render loads;
+    // further rows (only when K > 2C) take the separate pass at the end
+    float gr0[SCL_MAX_COMP], gr1[SCL_MAX_COMP];
 #pragma unroll
-    for (int k = 0; k < SCL_MAX_COMP; k++) accA[k] = 0.f;
+    for (int k = 0; k < SCL_MAX_COMP; k++) { gr0[k] = 0.f; gr1[k] = 0.f; }
+    const int r0 = c, r1 = c + C;
 
     if (kid < 0) {
         // identical PSFs: R = M, G = W^2 (M - I)   (observation.py:216-220)
@@ -325,11 +327,34 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
             float w = wgt ? wgt[p] : 1.f;
             float d = w * (m - img[p]);
             loss += (double)d * (double)d;
-            const float g = w * d;
-            gout[p] = g;
+            gout[p] = w * d;
+        }
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            float sv[SCL_MAX_COMP];
 #pragma unroll
-            for (int k = 0; k < SCL_MAX_COMP; k++)
-                if (k < K) accA[k] += g * S[(size_t)(k0 + k) * N + p];
+            for (int k = 0; k < SCL_MAX_COMP; k++) sv[k] = (k < K) ? S[(size_t)(k0 + k) * N + p] : 0.f;
+            float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+            for (int k = 0; k < SCL_MAX_COMP; k++) { a0 = (k == r0) ? sv[k] : a0; a1 = (k == r1) ? sv[k] : a1; }
+#pragma unroll
+            for (int k = 0; k < SCL_MAX_COMP; k++) { gr0[k] += a0 * sv[k]; gr1[k] += a1 * sv[k]; }
+        }
+        // Gram rows c and c + C: reduce now so that the accumulators die before the column phase
+        {
+#pragma unroll
+            for (int l = 0; l < SCL_MAX_COMP; l++) {
+                double v0 = warp_sum<double>((double)gr0[l]), v1 = warp_sum<double>((double)gr1[l]);
+                if (lane == 0) { sred[warp][l] = v0; sred[warp][SCL_MAX_COMP + l] = v1; }
+            }
+            __syncthreads();
+            if (threadIdx.x < 2 * SCL_MAX_COMP) {
+                const int l = threadIdx.x & (SCL_MAX_COMP - 1), r = (threadIdx.x < SCL_MAX_COMP) ? r0 : r1;
+                if (r < K && l < K) {
+                    double v = 0.0;
+                    for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
+                    gram[(size_t)b * 64 + r * 8 + l] = v;
+                }
+            }
         }
     } else {
         const int jg = grp_row_line();
@@ -345,17 +370,48 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                 const int x = 8 * n1 + t;
                 float m0 = 0.f, m1 = 0.f;
                 if (live && x < Nx) {
-                    for (int k = 0; k < K; k++) {
+                    float s0[SCL_MAX_COMP], s1[SCL_MAX_COMP];
+#pragma unroll
+                    for (int k = 0; k < SCL_MAX_COMP; k++) {
                         const float* Sk = S + (size_t)(k0 + k) * N;
-                        const float a = sA[k];
-                        m0 += a * Sk[y0 * Nx + x];
-                        if (y1 < Ny) m1 += a * Sk[y1 * Nx + x];
+                        s0[k] = (k < K) ? Sk[y0 * Nx + x] : 0.f;
+                        s1[k] = (k < K && y1 < Ny) ? Sk[y1 * Nx + x] : 0.f;
+                    }
+                    float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;      // S[r0], S[r1] at the two pixels
+#pragma unroll
+                    for (int k = 0; k < SCL_MAX_COMP; k++) {
+                        m0 += sA[k] * s0[k];
+                        m1 += sA[k] * s1[k];
+                        a0 = (k == r0) ? s0[k] : a0; b0 = (k == r0) ? s1[k] : b0;
+                        a1 = (k == r1) ? s0[k] : a1; b1 = (k == r1) ? s1[k] : b1;
+                    }
+#pragma unroll
+                    for (int k = 0; k < SCL_MAX_COMP; k++) {
+                        gr0[k] += a0 * s0[k] + b0 * s1[k];
+                        gr1[k] += a1 * s0[k] + b1 * s1[k];
                     }
                 }
                 v[n1] = make_float2(m0, m1);
             }
             fft128_t2f(v, line, 1, t, tw);
             untangle_store(v, line, t, live);
+        }
+        // Gram rows c and c + C: reduce now so that the accumulators die before the column phase
+        {
+#pragma unroll
+            for (int l = 0; l < SCL_MAX_COMP; l++) {
+                double v0 = warp_sum<double>((double)gr0[l]), v1 = warp_sum<double>((double)gr1[l]);
+                if (lane == 0) { sred[warp][l] = v0; sred[warp][SCL_MAX_COMP + l] = v1; }
+            }
+            __syncthreads();
+            if (threadIdx.x < 2 * SCL_MAX_COMP) {
+                const int l = threadIdx.x & (SCL_MAX_COMP - 1), r = (threadIdx.x < SCL_MAX_COMP) ? r0 : r1;
+                if (r < K && l < K) {
+                    double v = 0.0;
+                    for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
+                    gram[(size_t)b * 64 + r * 8 + l] = v;
+                }
+            }
         }
         __syncthreads();
         // ---- phase B: columns, x D
@@ -397,7 +453,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
         // ---- phase D: columns, x conj(D)
         column_phase_reg<true>(buf, tw, Dt, NR);
         __syncthreads();
-        // ---- phase E: inverse rows -> G, and this band's SED gradient
+        // ---- phase E: inverse rows -> G
         for (int j0 = 0; j0 < NP; j0 += 32) {
             const int j = j0 + jg;
             const bool live = j < NP;
@@ -410,16 +466,8 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
             for (int n1 = 0; n1 < 16; n1++) {
                 const int x = 8 * n1 + t;
                 if (live && x < Nx) {
-                    const float g0 = v[n1].y * inv, g1 = (y1 < Ny) ? v[n1].x * inv : 0.f;
-                    const int p0 = y0 * Nx + x, p1 = (y1 < Ny) ? y1 * Nx + x : p0;
-                    gout[p0] = g0;
-                    if (y1 < Ny) gout[p1] = g1;
-#pragma unroll
-                    for (int k = 0; k < SCL_MAX_COMP; k++)
-                        if (k < K) {
-                            const float* Sk = S + (size_t)(k0 + k) * N;
-                            accA[k] += g0 * Sk[p0] + g1 * Sk[p1];
-                        }
+                    gout[y0 * Nx + x] = v[n1].y * inv;
+                    if (y1 < Ny) gout[y1 * Nx + x] = v[n1].x * inv;
                 }
             }
         }
@@ -427,22 +475,8 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     double tot = block_sum<double>(loss, red);
     if (threadIdx.x == 0) loss_part[b * C + c] = 0.5 * tot;
 
-    // ---- SED gradient of this band: dA[k, c]
-    {
-#pragma unroll
-        for (int k = 0; k < SCL_MAX_COMP; k++) {
-            double v = warp_sum<double>((double)accA[k]);
-            if (lane == 0) sred[warp][k] = v;
-        }
-        __syncthreads();
-        if (threadIdx.x < K) {
-            double v = 0.0;
-            for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
-            dA[(size_t)(k0 + threadIdx.x) * C + c] = (float)v;
-        }
-    }
-    // ---- rows r = c, c + C, ... of the Gram matrix S S^T (Blend._set_lipschitz, blend.py:205-217)
-    for (int r = c; r < K; r += C) {
+    // ---- remaining rows r = c + 2C, ... (K > 2C only)
+    for (int r = c + 2 * C; r < K; r += C) {
         float acc[SCL_MAX_COMP];
 #pragma unroll
         for (int l = 0; l < SCL_MAX_COMP; l++) acc[l] = 0.f;

@@ -1,15 +1,14 @@
 // K2: per-blend scalar work between the likelihood kernel (K1) and the constraint kernel (K3):
-// loss bookkeeping, Lipschitz constants, SED gradient step.  Two threads per blend (one per Gram
-// matrix), everything in registers.
+// loss bookkeeping and Lipschitz constants.  Two threads per blend (one per Gram matrix), everything
+// in registers.
 //
 // Replaces (reference file:line):
 //   Blend.mse bookkeeping        blend.py:138 (loss BEFORE the step)
 //   Blend._set_lipschitz         blend.py:186-223
 //       exact:  L_sed = n_obs lambda_max(S S^T),  L_morph = n_obs lambda_max(A^T A)
 //       approx: L_sed = n_obs sum|S|^2, L_morph = n_obs sum|A|^2, x2 if the loss rose
-//   SED step                     blend.py:91-93   A[k] -= sed_grad[k] / L_sed
-// Inputs produced by K1: loss_part[b,c], dA[k,c] = sum_p G[c,p] S[k,p], gram[b] = S S^T (double 8x8).
-// The morphology step (blend.py:94-96) is applied by K3 with the L_morph written here.
+// Inputs produced by K1: loss_part[b,c], gram[b] = S S^T (double 8x8).
+// Both gradient steps (blend.py:91-96) are applied by K3 with the constants written here.
 //
 // lambda_max: cyclic Jacobi in f32 on the register-resident 8x8 matrix (zero padded) with the rotations
 // accumulated into V, then the Rayleigh quotient of the winning column in f64 against the f64 matrix:
@@ -83,10 +82,7 @@ __device__ __forceinline__ void jacobi8_top_vector(float (&a)[JN][JN], float (&v
 // grid: ceil(2B / 128); block: 128 threads; thread 2b handles S S^T of blend b, thread 2b+1 handles A^T A.
 extern "C" __global__ void __launch_bounds__(128)
 scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
-                float* __restrict__ A_new,            // [Ktot, C]  stepped SEDs
                 const int* __restrict__ comp_off,     // [B+1]
-                const unsigned* __restrict__ cflags,  // [Ktot]
-                const float* __restrict__ dA,         // [Ktot, C]  SED gradient (K1)
                 const double* __restrict__ gram,      // [B, 8, 8]  S S^T (K1), rows/cols >= K unspecified
                 const double* __restrict__ loss_part, // [B, C]
                 const int* __restrict__ active,       // [B]
@@ -181,13 +177,5 @@ scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
         if (step < logL_cap) logL[(size_t)b * logL_cap + step] = total;
         lips[b * 2] = L_sed;
         lips[b * 2 + 1] = L_morph;
-    }
-    // SED step, split between the two threads (blend.py:91-93)
-    const float step_sed = 1.0f / L_sed;
-    for (int i = which; i < K * C; i += 2) {
-        const int k = i / C;
-        float a = A[(size_t)k0 * C + i];
-        if (!(cflags[k0 + k] & SCL_F_FIX_SED)) a = a - step_sed * dA[(size_t)k0 * C + i];
-        A_new[(size_t)k0 * C + i] = a;
     }
 }

@@ -11,8 +11,7 @@
 #include "prox_dev.cuh"
 
 struct SclProxArgs {
-    const float* A_step;      // [Ktot, C]  SEDs after the gradient step (K2)
-    const float* G;           // [B, C, N]  d loss / d model (K1); nullptr: no morphology step (construction pass)
+    const float* G;           // [B, C, N]  d loss / d model (K1); nullptr: no gradient step (construction pass)
     const float* lips;        // [B, 2]     (L_sed, L_morph) (K2)
     float* A;                 // [Ktot, C]  in: previous iterate; out: new iterate
     float* S;                 // [Ktot, N]  in: previous iterate; out: new iterate
@@ -55,24 +54,49 @@ scl_k_prox(SclProxArgs a)
     const unsigned fl = a.cflags[k];
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
-    // morphology gradient step (blend.py:94-96): S[k] -= (1/L_morph) sum_c A[k,c] G[c]
+    // gradients of this component (chain rule through Component.get_model, component.py:166-167):
+    //   dS[p] = sum_c A[k,c] G[c,p]      dA[c] = sum_p G[c,p] S[k,p]
+    // and the morphology step (blend.py:94-96): S[k] -= (1/L_morph) dS
+    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
+    __shared__ float sAnew[SCL_MAX_BANDS];
     {
         const float* Sin = a.S + (size_t)k * N;
-        if (a.G && !(fl & SCL_F_FIX_MORPH)) {
+        if (a.G) {
+            const bool fixm = fl & SCL_F_FIX_MORPH;
             const float step_morph = 1.0f / a.lips[2 * b + 1];
             const float* Gb = a.G + (size_t)b * C * N;
-            float ak[SCL_MAX_BANDS];
+            float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
-            for (int c = 0; c < SCL_MAX_BANDS; c++) ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f;
+            for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f; dAc[c] = 0.f; }
             for (int p = threadIdx.x; p < N; p += blockDim.x) {
+                const float s = Sin[p];
                 float d = 0.f;
 #pragma unroll
                 for (int c = 0; c < SCL_MAX_BANDS; c++)
-                    if (c < C) d += ak[c] * Gb[(size_t)c * N + p];
-                X[p] = Sin[p] - step_morph * d;
+                    if (c < C) {
+                        const float g = Gb[(size_t)c * N + p];
+                        d += ak[c] * g;
+                        dAc[c] += g * s;
+                    }
+                X[p] = fixm ? s : s - step_morph * d;
+            }
+#pragma unroll
+            for (int c = 0; c < SCL_MAX_BANDS; c++) {
+                const double v = warp_sum<double>((double)dAc[c]);
+                if ((threadIdx.x & 31) == 0) sdA[threadIdx.x >> 5][c] = v;
+            }
+            __syncthreads();
+            if (threadIdx.x < C) {
+                // SED step (blend.py:91-93): A[k] -= (1/L_sed) dA
+                double v = 0.0;
+                for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][threadIdx.x];
+                float an = a.A[(size_t)k * C + threadIdx.x];
+                if (!(fl & SCL_F_FIX_SED)) an = an - (1.0f / a.lips[2 * b]) * (float)v;
+                sAnew[threadIdx.x] = an;
             }
         } else {
             for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
+            if (threadIdx.x < C) sAnew[threadIdx.x] = a.A[(size_t)k * C + threadIdx.x];
         }
     }
     if (threadIdx.x == 0) {
@@ -143,7 +167,7 @@ scl_k_prox(SclProxArgs a)
     if (threadIdx.x == 0) {
         double ad2 = 0.0, an2 = 0.0;
         for (int c = 0; c < C; c++) {
-            float v = a.A_step[(size_t)k * C + c];
+            float v = sAnew[c];
             if (constrained) {
                 if (v < 0.f) v = 0.f;
                 v = v * norm;
