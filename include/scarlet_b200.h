@@ -126,6 +126,10 @@ int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* cent
  * repeated from the same starting point without another host upload (stream-ordered device-to-device copies). */
 int scl_batch_snapshot(scl_batch* batch, void* stream);
 int scl_batch_restore(scl_batch* batch, void* stream);
+/* Profiling aid: while enabled, the constraint kernel adds the clock64 ticks each of its phases took (summed over
+ * CTAs: 0 gradient step, 1 centre + symmetry, 2 level list, 3 monotonic sweep, 4 normalise/write-back) to a device
+ * counter; the call returns the sums so far in out8 (may be NULL) and clears them. */
+int scl_batch_phase_clocks(scl_batch* batch, int enable, unsigned long long* out8);
 void scl_batch_destroy(scl_batch* batch);
 
 #ifdef __cplusplus

@@ -9,7 +9,7 @@ import threading
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libscarlet_b200.so")
+LIB_PATH = os.environ.get("SCL_LIB") or os.path.join(_HERE, "lib", "libscarlet_b200.so")     # SCL_LIB: experiment builds
 
 FFT_EDGE = 128
 SPEC_COLS = 65
@@ -336,6 +336,12 @@ class Batch:
     def constrain(self):
         """One `update()` pass with it = 0 on every component (what sources run at construction)."""
         _check(lib().scl_batch_constrain(self._h, c_void_p(self.stream)))
+
+    def phase_clocks(self, enable=True):
+        """Enable/disable/read the constraint kernel's per-phase clock sums (profiling)."""
+        out = (ctypes.c_ulonglong * 8)()
+        _check(lib().scl_batch_phase_clocks(self._h, int(bool(enable)), out))
+        return [int(v) for v in out]
 
     def snapshot(self):
         _check(lib().scl_batch_snapshot(self._h, c_void_p(self.stream)))

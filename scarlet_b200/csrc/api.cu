@@ -48,8 +48,8 @@ int next_fast_len(int target) {     // smallest 2^a 3^b 5^c >= target (scipy.fft
 }
 
 struct Tables {
-    float* wtab = nullptr;
-    double* ctab = nullptr;
+    float* wtab = nullptr;       // [9][(2Ny-1)(2Nx-1)][8]
+    double* ctab = nullptr;      // [(2Ny-1)(2Nx-1)][8]
 };
 std::mutex g_mu;
 std::map<std::pair<int, int>, Tables> g_tables;
@@ -98,8 +98,10 @@ int get_tables(int Ny, int Nx, Tables* t) {
 }
 
 size_t prox_smem(int Ny, int Nx) {
+    // X [N] (rounded to 16 bytes) | Z [Ny][(Nx+3)&~3] | tables
     int mx = Ny > Nx ? Ny : Nx;
-    return ((size_t)2 * Ny * Nx + 3 * (2 * mx - 1) + 2 * Nx + 8) * sizeof(float);
+    size_t n4 = ((size_t)Ny * Nx + 3) & ~(size_t)3;
+    return (n4 + (size_t)Ny * ((Nx + 3) & ~3) + 3 * (2 * mx - 1) + 2 * Nx + 32) * sizeof(float);
 }
 
 int check_shape(int Ny, int Nx) {
@@ -142,7 +144,7 @@ static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T 
     CK(dc.alloc(2 * (size_t)n));
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
-    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
+    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T) + 16 + scl_mono_work_bytes((int)N, 3 * (Ny > Nx ? Ny : Nx)), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
     CK(cudaGetLastError());
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));
@@ -212,7 +214,7 @@ int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* center
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
     if (shifts) CK(ds.up(shifts, s)); else CK(cudaMemsetAsync(ds.p, 0, 2 * (size_t)n * sizeof(double), s));
-    scl_k_symmetry<<<n, SCL_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl, g_nfl_even);
+    scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl, g_nfl_even);
     CK(cudaGetLastError());
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));

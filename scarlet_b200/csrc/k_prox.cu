@@ -32,11 +32,12 @@ struct SclProxArgs {
     int C, Ny, Nx, ph, pw, step;
     int it_override;          // >= 0: the iteration number update() sees (0 = source construction)
     double e_rel2;
+    unsigned long long* phase_clk;   // optional [8]: summed clock64 per phase over all CTAs (profiling; nullptr = off)
 };
 
 // dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
 // block: SCL_PROX_THREADS
-extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
 scl_k_prox(SclProxArgs a)
 {
     extern __shared__ __align__(16) float smem_f[];
@@ -45,13 +46,16 @@ scl_k_prox(SclProxArgs a)
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
     float* X = smem_f;
-    float* Z = X + N;
-    float* tab = Z + N;
+    float* Z = X + ((N + 3) & ~3);
+    float* tab = Z + Ny * ((Nx + 3) & ~3);
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
     __shared__ float sm;
     const unsigned fl = a.cflags[k];
+    long long tprev = a.phase_clk ? clock64() : 0;
+#define SCL_PHASE(i) do { if (a.phase_clk && threadIdx.x == 0) { long long t_ = clock64(); \
+        atomicAdd(a.phase_clk + (i), (unsigned long long)(t_ - tprev)); tprev = t_; } } while (0)
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
     // gradients of this component (chain rule through Component.get_model, component.py:166-167):
@@ -68,6 +72,7 @@ scl_k_prox(SclProxArgs a)
             float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f; dAc[c] = 0.f; }
+#pragma unroll 4
             for (int p = threadIdx.x; p < N; p += blockDim.x) {
                 const float s = Sin[p];
                 float d = 0.f;
@@ -104,6 +109,7 @@ scl_k_prox(SclProxArgs a)
         ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
     }
     __syncthreads();
+    SCL_PHASE(0);      // gradient step
 
     if (fl & SCL_F_CONSTRAINED) {
         scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
@@ -123,10 +129,22 @@ scl_k_prox(SclProxArgs a)
                 scl_flip_symmetry(X, Nx, w, 0, 1.0f);
             }
         }
+        SCL_PHASE(1);  // max_pixel, centroid, symmetry
         if (fl & SCL_F_MONOTONIC) {
-            if (Ny >= 2 && Nx >= 2) scl_monotonic_f32<SCL_PROX_THREADS>(X, Ny, Nx, sc[0], sc[1], a.wtab, 0.f);
-            else scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+            const int ay = max(sc[0], Ny - 1 - sc[0]), ax = max(sc[1], Nx - 1 - sc[1]);
+            const int vmax = 2 * max(ay, ax) + min(ay, ax);
+            if (Ny >= 2 && Nx >= 2 && Ny <= 256 && Nx <= 256 &&
+                scl_mono_work_bytes(N, vmax) <= (size_t)Ny * ((Nx + 3) & ~3) * sizeof(float)) {
+                const SclMonoWork wk = scl_mono_work(Z, N, vmax);           // Z is dead after the symmetry step
+                scl_mono_build(wk, Ny, Nx, sc[0], sc[1], vmax);
+                SCL_PHASE(2);  // level list
+                if (threadIdx.x < 32) scl_monotonic_f32_warp(X, Ny, Nx, sc[0], sc[1], wk, a.wtab, 0.f, vmax);
+                __syncthreads();
+            } else {
+                scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+            }
         }
+        SCL_PHASE(3);  // monotonic sweep
         // positive (update.py:27-32) + morph_max (update.py:62-65)
         float mx = -INFINITY;
         for (int p = threadIdx.x; p < N; p += blockDim.x) {
@@ -154,6 +172,7 @@ scl_k_prox(SclProxArgs a)
     // write back + convergence sums (blend.py:160-174)
     double d2 = 0.0, n2 = 0.0;
     float* Sout = a.S + (size_t)k * N;
+#pragma unroll 4
     for (int p = threadIdx.x; p < N; p += blockDim.x) {
         float v = constrained ? X[p] / norm : X[p];
         float old = Sout[p];
@@ -187,6 +206,8 @@ scl_k_prox(SclProxArgs a)
         a.center[2 * k] = sc[0]; a.center[2 * k + 1] = sc[1];
         a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
     }
+    SCL_PHASE(4);      // positivity, normalisation, write-back, convergence
+#undef SCL_PHASE
 }
 
 // K4: one thread per listed blend.  blend.py:157-176: never converged before it > 1.
@@ -258,10 +279,15 @@ scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, i
     T* g = imgs + (size_t)blockIdx.x * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
-    if (sizeof(T) == 4 && !NEAREST && Ny >= 2 && Nx >= 2 && blockDim.x == SCL_PROX_THREADS)
-        scl_monotonic_f32<SCL_PROX_THREADS>(reinterpret_cast<float*>(X), Ny, Nx, centers[2 * blockIdx.x],
-                                            centers[2 * blockIdx.x + 1], wtab, (float)thresh);
-    else
+    const int cy = centers[2 * blockIdx.x], cx = centers[2 * blockIdx.x + 1];
+    const int vmax = 2 * max(max(cy, Ny - 1 - cy), max(cx, Nx - 1 - cx)) + min(max(cy, Ny - 1 - cy), max(cx, Nx - 1 - cx));
+    if (sizeof(T) == 4 && !NEAREST && Ny >= 2 && Nx >= 2 && Ny <= 256 && Nx <= 256) {
+        // dynamic smem: image [N] T, then the level-list scratch
+        const SclMonoWork wk = scl_mono_work(smem_b + (((size_t)N * sizeof(T) + 15) & ~(size_t)15), N, vmax);
+        scl_mono_build(wk, Ny, Nx, cy, cx, vmax);
+        if (threadIdx.x < 32) scl_monotonic_f32_warp(reinterpret_cast<float*>(X), Ny, Nx, cy, cx, wk, wtab, (float)thresh, vmax);
+        __syncthreads();
+    } else
         scl_monotonic<T, NEAREST>(X, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
     for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
 }
@@ -278,8 +304,8 @@ scl_k_symmetry(float* __restrict__ imgs, const int* __restrict__ centers, const 
     extern __shared__ __align__(16) float smem_f[];
     const int N = Ny * Nx;
     float* X = smem_f;
-    float* Z = X + N;
-    float* tab = Z + N;
+    float* Z = X + ((N + 3) & ~3);
+    float* tab = Z + Ny * ((Nx + 3) & ~3);
     float* g = imgs + (size_t)blockIdx.x * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();

@@ -119,8 +119,8 @@ __device__ __forceinline__ void scl_dirichlet(float* T, float* H, int n, int F, 
     }
 }
 
-// k-space symmetry on the window w of X (in place).  Z: scratch of ny*nx floats;
-// tab: scratch of >= 3*(2*max(ny,nx)-1) + 2*nx floats.  nfl: next_fast_len table
+// k-space symmetry on the window w of X (in place).  Z: 16-byte aligned scratch of ny*((nx+3)&~3) floats;
+// tab: scratch of >= 3*(2*max(ny,nx)-1) + 2*nx + 16 floats.  nfl: next_fast_len table
 // (nfl[n] = smallest 5-smooth >= n), nfl_even likewise but even.
 __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, double dx,
                                     float* Z, float* tab, const int* __restrict__ nfl,
@@ -136,27 +136,35 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
     scl_dirichlet(Tx, Hx, nx, Fx, 2.0 * dx, true);
     __syncthreads();
     float* Xw = X + w.y0 * Nx + w.x0;
-    // Z[i][j] = sum_l Xw[i][l] Tx[j + l]      (4x4 register tiles)
-    const int ty4 = (ny + 3) / 4, tx4 = (nx + 3) / 4;
-    for (int tile = threadIdx.x; tile < ty4 * tx4; tile += blockDim.x) {
-        int i0 = (tile / tx4) * 4, j0 = (tile % tx4) * 4;
-        float acc[4][4] = {};
+    // Z[i][j] = sum_l Xw[i][l] Tx[j + l]: 8x4 register tiles, the four table values slide along l (one new
+    // load per step).  Rows/columns of a tile that fall outside the window read in-bounds garbage whose
+    // products only reach outputs that are never used (Z's pad columns, unsaved rows).
+    const int Zs = (nx + 3) & ~3;
+    const int nty = (ny + 7) / 8, ntx = Zs / 4;
+    for (int tile = threadIdx.x; tile < nty * ntx; tile += blockDim.x) {
+        const int i0 = (tile / ntx) * 8, j0 = (tile % ntx) * 4;
+        float acc[8][4];
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
+        const float* xr = Xw + i0 * Nx;
+        const float* tp = Tx + j0;
+        float t0 = tp[0], t1 = tp[1], t2 = tp[2];
+#pragma unroll 4
         for (int l = 0; l < nx; l++) {
-            float xv[4], tv[4];
+            const float t3 = tp[l + 3];
 #pragma unroll
-            for (int r = 0; r < 4; r++) xv[r] = (i0 + r < ny) ? Xw[(i0 + r) * Nx + l] : 0.f;
-#pragma unroll
-            for (int c = 0; c < 4; c++) tv[c] = (j0 + c < nx) ? Tx[j0 + c + l] : 0.f;
-#pragma unroll
-            for (int r = 0; r < 4; r++)
-#pragma unroll
-                for (int c = 0; c < 4; c++) acc[r][c] += xv[r] * tv[c];
+            for (int r = 0; r < 8; r++) {
+                const float xv = xr[r * Nx + l];
+                acc[r][0] += xv * t0; acc[r][1] += xv * t1; acc[r][2] += xv * t2; acc[r][3] += xv * t3;
+            }
+            t0 = t1; t1 = t2; t2 = t3;
         }
 #pragma unroll
-        for (int r = 0; r < 4; r++)
-#pragma unroll
-            for (int c = 0; c < 4; c++)
-                if (i0 + r < ny && j0 + c < nx) Z[(i0 + r) * nx + j0 + c] = acc[r][c];
+        for (int r = 0; r < 8; r++)
+            if (i0 + r < ny)
+                *reinterpret_cast<float4*>(Z + (i0 + r) * Zs + j0) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
     }
     const bool nyq = (Fy % 2 == 0);
     const int oy = (Fy - ny + 1) / 2 - Fy / 2;
@@ -180,30 +188,38 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
         }
         __syncthreads();
     }
-    // Y[i][j] = sum_l Ty[i + l] Z[l][j];  X <- (X <= 0) ? 0 : (X + Y)/2
-    for (int tile = threadIdx.x; tile < ty4 * tx4; tile += blockDim.x) {
-        int i0 = (tile / tx4) * 4, j0 = (tile % tx4) * 4;
-        float acc[4][4] = {};
+    // Y[i][j] = sum_l Ty[i + l] Z[l][j];  X <- (X <= 0) ? 0 : (X + Y)/2       (8x4 tiles, eight sliding table values)
+    for (int tile = threadIdx.x; tile < nty * ntx; tile += blockDim.x) {
+        const int i0 = (tile / ntx) * 8, j0 = (tile % ntx) * 4;
+        float acc[8][4];
+#pragma unroll
+        for (int r = 0; r < 8; r++)
+#pragma unroll
+            for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
+        const float* tp = Ty + i0;
+        float t[8];
+#pragma unroll
+        for (int r = 0; r < 7; r++) t[r] = tp[r];
+#pragma unroll 8
         for (int l = 0; l < ny; l++) {
-            float tv[4], zv[4];
+            t[7] = tp[l + 7];
+            const float4 zv = *reinterpret_cast<const float4*>(Z + l * Zs + j0);
 #pragma unroll
-            for (int r = 0; r < 4; r++) tv[r] = (i0 + r < ny) ? Ty[i0 + r + l] : 0.f;
+            for (int r = 0; r < 8; r++) {
+                acc[r][0] += t[r] * zv.x; acc[r][1] += t[r] * zv.y; acc[r][2] += t[r] * zv.z; acc[r][3] += t[r] * zv.w;
+            }
 #pragma unroll
-            for (int c = 0; c < 4; c++) zv[c] = (j0 + c < nx) ? Z[l * nx + j0 + c] : 0.f;
-#pragma unroll
-            for (int r = 0; r < 4; r++)
-#pragma unroll
-                for (int c = 0; c < 4; c++) acc[r][c] += tv[r] * zv[c];
+            for (int r = 0; r < 7; r++) t[r] = t[r + 1];
         }
 #pragma unroll
-        for (int r = 0; r < 4; r++)
+        for (int r = 0; r < 8; r++)
 #pragma unroll
             for (int c = 0; c < 4; c++) {
-                int i = i0 + r, j = j0 + c;
+                const int i = i0 + r, j = j0 + c;
                 if (i < ny && j < nx) {
                     float y = acc[r][c];
                     if (nyq) y += (((i + oy) & 1) ? -1.f : 1.f) * vvec[j];
-                    float x = Xw[i * Nx + j];
+                    const float x = Xw[i * Nx + j];
                     Xw[i * Nx + j] = (x <= 0.f) ? 0.f : 0.5f * (x + y);
                 }
             }
@@ -328,16 +344,24 @@ __device__ __forceinline__ SclMonoLoc scl_mono_locate(int v, int a, int amax, in
 }
 
 __device__ __forceinline__ void scl_mono_apply(float* X, int Nx, int p, const float4& w0, const float4& w1, float omt) {
+    // all eight neighbour loads are issued together (a tap with zero weight may lie outside the image: it reads
+    // the pixel itself instead); the sum then runs in tap order over the positive weights only
+    // (operators_pybind11.cc:39-47), un-fused so that it rounds like the reference
+    const float x0 = X[w0.x > 0.f ? p - Nx - 1 : p], x1 = X[w0.y > 0.f ? p - Nx : p];
+    const float x2 = X[w0.z > 0.f ? p - Nx + 1 : p], x3 = X[w0.w > 0.f ? p - 1 : p];
+    const float x4 = X[w1.x > 0.f ? p + 1 : p], x5 = X[w1.y > 0.f ? p + Nx - 1 : p];
+    const float x6 = X[w1.z > 0.f ? p + Nx : p], x7 = X[w1.w > 0.f ? p + Nx + 1 : p];
+    const float cur = X[p];
     float ref = 0.f;
-    if (w0.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx - 1], w0.x));
-    if (w0.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx], w0.y));
-    if (w0.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - Nx + 1], w0.z));
-    if (w0.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p - 1], w0.w));
-    if (w1.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + 1], w1.x));
-    if (w1.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx - 1], w1.y));
-    if (w1.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx], w1.z));
-    if (w1.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(X[p + Nx + 1], w1.w));
-    const float r = __fmul_rn(ref, omt), cur = X[p];
+    if (w0.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(x0, w0.x));
+    if (w0.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(x1, w0.y));
+    if (w0.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(x2, w0.z));
+    if (w0.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(x3, w0.w));
+    if (w1.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(x4, w1.x));
+    if (w1.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(x5, w1.y));
+    if (w1.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(x6, w1.z));
+    if (w1.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(x7, w1.w));
+    const float r = __fmul_rn(ref, omt);
     X[p] = (r < cur) ? r : cur;
 }
 
@@ -379,6 +403,142 @@ __device__ void scl_monotonic_f32(float* X, int Ny, int Nx, int cy, int cx, cons
         }
         scl_mono_sync<NT>();
     }
+}
+
+// ---- single-warp wavefront over a per-centre level list ----------------------
+// The sweep has ~2 max(H,W) + min(H,W) dependent levels with a few dozen pixels each.  The CTA first sorts the
+// image's pixels by level into a list in shared memory (counting sort; the order inside a level is irrelevant,
+// see above), then ONE warp walks the list, 32 pixels per pass, while the other warps wait at a barrier and
+// issue nothing.  The weights of a pass come from wt9 (L2, several hundred cycles away): each lane copies its
+// 32 bytes with cp.async into a ring of SCL_MONO_RING pass slots in shared memory, several passes ahead of
+// their use, so that the dependent chain of a level is shared memory only.
+#define SCL_MAX_LEVELS 480
+#define SCL_MONO_RING 6
+#ifndef SCL_EXP
+#define SCL_EXP 0
+#endif
+struct SclMonoWork {            // views into the scratch (aliases the symmetry step's Z buffer)
+    int* start;                 // [vmax + 3] first list index of each level
+    int* fill;                  // [vmax + 3]
+    unsigned short* list;       // [N] packed (y << 8 | x), level-ordered
+    float4* ring;               // [SCL_MONO_RING][32][2]
+};
+__host__ __device__ inline size_t scl_mono_work_bytes(int N, int vmax) {
+    return (((size_t)8 * (vmax + 3) + 2 * (size_t)N + 15) & ~(size_t)15) + (size_t)SCL_MONO_RING * 32 * 32;
+}
+__device__ __forceinline__ SclMonoWork scl_mono_work(void* base, int N, int vmax) {
+    SclMonoWork w;
+    unsigned char* b = reinterpret_cast<unsigned char*>(base);
+    w.ring = reinterpret_cast<float4*>(b);                               // 16-byte aligned first
+    b += (size_t)SCL_MONO_RING * 32 * 32;
+    w.start = reinterpret_cast<int*>(b);
+    w.fill = w.start + (vmax + 3);
+    w.list = reinterpret_cast<unsigned short*>(w.fill + (vmax + 3));
+    (void)N;
+    return w;
+}
+
+__device__ __forceinline__ int scl_mono_level(int Yo, int Xo) {
+    const int a = abs(Yo), b = abs(Xo);
+    return a > b ? 2 * a + b : 2 * b + a;
+}
+
+// all threads of the CTA; needs Ny, Nx <= 256
+__device__ void scl_mono_build(const SclMonoWork& wk, int Ny, int Nx, int cy, int cx, int vmax) {
+    const int N = Ny * Nx;
+    for (int i = threadIdx.x; i < vmax + 3; i += blockDim.x) wk.start[i] = 0;
+    __syncthreads();
+    const int dyb = blockDim.x / Nx, dxb = blockDim.x - dyb * Nx;      // (y, x) advance of one stride
+    {
+        int y = threadIdx.x / Nx, x = threadIdx.x - y * Nx;
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            const int v = scl_mono_level(y - cy, x - cx);
+            if (v > 0) atomicAdd(&wk.start[v + 1], 1);
+            y += dyb; x += dxb;
+            if (x >= Nx) { x -= Nx; y++; }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        // inclusive scan of the counts (level v is counted at v + 1) -> start[v] = first list index of level v
+        const int n = vmax + 3, per = (n + 31) / 32, lane = threadIdx.x;
+        int sum = 0;
+        for (int i = lane * per; i < min(n, (lane + 1) * per); i++) sum += wk.start[i];
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int y = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        int run = incl - sum;
+        for (int i = lane * per; i < min(n, (lane + 1) * per); i++) {
+            run += wk.start[i];
+            wk.start[i] = run;
+            wk.fill[i] = run;
+        }
+    }
+    __syncthreads();
+    {
+        int y = threadIdx.x / Nx, x = threadIdx.x - y * Nx;
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            const int v = scl_mono_level(y - cy, x - cx);
+            if (v > 0) wk.list[atomicAdd(&wk.fill[v], 1)] = (unsigned short)((y << 8) | x);
+            y += dyb; x += dxb;
+            if (x >= Nx) { x -= Nx; y++; }
+        }
+    }
+    __syncthreads();
+}
+
+// Called by the 32 lanes of ONE warp after scl_mono_build.  Ny, Nx >= 2.
+__device__ void scl_monotonic_f32_warp(float* X, int Ny, int Nx, int cy, int cx, const SclMonoWork& wk,
+                                       const float* __restrict__ wt9, float thresh, int vmax) {
+    const float omt = 1.f - thresh;
+    const int lane = threadIdx.x & 31;
+    const int H2 = 2 * Ny - 1, W2 = 2 * Nx - 1;
+    int cv = 2, cpos = wk.start[2], cend = wk.start[3];           // issue cursor (warp-uniform)
+    // one pass: bit 31 = pass exists, bit 30 = last pass of its level, bit 29 = this lane has a pixel, low bits = p
+    auto issue = [&](int slot) -> unsigned {
+        unsigned m = 0;
+        if (cv <= vmax) {
+            m = 0x80000000u;
+            const int idx = cpos + lane;
+            if (idx < cend) {
+                const int yx = wk.list[idx], y = yx >> 8, x = yx & 255;
+                const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
+                const float* wp = wt9 + ((size_t)((by * 3 + bx) * H2 + (y - cy + Ny - 1)) * W2 + (x - cx + Nx - 1)) * 8;
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(wk.ring + (slot * 32 + lane) * 2);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(dst), "l"(wp));
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(dst + 16), "l"(wp + 4));
+                m |= 0x20000000u | (unsigned)(y * Nx + x);
+            }
+            cpos += 32;
+            if (cpos >= cend) { m |= 0x40000000u; cv++; cpos = wk.start[cv]; cend = wk.start[cv + 1]; }
+        }
+        asm volatile("cp.async.commit_group;\n" ::);
+        return m;
+    };
+    // passes i .. i + RING - 2 are in flight while pass i is processed
+    unsigned meta[SCL_MONO_RING - 1];
+#pragma unroll
+    for (int d = 0; d < SCL_MONO_RING - 1; d++) meta[d] = issue(d);
+    int slot = 0;
+    while (meta[0] & 0x80000000u) {
+        const unsigned m = meta[0];
+#pragma unroll
+        for (int d = 0; d + 1 < SCL_MONO_RING - 1; d++) meta[d] = meta[d + 1];
+        int nslot = slot + SCL_MONO_RING - 1;
+        if (nslot >= SCL_MONO_RING) nslot -= SCL_MONO_RING;
+        meta[SCL_MONO_RING - 2] = issue(nslot);
+        asm volatile("cp.async.wait_group %0;\n" :: "n"(SCL_MONO_RING - 1));
+        if (m & 0x20000000u) {
+            const float4 w0 = wk.ring[(slot * 32 + lane) * 2], w1 = wk.ring[(slot * 32 + lane) * 2 + 1];
+            scl_mono_apply(X, Nx, (int)(m & 0xffffffu), w0, w1, omt);
+        }
+        if (m & 0x40000000u) __syncwarp();
+        slot = (slot + 1 == SCL_MONO_RING) ? 0 : slot + 1;
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::);
 }
 
 template <typename T, bool NEAREST>
