@@ -164,7 +164,7 @@ def run_b200(args):
         __graft_entry__.build()
     if world > 1:
         dist.barrier()
-    from scarlet_b200 import synth
+    from scarlet_b200 import synth, shard
     from scarlet_b200.batch import BlendBatch
 
     cpu = None
@@ -174,7 +174,7 @@ def run_b200(args):
     # ---- inputs: rank r owns blend indices [r*B, (r+1)*B)
     B = args.blends
     t0 = time.perf_counter()
-    data = synth.make_blends(range(rank * B, (rank + 1) * B), C, NY, NX, psf_size=PSF)
+    data = synth.make_blends(shard.weak_range(B, rank), C, NY, NX, psf_size=PSF)
     t_gen = time.perf_counter() - t0
     t0 = time.perf_counter()
     bb = BlendBatch(data["images"], data["psfs"], data["model_psf"], data["centers"], data["bg_rms"],
@@ -235,19 +235,12 @@ def run_b200(args):
     for a in list(bb.host.values()) + list(res.values()):
         if isinstance(a, np.ndarray) and a.nbytes >= 4096:
             cudart.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
-    rec = torch.empty((bb.B, 3), dtype=torch.float32, device="cuda")
-
     def e2e_step():
         bb.upload()
         bb.fit_device(MAX_ITER, E_REL, check_every=args.check_every)
         o = bb.download(morph=True, out=res)
-        if world > 1:       # per-blend result records gathered over NCCL (north_star: NCCL only for results)
-            n = o["n_iter"]
-            rec.copy_(torch.from_numpy(np.stack([n, o["active"], o["logL"][np.arange(bb.B), np.maximum(n - 1, 0)]], 1)
-                                       .astype(np.float32)))
-            allrec = [torch.empty_like(rec) for _ in range(world)]
-            dist.all_gather(allrec, rec)
-        return o
+        # per-blend result records gathered over NCCL (north_star: NCCL only for results)
+        return shard.gather_records(shard.result_records(o, comp_off))
     e2e_step()
     barrier()
     t0 = time.perf_counter()
