@@ -74,7 +74,8 @@ int ensure_globals() {
         CK(cudaMemcpy(g_nfl_even, b.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
     }
     if (!g_attr_done) {
-        CK(cudaFuncSetAttribute(scl_k_forward_adjoint, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_forward_adjoint<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_forward_adjoint<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         const int big = 200 * 1024;
         CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));

@@ -17,10 +17,31 @@
 #pragma once
 #include "fft_smem.cuh"
 
+// 4-point DFT whose inputs 2 and 3 are zero
+__device__ __forceinline__ void dft4_in2(float2& a0, float2& a1, float2& a2, float2& a3) {
+    const float2 x0 = a0, x1 = a1, m = make_float2(x1.y, -x1.x);       // -i * x1
+    a0 = cadd(x0, x1);
+    a1 = cadd(x0, m);
+    a2 = csub(x0, x1);
+    a3 = csub(x0, m);
+}
+// 4-point DFT of which only outputs 0 and 1 are wanted (a2, a3 left undefined)
+__device__ __forceinline__ void dft4_out2(float2& a0, float2& a1, float2& a2, float2& a3) {
+    const float2 s02 = cadd(a0, a2), d02 = csub(a0, a2), s13 = cadd(a1, a3), d13 = csub(a1, a3);
+    a0 = cadd(s02, s13);
+    a1 = cadd(d02, make_float2(d13.y, -d13.x));
+}
+
+// 16-point forward DFT, natural order in and out.
+// IN8: inputs a[8..15] are zero (zero-padded signal); OUT8: only X[0..7] are wanted (cropped result).
+template <bool IN8, bool OUT8>
 __device__ __forceinline__ void dft16(float2 (&a)[16]) {
     // step 1: 4-point DFTs over n1' of x[n0 + 4 n1'] -> y[n0][k0] kept at a[n0 + 4 k0]
 #pragma unroll
-    for (int n0 = 0; n0 < 4; n0++) dft4(a[n0], a[n0 + 4], a[n0 + 8], a[n0 + 12]);
+    for (int n0 = 0; n0 < 4; n0++) {
+        if (IN8) dft4_in2(a[n0], a[n0 + 4], a[n0 + 8], a[n0 + 12]);
+        else dft4(a[n0], a[n0 + 4], a[n0 + 8], a[n0 + 12]);
+    }
     // twiddles w16^(n0*k0)
     const float c1 = 0.92387953251128675613f, s1 = 0.38268343236508977173f, h = 0.70710678118654752440f;
     a[1 + 4] = cmul(a[1 + 4], make_float2(c1, -s1));          // w^1
@@ -34,7 +55,10 @@ __device__ __forceinline__ void dft16(float2 (&a)[16]) {
     a[3 + 12] = cmul(a[3 + 12], make_float2(-c1, s1));        // w^9
     // step 2: 4-point DFTs over n0 -> X[k0 + 4 k1'] at a[4 k0 + k1']
 #pragma unroll
-    for (int k0 = 0; k0 < 4; k0++) dft4(a[4 * k0], a[4 * k0 + 1], a[4 * k0 + 2], a[4 * k0 + 3]);
+    for (int k0 = 0; k0 < 4; k0++) {
+        if (OUT8) dft4_out2(a[4 * k0], a[4 * k0 + 1], a[4 * k0 + 2], a[4 * k0 + 3]);
+        else dft4(a[4 * k0], a[4 * k0 + 1], a[4 * k0 + 2], a[4 * k0 + 3]);
+    }
     // natural order: X[k] sits at a[4 (k & 3) + (k >> 2)]
     float2 b[16];
 #pragma unroll
@@ -58,8 +82,10 @@ __device__ __forceinline__ void fill_twiddles_reg(float2* tw) {
 
 // time -> freq.  v in: x[8*n1 + t]; v out: X[t + 8*s + 16*k2] at v[8*s + k2].
 // All 32 lanes of the warp call together; `line` may be any valid address for lanes whose data is ignored.
+// IN64: x[n] = 0 for n >= 64 (registers 8..15 are ignored).
+template <bool IN64>
 __device__ __forceinline__ void fft128_t2f(float2 (&v)[16], float2* line, int es, int t, const float2* tw) {
-    dft16(v);
+    dft16<IN64, false>(v);
 #pragma unroll
     for (int k1 = 1; k1 < 16; k1++) v[k1] = cmul(v[k1], tw[k1 * 8 + t]);
 #pragma unroll
@@ -82,6 +108,8 @@ __device__ __forceinline__ void fft128_t2f(float2 (&v)[16], float2* line, int es
 }
 
 // freq -> time (same forward-sign DFT).  v in: X[t + 8*s + 16*k2] at v[8*s + k2]; v out: x[8*n1 + t] at v[n1].
+// OUT64: only x[n], n < 64 are wanted (registers 8..15 come back undefined).
+template <bool OUT64>
 __device__ __forceinline__ void fft128_f2t(float2 (&v)[16], float2* line, int es, int t, const float2* tw) {
     {
         float2 lo[8], hi[8];
@@ -105,7 +133,7 @@ __device__ __forceinline__ void fft128_f2t(float2 (&v)[16], float2* line, int es
 #pragma unroll
     for (int k1 = 0; k1 < 16; k1++) v[k1] = line[(8 * k1 + (t ^ (k1 & 7))) * es];
     __syncwarp();
-    dft16(v);
+    dft16<false, OUT64>(v);
 }
 
 // Partner values for the conjugate-symmetry split of a freq-distributed line: r[i] = X[(128 - k) & 127] for the

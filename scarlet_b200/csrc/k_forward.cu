@@ -212,8 +212,10 @@ __device__ __forceinline__ void load_retangle(float2 (&v)[16], const float2* row
 
 // forward column FFT, x D (or conj D), inverse column FFT; result left swapped in rows [0, NR).
 // Dt: transposed kernel spectrum [65][128] (Dt[kx*128 + ky]).
-template <bool CONJ>
-__device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, const float2* __restrict__ Dt, int NR) {
+template <bool HALF>
+__device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, const float2* __restrict__ Dt, int NR,
+                                                 bool conj) {
+    const float cs = conj ? -1.f : 1.f;          // multiply by D or by conj(D)
     const int t = threadIdx.x & 7;
 #pragma unroll 1
     for (int round = 0; round < 2; round++) {
@@ -223,18 +225,18 @@ __device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, 
 #pragma unroll
         for (int n1 = 0; n1 < 16; n1++) {
             const int y = 8 * n1 + t;
-            v[n1] = (y < NR) ? col[y * RS] : make_float2(0.f, 0.f);
+            v[n1] = (y < NR && (!HALF || n1 < 8)) ? col[y * RS] : make_float2(0.f, 0.f);
         }
-        fft128_t2f(v, col, RS, t, tw);
+        fft128_t2f<HALF>(v, col, RS, t, tw);
         if (kx > 0) {
             const float2* Dc = Dt + kx * 128;
 #pragma unroll
             for (int s = 0; s < 2; s++)
 #pragma unroll
                 for (int k2 = 0; k2 < 8; k2++) {
-                    const float2 d = Dc[t + 8 * s + 16 * k2];
-                    const float2 x = v[8 * s + k2];
-                    v[8 * s + k2] = cswap(CONJ ? cmulc(x, d) : cmul(x, d));
+                    float2 d = Dc[t + 8 * s + 16 * k2];
+                    d.y *= cs;
+                    v[8 * s + k2] = cswap(cmul(v[8 * s + k2], d));
                 }
         }
         if (__any_sync(0xffffffffu, kx == 0)) {
@@ -250,16 +252,17 @@ __device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, 
                         const float2 c1 = v[8 * s + k2], c2 = r[8 * s + k2];
                         float2 p0 = make_float2(0.5f * (c1.x + c2.x), 0.5f * (c1.y - c2.y));
                         float2 pn = make_float2(0.5f * (c1.y + c2.y), 0.5f * (c2.x - c1.x));
-                        const float2 d0 = Dt[ky], dn = Dt[64 * 128 + ky];
-                        p0 = CONJ ? cmulc(p0, d0) : cmul(p0, d0);
-                        pn = CONJ ? cmulc(pn, dn) : cmul(pn, dn);
+                        float2 d0 = Dt[ky], dn = Dt[64 * 128 + ky];
+                        d0.y *= cs; dn.y *= cs;
+                        p0 = cmul(p0, d0);
+                        pn = cmul(pn, dn);
                         v[8 * s + k2] = cswap(make_float2(p0.x - pn.y, p0.y + pn.x));
                     }
             }
         }
-        fft128_f2t(v, col, RS, t, tw);
+        fft128_f2t<HALF>(v, col, RS, t, tw);
 #pragma unroll
-        for (int n1 = 0; n1 < 16; n1++) {
+        for (int n1 = 0; n1 < (HALF ? 8 : 16); n1++) {
             const int y = 8 * n1 + t;
             if (y < NR) col[y * RS] = v[n1];
         }
@@ -270,7 +273,9 @@ __device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, 
 
 // grid: (C * n_listed_blends); block: SCL_THREADS; dynamic smem: kFwdSmem (api.cu)
 //   buf [128][65] float2 | tw [256] float2 | dummy line [130] float2 | red [32] double
-extern "C" __global__ void __launch_bounds__(SCL_THREADS, 2)
+// HALF: Nx <= 64 and Ny <= 64 -- the zero-padded halves of every line are pruned from the transforms.
+template <bool HALF>
+__global__ void __launch_bounds__(SCL_THREADS, 2)
 scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const float* __restrict__ S,        // [Ktot, N]
                       const int* __restrict__ comp_off,   // [B+1]
@@ -285,8 +290,8 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       double* __restrict__ gram,          // [B, 8, 8]  rows r = c, c+C, .. of S S^T
                       int C, int Ny, int Nx)
 {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    float2* buf = reinterpret_cast<float2*>(smem_raw);
+    extern __shared__ __align__(16) unsigned char smem_fwd[];
+    float2* buf = reinterpret_cast<float2*>(smem_fwd);
     float2* tw = buf + F * RS;
     float2* dummy = tw + 256;
     double* red = reinterpret_cast<double*>(dummy + LS);
@@ -358,118 +363,113 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
         }
     } else {
         const int jg = grp_row_line();
-        // ---- phase A: render row pairs (ComponentTree.get_model), row FFT, untangle
-        for (int j0 = 0; j0 < NP; j0 += 32) {
-            const int j = j0 + jg;
-            const bool live = j < NP;
-            float2* line = live ? buf + j * LS : dummy;
-            const int y0 = 2 * j, y1 = 2 * j + 1;
-            float2 v[16];
+        // Three row passes share one copy of the code (the unrolled FFT bodies are large; one copy keeps the kernel
+        // inside the instruction cache):
+        //   pass 0: render row pairs (ComponentTree.get_model)            -> row FFT -> columns x D
+        //   pass 1: inverse rows -> R; r = W^2 (R - I), logL              -> row FFT -> columns x conj(D)
+        //   pass 2: inverse rows -> G
+#pragma unroll 1
+        for (int pass = 0; pass < 3; pass++) {
+            for (int j0 = 0; j0 < NP; j0 += 32) {
+                const int j = j0 + jg;
+                const bool live = j < NP;
+                float2* line = live ? buf + j * LS : dummy;
+                const int y0 = 2 * j, y1 = 2 * j + 1;
+                float2 v[16];
+                if (pass > 0) {
+                    load_retangle(v, line, t, live);
+                    fft128_f2t<HALF>(v, line, 1, t, tw);
+                }
+                if (pass == 0) {
 #pragma unroll
-            for (int n1 = 0; n1 < 16; n1++) {
-                const int x = 8 * n1 + t;
-                float m0 = 0.f, m1 = 0.f;
-                if (live && x < Nx) {
-                    float s0[SCL_MAX_COMP], s1[SCL_MAX_COMP];
+                    for (int n1 = (HALF ? 8 : 16); n1 < 16; n1++) v[n1] = make_float2(0.f, 0.f);
 #pragma unroll
-                    for (int k = 0; k < SCL_MAX_COMP; k++) {
-                        const float* Sk = S + (size_t)(k0 + k) * N;
-                        s0[k] = (k < K) ? Sk[y0 * Nx + x] : 0.f;
-                        s1[k] = (k < K && y1 < Ny) ? Sk[y1 * Nx + x] : 0.f;
+                    for (int n1 = 0; n1 < (HALF ? 8 : 16); n1++) {
+                        const int x = 8 * n1 + t;
+                        float m0 = 0.f, m1 = 0.f;
+                        if (live && x < Nx) {
+                            float s0[SCL_MAX_COMP], s1[SCL_MAX_COMP];
+#pragma unroll
+                            for (int k = 0; k < SCL_MAX_COMP; k++) {
+                                const float* Sk = S + (size_t)(k0 + k) * N;
+                                s0[k] = (k < K) ? Sk[y0 * Nx + x] : 0.f;
+                                s1[k] = (k < K && y1 < Ny) ? Sk[y1 * Nx + x] : 0.f;
+                            }
+                            float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;      // S[r0], S[r1] at the two pixels
+#pragma unroll
+                            for (int k = 0; k < SCL_MAX_COMP; k++) {
+                                m0 += sA[k] * s0[k];
+                                m1 += sA[k] * s1[k];
+                                a0 = (k == r0) ? s0[k] : a0; b0 = (k == r0) ? s1[k] : b0;
+                                a1 = (k == r1) ? s0[k] : a1; b1 = (k == r1) ? s1[k] : b1;
+                            }
+#pragma unroll
+                            for (int k = 0; k < SCL_MAX_COMP; k++) {
+                                gr0[k] += a0 * s0[k] + b0 * s1[k];
+                                gr1[k] += a1 * s0[k] + b1 * s1[k];
+                            }
+                        }
+                        v[n1] = make_float2(m0, m1);
                     }
-                    float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;      // S[r0], S[r1] at the two pixels
+                } else if (pass == 1) {
 #pragma unroll
-                    for (int k = 0; k < SCL_MAX_COMP; k++) {
-                        m0 += sA[k] * s0[k];
-                        m1 += sA[k] * s1[k];
-                        a0 = (k == r0) ? s0[k] : a0; b0 = (k == r0) ? s1[k] : b0;
-                        a1 = (k == r1) ? s0[k] : a1; b1 = (k == r1) ? s1[k] : b1;
+                    for (int n1 = (HALF ? 8 : 16); n1 < 16; n1++) v[n1] = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int n1 = 0; n1 < (HALF ? 8 : 16); n1++) {
+                        const int x = 8 * n1 + t;
+                        float o0 = 0.f, o1 = 0.f;
+                        if (live && x < Nx) {
+                            const float rr0 = v[n1].y * inv, rr1 = v[n1].x * inv;       // swapped: (im, re)
+                            const int p0 = y0 * Nx + x, p1 = y1 * Nx + x;
+                            const float w0 = wgt ? wgt[p0] : 1.f;
+                            const float d0 = w0 * (rr0 - img[p0]);
+                            loss += (double)d0 * (double)d0;
+                            o0 = w0 * d0;
+                            if (y1 < Ny) {
+                                const float w1 = wgt ? wgt[p1] : 1.f;
+                                const float d1 = w1 * (rr1 - img[p1]);
+                                loss += (double)d1 * (double)d1;
+                                o1 = w1 * d1;
+                            }
+                        }
+                        v[n1] = make_float2(o0, o1);
                     }
+                } else {
 #pragma unroll
-                    for (int k = 0; k < SCL_MAX_COMP; k++) {
-                        gr0[k] += a0 * s0[k] + b0 * s1[k];
-                        gr1[k] += a1 * s0[k] + b1 * s1[k];
+                    for (int n1 = 0; n1 < (HALF ? 8 : 16); n1++) {
+                        const int x = 8 * n1 + t;
+                        if (live && x < Nx) {
+                            gout[y0 * Nx + x] = v[n1].y * inv;
+                            if (y1 < Ny) gout[y1 * Nx + x] = v[n1].x * inv;
+                        }
                     }
                 }
-                v[n1] = make_float2(m0, m1);
+                if (pass < 2) {
+                    fft128_t2f<HALF>(v, line, 1, t, tw);
+                    untangle_store(v, line, t, live);
+                }
             }
-            fft128_t2f(v, line, 1, t, tw);
-            untangle_store(v, line, t, live);
-        }
-        // Gram rows c and c + C: reduce now so that the accumulators die before the column phase
-        {
+            if (pass == 2) break;
+            if (pass == 0) {
+                // Gram rows c and c + C: reduce now so that the accumulators die before the column phase
 #pragma unroll
-            for (int l = 0; l < SCL_MAX_COMP; l++) {
-                double v0 = warp_sum<double>((double)gr0[l]), v1 = warp_sum<double>((double)gr1[l]);
-                if (lane == 0) { sred[warp][l] = v0; sred[warp][SCL_MAX_COMP + l] = v1; }
+                for (int l = 0; l < SCL_MAX_COMP; l++) {
+                    double v0 = warp_sum<double>((double)gr0[l]), v1 = warp_sum<double>((double)gr1[l]);
+                    if (lane == 0) { sred[warp][l] = v0; sred[warp][SCL_MAX_COMP + l] = v1; }
+                }
+                __syncthreads();
+                if (threadIdx.x < 2 * SCL_MAX_COMP) {
+                    const int l = threadIdx.x & (SCL_MAX_COMP - 1), r = (threadIdx.x < SCL_MAX_COMP) ? r0 : r1;
+                    if (r < K && l < K) {
+                        double v = 0.0;
+                        for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
+                        gram[(size_t)b * 64 + r * 8 + l] = v;
+                    }
+                }
             }
             __syncthreads();
-            if (threadIdx.x < 2 * SCL_MAX_COMP) {
-                const int l = threadIdx.x & (SCL_MAX_COMP - 1), r = (threadIdx.x < SCL_MAX_COMP) ? r0 : r1;
-                if (r < K && l < K) {
-                    double v = 0.0;
-                    for (int w = 0; w < nwarp; w++) v += sred[w][threadIdx.x];
-                    gram[(size_t)b * 64 + r * 8 + l] = v;
-                }
-            }
-        }
-        __syncthreads();
-        // ---- phase B: columns, x D
-        column_phase_reg<false>(buf, tw, Dt, NR);
-        __syncthreads();
-        // ---- phase C: inverse rows -> R; residual r = W^2 (R - I) and logL; forward rows of r
-        for (int j0 = 0; j0 < NP; j0 += 32) {
-            const int j = j0 + jg;
-            const bool live = j < NP;
-            float2* line = live ? buf + j * LS : dummy;
-            const int y0 = 2 * j, y1 = 2 * j + 1;
-            float2 v[16];
-            load_retangle(v, line, t, live);
-            fft128_f2t(v, line, 1, t, tw);
-#pragma unroll
-            for (int n1 = 0; n1 < 16; n1++) {
-                const int x = 8 * n1 + t;
-                float o0 = 0.f, o1 = 0.f;
-                if (live && x < Nx) {
-                    const float r0 = v[n1].y * inv, r1 = v[n1].x * inv;       // swapped: (im, re)
-                    const int p0 = y0 * Nx + x, p1 = y1 * Nx + x;
-                    const float w0 = wgt ? wgt[p0] : 1.f;
-                    const float d0 = w0 * (r0 - img[p0]);
-                    loss += (double)d0 * (double)d0;
-                    o0 = w0 * d0;
-                    if (y1 < Ny) {
-                        const float w1 = wgt ? wgt[p1] : 1.f;
-                        const float d1 = w1 * (r1 - img[p1]);
-                        loss += (double)d1 * (double)d1;
-                        o1 = w1 * d1;
-                    }
-                }
-                v[n1] = make_float2(o0, o1);
-            }
-            fft128_t2f(v, line, 1, t, tw);
-            untangle_store(v, line, t, live);
-        }
-        __syncthreads();
-        // ---- phase D: columns, x conj(D)
-        column_phase_reg<true>(buf, tw, Dt, NR);
-        __syncthreads();
-        // ---- phase E: inverse rows -> G
-        for (int j0 = 0; j0 < NP; j0 += 32) {
-            const int j = j0 + jg;
-            const bool live = j < NP;
-            float2* line = live ? buf + j * LS : dummy;
-            const int y0 = 2 * j, y1 = 2 * j + 1;
-            float2 v[16];
-            load_retangle(v, line, t, live);
-            fft128_f2t(v, line, 1, t, tw);
-#pragma unroll
-            for (int n1 = 0; n1 < 16; n1++) {
-                const int x = 8 * n1 + t;
-                if (live && x < Nx) {
-                    gout[y0 * Nx + x] = v[n1].y * inv;
-                    if (y1 < Ny) gout[y1 * Nx + x] = v[n1].x * inv;
-                }
-            }
+            column_phase_reg<HALF>(buf, tw, Dt, NR, pass == 1);
+            __syncthreads();
         }
     }
     double tot = block_sum<double>(loss, red);
@@ -501,6 +501,11 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
         }
     }
 }
+
+#define SCL_FWD_ARGS const float*, const float*, const int*, const float*, const float*, const float2*, const int*, \
+    const int*, const int*, float*, double*, double*, int, int, int
+template __global__ void scl_k_forward_adjoint<true>(SCL_FWD_ARGS);
+template __global__ void scl_k_forward_adjoint<false>(SCL_FWD_ARGS);
 
 // [n][128][65] -> [n][65][128]; grid: n * 65 blocks of 128 threads
 extern "C" __global__ void scl_k_transpose_spec(const float2* __restrict__ in, float2* __restrict__ out) {
