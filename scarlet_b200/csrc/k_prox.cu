@@ -72,18 +72,28 @@ scl_k_prox(SclProxArgs a)
             float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f; dAc[c] = 0.f; }
-#pragma unroll 4
-            for (int p = threadIdx.x; p < N; p += blockDim.x) {
-                const float s = Sin[p];
-                float d = 0.f;
+            // four pixels per thread and round: all their loads (S and C bands of G) are issued before any use
+            for (int p0 = threadIdx.x; p0 < N; p0 += 4 * blockDim.x) {
+                float sv[4], gv[4][SCL_MAX_BANDS];
 #pragma unroll
-                for (int c = 0; c < SCL_MAX_BANDS; c++)
-                    if (c < C) {
-                        const float g = Gb[(size_t)c * N + p];
-                        d += ak[c] * g;
-                        dAc[c] += g * s;
+                for (int u = 0; u < 4; u++) {
+                    const int p = p0 + u * blockDim.x;
+                    const bool in = p < N;
+                    sv[u] = in ? Sin[p] : 0.f;
+#pragma unroll
+                    for (int c = 0; c < SCL_MAX_BANDS; c++) gv[u][c] = (in && c < C) ? Gb[(size_t)c * N + p] : 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int p = p0 + u * blockDim.x;
+                    float d = 0.f;
+#pragma unroll
+                    for (int c = 0; c < SCL_MAX_BANDS; c++) {
+                        d += ak[c] * gv[u][c];
+                        dAc[c] += gv[u][c] * sv[u];
                     }
-                X[p] = fixm ? s : s - step_morph * d;
+                    if (p < N) X[p] = fixm ? sv[u] : sv[u] - step_morph * d;
+                }
             }
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) {
@@ -172,14 +182,21 @@ scl_k_prox(SclProxArgs a)
     // write back + convergence sums (blend.py:160-174)
     double d2 = 0.0, n2 = 0.0;
     float* Sout = a.S + (size_t)k * N;
-#pragma unroll 4
-    for (int p = threadIdx.x; p < N; p += blockDim.x) {
-        float v = constrained ? X[p] / norm : X[p];
-        float old = Sout[p];
-        double df = (double)old - (double)v;
-        d2 += df * df;
-        n2 += (double)v * (double)v;
-        Sout[p] = v;
+    for (int p0 = threadIdx.x; p0 < N; p0 += 8 * blockDim.x) {
+        float old[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) { const int p = p0 + u * blockDim.x; old[u] = (p < N) ? Sout[p] : 0.f; }
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const int p = p0 + u * blockDim.x;
+            if (p < N) {
+                const float v = constrained ? X[p] / norm : X[p];
+                const double df = (double)old[u] - (double)v;
+                d2 += df * df;
+                n2 += (double)v * (double)v;
+                Sout[p] = v;
+            }
+        }
     }
     d2 = block_sum<double>(d2, red);
     n2 = block_sum<double>(n2, red);
