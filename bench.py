@@ -178,7 +178,7 @@ def run_b200(args):
     t_gen = time.perf_counter() - t0
     t0 = time.perf_counter()
     bb = BlendBatch(data["images"], data["psfs"], data["model_psf"], data["centers"], data["bg_rms"],
-                    weights=data["weights"])
+                    weights=data["weights"], streams=args.streams)
     t_init = time.perf_counter() - t0
     bb.snapshot()
     comp_off = bb.host["comp_off"]
@@ -252,10 +252,11 @@ def run_b200(args):
                d2h_bytes_per_step=int(allsum(float(bb.d2h_bytes))), ms_per_step=e2e_s * 1e3 / args.steps)
 
     # ---- roofline of each kernel: fixed-iteration pass (e_rel = 0: every blend active in every launch)
+    # (chunked batch: one chunk after another, so a "launch" below is the chunk launches of one iteration together)
     bb.restore()
-    bb.fit_device(8, 0.0, check_every=1000)
+    bb.fit_device(8, 0.0, check_every=1000, serial=True)
     bb.restore()
-    fx = bb.fit_device(args.roofline_iters, 0.0, check_every=1000, profile=True)
+    fx = bb.fit_device(args.roofline_iters, 0.0, check_every=1000, profile=True, serial=True)
     per_launch, it_bytes = alg_bytes(comp_off)
     names = ["scl_k_forward_adjoint", "scl_k_lipschitz", "scl_k_prox", "scl_k_converge"]
     kernels = []
@@ -286,6 +287,7 @@ def run_b200(args):
                     config=dict(workload=WORKLOAD, blends_per_gpu=int(bb.B), components_per_gpu=int(bb.K),
                                 max_iter=MAX_ITER, e_rel=E_REL, mean_iters_per_blend=iters_total / blends_total,
                                 l2="inputs per GPU (%.1f GB) exceed the 126 MB L2" % (bb.h2d_bytes / 1e9),
+                                streams_per_gpu=args.streams,
                                 sharding="blend-parallel, rank r owns blends [r*B,(r+1)*B), no data-path collective",
                                 input_gen_s=t_gen, source_init_s=t_init, failed_sources=bb.n_failed),
                     pgm_iters_per_sec=iters_total * args.steps / (ms / 1e3),
@@ -328,6 +330,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--blends", type=int, default=10000, help="blends per GPU")
     ap.add_argument("--check-every", type=int, default=8)
+    ap.add_argument("--streams", type=int, default=4, help="independently driven chunks per GPU (BlendBatch streams=)")
     ap.add_argument("--roofline-iters", type=int, default=40)
     ap.add_argument("--ref-per-worker", type=int, default=6)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

@@ -37,6 +37,10 @@ extern "C" {
 int scl_version(void);
 const char* scl_last_error(void);
 int scl_device_count(void);
+/* A CUDA stream for the `void* stream` arguments below (for callers without their own CUDA binding, e.g. ctypes).
+ * Blocking flavour: ordered against the legacy default stream, so events recorded there bracket its work. */
+int scl_stream_create(void** stream);
+int scl_stream_destroy(void* stream);
 
 /* ---- operator tables --------------------------------------------------------------
  * Monotonicity weights depend only on the pixel's offset from the peak (plus the image

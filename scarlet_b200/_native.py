@@ -67,6 +67,18 @@ def require_device():
         raise RuntimeError("scarlet_b200 needs a CUDA device (no CPU fallback)")
 
 
+def stream_create():
+    """A CUDA stream handle (int) for the `stream=` arguments of this module."""
+    s = c_void_p()
+    _check(lib().scl_stream_create(ctypes.byref(s)))
+    return s.value
+
+
+def stream_destroy(stream):
+    if stream:
+        _check(lib().scl_stream_destroy(c_void_p(stream)))
+
+
 def _p(a):
     return None if a is None else a.ctypes.data_as(c_void_p)
 

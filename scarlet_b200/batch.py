@@ -5,6 +5,8 @@ point for BASELINE configs 3-4: the scene catalogue goes in as arrays, every sou
 `ExtendedSource.__init__` would (source.py:139-180,444-492) with the array operators batched on the device,
 and `fit` runs `Blend.fit` for all blends in one launch sequence through the C ABI.
 """
+from concurrent.futures import ThreadPoolExecutor
+
 import numpy as np
 
 from . import _native, fft
@@ -19,6 +21,108 @@ class _Images:
         self.images = images
 
 
+_PER_COMP = ("sed", "morph", "cflags", "center", "shift", "conv")
+_PER_BLEND = ("images", "weights", "cw_idx", "it0", "prev_loss")
+
+
+class _Chunks:
+    """The same interface as `_native.Batch`, over contiguous blend ranges that each own a `scl_batch` handle and a
+    CUDA stream and are driven by one host thread each (the C calls release the GIL).  Blends are independent
+    (SURVEY 8e), so the chunks never talk; running them side by side lets one chunk's kernels fill the SMs another
+    leaves idle (tail waves, the thin per-blend kernels, the long tail of slowly converging blends) and overlaps
+    one chunk's host<->device copies with another's iterations."""
+
+    def __init__(self, n, host):
+        self.C, self.Ny, self.Nx = host["C"], host["Ny"], host["Nx"]
+        off = np.asarray(host["comp_off"])
+        B = len(off) - 1
+        n = max(1, min(int(n), B))
+        # blend boundaries giving every chunk about the same number of components
+        cuts = np.searchsorted(off, off[-1] * np.arange(1, n) / n)
+        self.bounds = np.unique(np.concatenate([[0], cuts, [B]])).astype(int)
+        self.koff = off[self.bounds].astype(int)
+        self.streams = [_native.stream_create() for _ in range(len(self.bounds) - 1)]
+        self.parts = [_native.Batch(stream=s, **self._slice(host, i)) for i, s in enumerate(self.streams)]
+        self.pool = ThreadPoolExecutor(len(self.parts))
+        self.B, self.K = B, int(off[-1])
+        self.max_iter = 0
+        self.d2h_bytes = 0
+
+    def _slice(self, a, i):
+        """Chunk i's views of batch-wide arrays (dict keyed like the Batch constructor / download result)."""
+        b0, b1 = self.bounds[i], self.bounds[i + 1]
+        k0, k1 = self.koff[i], self.koff[i + 1]
+        out = {}
+        for key, v in a.items():
+            if v is None or key in ("C", "Ny", "Nx", "kernel_spec", "cw"):
+                out[key] = v
+            elif key == "comp_off":
+                out[key] = (np.asarray(v[b0:b1 + 1]) - k0).astype(np.int32)
+            elif key == "ker_idx":
+                out[key] = v[b0 * self.C:b1 * self.C]
+            elif key in _PER_COMP:
+                out[key] = v[k0:k1]
+            else:                                   # per blend: images, weights, cw_idx, it0, prev_loss, n_iter, ...
+                out[key] = v[b0:b1]
+        return out
+
+    def _map(self, fn):
+        return list(self.pool.map(fn, range(len(self.parts))))
+
+    @property
+    def h2d_bytes(self):
+        return sum(p.h2d_bytes for p in self.parts)
+
+    def upload(self, **host):
+        self._map(lambda i: self.parts[i].upload(**{k: v for k, v in self._slice(host, i).items()
+                                                    if k not in ("C", "Ny", "Nx")}))
+
+    def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False, serial=False):
+        """`serial=True` runs the chunks one after another (isolated per-kernel timings)."""
+        run = (lambda i: self.parts[i].fit(max_iter, e_rel, approximate_L, check_every, profile))
+        infos = [run(i) for i in range(len(self.parts))] if serial else self._map(run)
+        self.max_iter = int(max_iter)
+        agg = sum if serial else max
+        return dict(device_ms=agg(r["device_ms"] for r in infos), steps=max(r["steps"] for r in infos),
+                    kernel_ms=[sum(r["kernel_ms"][j] for r in infos) for j in range(4)],
+                    launches=sum(r["launches"] for r in infos))
+
+    def constrain(self):
+        self._map(lambda i: self.parts[i].constrain())
+
+    def snapshot(self):
+        self._map(lambda i: self.parts[i].snapshot())
+
+    def restore(self):
+        self._map(lambda i: self.parts[i].restore())
+
+    def phase_clocks(self, enable=True):
+        return [sum(v) for v in zip(*[p.phase_clocks(enable) for p in self.parts])]
+
+    alloc_results = _native.Batch.alloc_results
+
+    def download(self, morph=True, out=None):
+        if out is None:
+            out = self.alloc_results(self.max_iter, morph)
+        self._map(lambda i: self.parts[i].download(morph=morph, out=self._slice(out, i)))
+        self.d2h_bytes = sum(p.d2h_bytes for p in self.parts)
+        return out
+
+    def close(self):
+        for p in self.parts:
+            p.close()
+        for s in self.streams:
+            _native.stream_destroy(s)
+        self.parts, self.streams = [], []
+        self.pool.shutdown()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 class BlendBatch:
     """B blends sharing (C, Ny, Nx), one set of band PSFs and one model PSF.
 
@@ -29,10 +133,11 @@ class BlendBatch:
     Sources whose detection coadd has no pixel above the noise cut raise SourceInitError in the reference
     (source.py:171-173); here they are dropped and counted in `n_failed`; blends left without a source are
     dropped too (`kept` lists the surviving blend indices).
+    streams > 1 splits the batch into that many independently driven chunks, one CUDA stream each (`_Chunks`).
     """
 
     def __init__(self, images, psfs, model_psf, centers, bg_rms, weights=None, thresh=1.0,
-                 symmetric=True, monotonic=True, stream=None):
+                 symmetric=True, monotonic=True, stream=None, streams=1):
         _native.require_device()
         images = np.ascontiguousarray(images, dtype=np.float32)
         B, C, Ny, Nx = images.shape
@@ -94,7 +199,7 @@ class BlendBatch:
             it0=np.zeros(Bk, np.int32), prev_loss=np.zeros(Bk, np.float64))
         self.B, self.K = Bk, K
         self.mse = [[] for _ in range(Bk)]
-        self._dev = _native.Batch(stream=stream, **self.host)
+        self._dev = _Chunks(streams, self.host) if streams > 1 else _native.Batch(stream=stream, **self.host)
         # first constraint pass, it = 0 (source.py:492)
         self._dev.constrain()
         self._pull(self._dev.download())
@@ -117,8 +222,11 @@ class BlendBatch:
         """Host state -> device (what a fresh `fit` on host-resident blends costs)."""
         self._dev.upload(**{k: v for k, v in self.host.items() if k not in ("C", "Ny", "Nx")})
 
-    def fit_device(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False):
-        """The loop only, on the state already in HBM; returns the timing dict of _native.Batch.fit."""
+    def fit_device(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False, serial=False):
+        """The loop only, on the state already in HBM; returns the timing dict of _native.Batch.fit.
+        `serial` (chunked batches only): one chunk after another instead of side by side."""
+        if isinstance(self._dev, _Chunks):
+            return self._dev.fit(max_iter, e_rel, approximate_L, check_every, profile, serial)
         return self._dev.fit(max_iter, e_rel, approximate_L, check_every, profile)
 
     def download(self, morph=True, out=None):

@@ -164,6 +164,18 @@ int scl_device_count(void) {
     return n;
 }
 
+int scl_stream_create(void** stream) {
+    if (!stream) return fail(SCL_E_ARG, "null stream pointer%s%s");
+    cudaStream_t s;
+    CK(cudaStreamCreate(&s));
+    *stream = (void*)s;
+    return SCL_OK;
+}
+int scl_stream_destroy(void* stream) {
+    if (stream) CK(cudaStreamDestroy((cudaStream_t)stream));
+    return SCL_OK;
+}
+
 int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab) {
     int rc = check_shape(Ny, Nx);
     if (rc) return rc;

@@ -37,6 +37,51 @@ struct SclProxArgs {
 
 // dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
 // block: SCL_PROX_THREADS
+// Gradient step of one component over its N pixels (the band count is a template parameter so that the band
+// loops unroll without predicates and every load address is one 64-bit add):
+//   X[p] = S[p] - step_morph * sum_c A[c] G[c][p]   (S[p] if fixm),   dAc[c] += sum_p G[c][p] S[p]
+// Four pixels per thread and round: all their loads (S and CC bands of G) are issued before any use.
+template <int CC>
+__device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, const float* __restrict__ Gb, float* X, int N,
+                                              const float (&ak)[SCL_MAX_BANDS], float (&dAc)[SCL_MAX_BANDS],
+                                              bool fixm, float step_morph) {
+    constexpr int PX = 4;
+    const int nt = blockDim.x;
+    int p0 = threadIdx.x;
+    for (; p0 + (PX - 1) * nt < N; p0 += PX * nt) {
+        float sv[PX], gv[PX][CC];
+#pragma unroll
+        for (int u = 0; u < PX; u++) {
+            const float* gp = Gb + (p0 + u * nt);
+            sv[u] = Sin[p0 + u * nt];
+#pragma unroll
+            for (int c = 0; c < CC; c++) gv[u][c] = gp[c * N];
+        }
+#pragma unroll
+        for (int u = 0; u < PX; u++) {
+            float d = 0.f;
+#pragma unroll
+            for (int c = 0; c < CC; c++) {
+                d += ak[c] * gv[u][c];
+                dAc[c] += gv[u][c] * sv[u];
+            }
+            X[p0 + u * nt] = fixm ? sv[u] : sv[u] - step_morph * d;
+        }
+    }
+    for (; p0 < N; p0 += nt) {
+        const float s = Sin[p0];
+        float g[CC], d = 0.f;
+#pragma unroll
+        for (int c = 0; c < CC; c++) g[c] = Gb[c * N + p0];
+#pragma unroll
+        for (int c = 0; c < CC; c++) {
+            d += ak[c] * g[c];
+            dAc[c] += g[c] * s;
+        }
+        X[p0] = fixm ? s : s - step_morph * d;
+    }
+}
+
 extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
 scl_k_prox(SclProxArgs a)
 {
@@ -65,35 +110,18 @@ scl_k_prox(SclProxArgs a)
     __shared__ float sAnew[SCL_MAX_BANDS];
     {
         const float* Sin = a.S + (size_t)k * N;
-        if (a.G) {
+        if (a.G && !(SCL_EXP & 16)) {
             const bool fixm = fl & SCL_F_FIX_MORPH;
             const float step_morph = 1.0f / a.lips[2 * b + 1];
             const float* Gb = a.G + (size_t)b * C * N;
             float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f; dAc[c] = 0.f; }
-            // four pixels per thread and round: all their loads (S and C bands of G) are issued before any use
-            for (int p0 = threadIdx.x; p0 < N; p0 += 4 * blockDim.x) {
-                float sv[4], gv[4][SCL_MAX_BANDS];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const int p = p0 + u * blockDim.x;
-                    const bool in = p < N;
-                    sv[u] = in ? Sin[p] : 0.f;
-#pragma unroll
-                    for (int c = 0; c < SCL_MAX_BANDS; c++) gv[u][c] = (in && c < C) ? Gb[(size_t)c * N + p] : 0.f;
-                }
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const int p = p0 + u * blockDim.x;
-                    float d = 0.f;
-#pragma unroll
-                    for (int c = 0; c < SCL_MAX_BANDS; c++) {
-                        d += ak[c] * gv[u][c];
-                        dAc[c] += gv[u][c] * sv[u];
-                    }
-                    if (p < N) X[p] = fixm ? sv[u] : sv[u] - step_morph * d;
-                }
+            switch (C) {
+#define SCL_STEP_CASE(CC) case CC: scl_step_loop<CC>(Sin, Gb, X, N, ak, dAc, fixm, step_morph); break;
+                SCL_STEP_CASE(1) SCL_STEP_CASE(2) SCL_STEP_CASE(3) SCL_STEP_CASE(4)
+                SCL_STEP_CASE(5) SCL_STEP_CASE(6) SCL_STEP_CASE(7) SCL_STEP_CASE(8)
+#undef SCL_STEP_CASE
             }
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) {

@@ -22,6 +22,6 @@ if os.environ.get("SCL_PHASES"):
     clk = bb._dev.phase_clocks(False)
     tot = sum(clk) or 1
     print("K3 phase clocks per CTA: " + ", ".join("%s %.0f (%.0f%%)" % (n, c / (bb.K * info["steps"]), 100 * c / tot) for n, c in
-          zip(["step", "centre+symmetry", "list", "sweep", "finish"], clk)))
+          zip(["step", "centre+symmetry", "list", "sweep", "finish", "x5", "x6", "x7"], clk)))
 print("B=%d K=%d iters=%d device_ms=%.3f kernel_ms/launch=%s" % (
     bb.B, bb.K, info["steps"], info["device_ms"], [round(v / info["steps"], 4) for v in info["kernel_ms"]]))
