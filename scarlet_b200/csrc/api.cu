@@ -50,7 +50,13 @@ int next_fast_len(int target) {     // smallest 2^a 3^b 5^c >= target (scipy.fft
 struct Tables {
     float* wtab = nullptr;       // [9][(2Ny-1)(2Nx-1)][8]
     double* ctab = nullptr;      // [(2Ny-1)(2Nx-1)][8]
+    unsigned* plist = nullptr;   // sweep plans of every centre (prox_dev.cuh), 32 entries per pass
+    unsigned* pfirst = nullptr;  // [N + 1] first pass of each centre
+    int pbits = 0;               // 0: no plan (shape too large): generic monotonic path
+    SclMonoPlan plan() const { SclMonoPlan p; p.list = plist; p.first = pfirst; p.pbits = pbits; return p; }
+    void release() { cudaFree(wtab); cudaFree(ctab); cudaFree(plist); cudaFree(pfirst); }
 };
+constexpr size_t kPlanBudget = (size_t)768 << 20;    // bytes of sweep plans per shape
 std::mutex g_mu;
 std::map<std::pair<int, int>, Tables> g_tables;
 int* g_nfl = nullptr;        // device [1024]
@@ -89,29 +95,6 @@ int ensure_globals() {
     return SCL_OK;
 }
 
-int get_tables(int Ny, int Nx, Tables* t) {
-    std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_tables.find({Ny, Nx});
-    if (it == g_tables.end())
-        return fail(SCL_E_ARG, "no monotonic tables registered for this shape (call scl_set_monotonic_tables)%s%s");
-    *t = it->second;
-    return SCL_OK;
-}
-
-size_t prox_smem(int Ny, int Nx) {
-    // X [N] (rounded to 16 bytes) | Z [Ny][(Nx+3)&~3] | tables
-    int mx = Ny > Nx ? Ny : Nx;
-    size_t n4 = ((size_t)Ny * Nx + 3) & ~(size_t)3;
-    return (n4 + (size_t)Ny * ((Nx + 3) & ~3) + 3 * (2 * mx - 1) + 2 * Nx + 32) * sizeof(float);
-}
-
-int check_shape(int Ny, int Nx) {
-    if (Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "empty image shape%s%s");
-    if (prox_smem(Ny, Nx) > 200 * 1024 || 2 * Ny + 10 >= kNflN || 2 * Nx + 10 >= kNflN)
-        return fail(SCL_E_LIMIT, "image shape exceeds the shared-memory resident limit%s%s");
-    return SCL_OK;
-}
-
 template <typename T>
 struct DevBuf {
     T* p = nullptr;
@@ -124,6 +107,64 @@ struct DevBuf {
     cudaError_t up(const T* h, cudaStream_t s) { return cudaMemcpyAsync(p, h, n * sizeof(T), cudaMemcpyHostToDevice, s); }
     cudaError_t down(T* h, cudaStream_t s) const { return cudaMemcpyAsync(h, p, n * sizeof(T), cudaMemcpyDeviceToHost, s); }
 };
+
+// Sweep plans of every centre of the shape (prox_dev.cuh "precomputed per-centre plan"): count, prefix on the
+// host, emit.  Shapes whose plans would not fit the entry format or the budget keep pbits = 0.
+int build_plans(int Ny, int Nx, Tables* t) {
+    const int N = Ny * Nx;
+    if (Ny < 2 || Nx < 2 || Ny > 256 || Nx > 256) return SCL_OK;
+    int pbits = 1;
+    while ((1 << pbits) < N) pbits++;
+    const unsigned long long rows = 9ull * (2 * Ny - 1) * (2 * Nx - 1);
+    if (rows >= (1ull << (32 - pbits)) - 1) return SCL_OK;
+    const int mx = Ny > Nx ? Ny : Nx;
+    const size_t smem = scl_mono_work_bytes(N, 3 * mx) + (3 * mx + 3) * sizeof(int) + 16;
+    CK(cudaFuncSetAttribute(scl_k_mono_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    DevBuf<unsigned> cnt;
+    CK(cnt.alloc(N));
+    scl_k_mono_plan<<<N, SCL_THREADS, smem>>>(Ny, Nx, pbits, cnt.p, nullptr, nullptr);
+    CK(cudaGetLastError());
+    std::vector<unsigned> h(N), first(N + 1);
+    CK(cudaMemcpy(h.data(), cnt.p, N * sizeof(unsigned), cudaMemcpyDeviceToHost));
+    unsigned long long run = 0;
+    for (int i = 0; i < N; i++) { first[i] = (unsigned)run; run += h[i]; }
+    first[N] = (unsigned)run;
+    if (run * 128 > kPlanBudget || run >= (1ull << 32)) return SCL_OK;
+    CK(cudaMalloc(&t->pfirst, (N + 1) * sizeof(unsigned)));
+    CK(cudaMalloc(&t->plist, (size_t)(run ? run : 1) * 128));
+    CK(cudaMemcpy(t->pfirst, first.data(), (N + 1) * sizeof(unsigned), cudaMemcpyHostToDevice));
+    scl_k_mono_plan<<<N, SCL_THREADS, smem>>>(Ny, Nx, pbits, nullptr, t->pfirst, t->plist);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    t->pbits = pbits;
+    return SCL_OK;
+}
+
+int get_tables(int Ny, int Nx, Tables* t) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_tables.find({Ny, Nx});
+    if (it == g_tables.end())
+        return fail(SCL_E_ARG, "no monotonic tables registered for this shape (call scl_set_monotonic_tables)%s%s");
+    *t = it->second;
+    return SCL_OK;
+}
+
+size_t prox_smem(int Ny, int Nx) {
+    // pad [(Nx+4)&~3] | X [N] (rounded to 16 bytes) | Z [Ny][(Nx+3)&~3] | tables; Z + tables >= SCL_MONO_STREAM_BYTES
+    int mx = Ny > Nx ? Ny : Nx;
+    size_t n4 = ((size_t)Ny * Nx + 3) & ~(size_t)3;
+    size_t zt = ((size_t)Ny * ((Nx + 3) & ~3) + 3 * (2 * mx - 1) + 2 * Nx + 32) * sizeof(float);
+    if (zt < SCL_MONO_STREAM_BYTES) zt = SCL_MONO_STREAM_BYTES;
+    return (((Nx + 4) & ~3) + n4) * sizeof(float) + zt;
+}
+
+int check_shape(int Ny, int Nx) {
+    if (Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "empty image shape%s%s");
+    if (prox_smem(Ny, Nx) > 200 * 1024 || 2 * Ny + 10 >= kNflN || 2 * Nx + 10 >= kNflN)
+        return fail(SCL_E_LIMIT, "image shape exceeds the shared-memory resident limit%s%s");
+    return SCL_OK;
+}
+
 
 template <typename T, bool NEAREST>
 static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T thresh, void* stream) {
@@ -145,7 +186,8 @@ static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T 
     CK(dc.alloc(2 * (size_t)n));
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
-    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T) + 16 + scl_mono_work_bytes((int)N, 3 * (Ny > Nx ? Ny : Nx)), s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab);
+    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T) + (Nx + 1) * sizeof(T) + 32 + SCL_MONO_STREAM_BYTES, s>>>(
+        dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan());
     CK(cudaGetLastError());
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));
@@ -186,9 +228,10 @@ int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ct
     CK(cudaMalloc(&t.ctab, n * sizeof(double)));
     CK(cudaMemcpy(t.wtab, wtab, 9 * n * sizeof(float), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(t.ctab, ctab, n * sizeof(double), cudaMemcpyHostToDevice));
+    if ((rc = build_plans(Ny, Nx, &t))) { t.release(); return rc; }
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_tables.find({Ny, Nx});
-    if (it != g_tables.end()) { cudaFree(it->second.wtab); cudaFree(it->second.ctab); }
+    if (it != g_tables.end()) it->second.release();
     g_tables[{Ny, Nx}] = t;
     return SCL_OK;
 }

@@ -27,6 +27,7 @@ struct SclProxArgs {
     const int* cw_idx;        // [B]
     const float* wtab;        // monotonic tables (see prox_dev.cuh)
     const double* ctab;
+    SclMonoPlan plan;         // per-centre sweep plans of this shape (pbits == 0: none)
     const int* nfl;           // next_fast_len tables
     const int* nfl_even;
     int C, Ny, Nx, ph, pw, step;
@@ -90,7 +91,7 @@ scl_k_prox(SclProxArgs a)
     const int b = a.comp_blend[k];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* X = smem_f;
+    float* X = smem_f + ((Nx + 4) & ~3);        // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
     float* Z = X + ((N + 3) & ~3);
     float* tab = Z + Ny * ((Nx + 3) & ~3);
     __shared__ double red[32];
@@ -169,14 +170,14 @@ scl_k_prox(SclProxArgs a)
         }
         SCL_PHASE(1);  // max_pixel, centroid, symmetry
         if (fl & SCL_F_MONOTONIC) {
-            const int ay = max(sc[0], Ny - 1 - sc[0]), ax = max(sc[1], Nx - 1 - sc[1]);
-            const int vmax = 2 * max(ay, ax) + min(ay, ax);
-            if (Ny >= 2 && Nx >= 2 && Ny <= 256 && Nx <= 256 &&
-                scl_mono_work_bytes(N, vmax) <= (size_t)Ny * ((Nx + 3) & ~3) * sizeof(float)) {
-                const SclMonoWork wk = scl_mono_work(Z, N, vmax);           // Z is dead after the symmetry step
-                scl_mono_build(wk, Ny, Nx, sc[0], sc[1], vmax);
-                SCL_PHASE(2);  // level list
-                if (threadIdx.x < 32) scl_monotonic_f32_warp(X, Ny, Nx, sc[0], sc[1], wk, a.wtab, 0.f, vmax);
+            if (a.plan.pbits) {
+                // Z and the tables are dead after the symmetry step: scratch of the streamed sweep
+                if (threadIdx.x < 32) {
+                    const int ctr = sc[0] * Nx + sc[1];
+                    const unsigned f0 = a.plan.first[ctr], f1 = a.plan.first[ctr + 1];
+                    scl_monotonic_f32_stream(X, Nx, a.plan.list + (size_t)f0 * 32, (int)(f1 - f0), a.plan.pbits,
+                                             a.wtab, 0.f, Z);
+                }
                 __syncthreads();
             } else {
                 scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
@@ -313,32 +314,54 @@ scl_k_compact(const int* __restrict__ active, const int* __restrict__ comp_off, 
 // ---------------------------------------------------------------- standalone operators
 // (drop-in device paths for scarlet.operator.prox_* / operators_pybind11.*)
 // one CTA per image; images [n, Ny, Nx] float32 in global memory, updated in place.
+// dynamic smem: front pad (scl_mono_load) | image [N] T | SCL_MONO_STREAM_BYTES
 template <typename T, bool NEAREST>
 __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, int Nx, T thresh,
-                const float* __restrict__ wtab, const double* __restrict__ ctab)
+                const float* __restrict__ wtab, const double* __restrict__ ctab, SclMonoPlan plan)
 {
     extern __shared__ __align__(16) unsigned char smem_b[];
     const int N = Ny * Nx;
-    T* X = reinterpret_cast<T*>(smem_b);
+    const size_t pad = (((size_t)Nx + 1) * sizeof(T) + 15) & ~(size_t)15;
+    T* X = reinterpret_cast<T*>(smem_b + pad);
     T* g = imgs + (size_t)blockIdx.x * N;
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
     const int cy = centers[2 * blockIdx.x], cx = centers[2 * blockIdx.x + 1];
-    const int vmax = 2 * max(max(cy, Ny - 1 - cy), max(cx, Nx - 1 - cx)) + min(max(cy, Ny - 1 - cy), max(cx, Nx - 1 - cx));
-    if (sizeof(T) == 4 && !NEAREST && Ny >= 2 && Nx >= 2 && Ny <= 256 && Nx <= 256) {
-        // dynamic smem: image [N] T, then the level-list scratch
-        const SclMonoWork wk = scl_mono_work(smem_b + (((size_t)N * sizeof(T) + 15) & ~(size_t)15), N, vmax);
-        scl_mono_build(wk, Ny, Nx, cy, cx, vmax);
-        if (threadIdx.x < 32) scl_monotonic_f32_warp(reinterpret_cast<float*>(X), Ny, Nx, cy, cx, wk, wtab, (float)thresh, vmax);
+    if (sizeof(T) == 4 && !NEAREST && plan.pbits) {
+        if (threadIdx.x < 32) {
+            const unsigned f0 = plan.first[cy * Nx + cx], f1 = plan.first[cy * Nx + cx + 1];
+            scl_monotonic_f32_stream(reinterpret_cast<float*>(X), Nx, plan.list + (size_t)f0 * 32, (int)(f1 - f0),
+                                     plan.pbits, wtab, (float)thresh,
+                                     smem_b + pad + (((size_t)N * sizeof(T) + 15) & ~(size_t)15));
+        }
         __syncthreads();
     } else
-        scl_monotonic<T, NEAREST>(X, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
+        scl_monotonic<T, NEAREST>(X, Ny, Nx, cy, cx, wtab, ctab, thresh);
     for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
 }
-template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*);
-template __global__ void scl_k_monotonic<double, false>(double*, const int*, int, int, double, const float*, const double*);
-template __global__ void scl_k_monotonic<double, true>(double*, const int*, int, int, double, const float*, const double*);
+template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*, SclMonoPlan);
+template __global__ void scl_k_monotonic<double, false>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan);
+template __global__ void scl_k_monotonic<double, true>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan);
+
+// Plan builder (see prox_dev.cuh): one CTA per centre c = cy * Nx + cx.  With list == nullptr only the number of
+// passes is written (npass[c]); otherwise the passes themselves, at first[c].
+// dynamic smem: scl_mono_work_bytes(N, vmax_max) + (vmax_max + 3) ints
+extern "C" __global__ void __launch_bounds__(SCL_THREADS)
+scl_k_mono_plan(int Ny, int Nx, int pbits, unsigned* __restrict__ npass, const unsigned* __restrict__ first,
+                unsigned* __restrict__ list)
+{
+    extern __shared__ __align__(16) unsigned char smem_p[];
+    const int N = Ny * Nx, cy = blockIdx.x / Nx, cx = blockIdx.x % Nx;
+    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
+    const int vmax = 2 * max(ay, ax) + min(ay, ax);
+    const SclMonoWork wk = scl_mono_work(smem_p, N, vmax);
+    int* pbase = reinterpret_cast<int*>(smem_p + scl_mono_work_bytes(N, vmax));
+    scl_mono_build(wk, Ny, Nx, cy, cx, vmax);
+    const int total = scl_mono_emit(wk, Ny, Nx, cy, cx, vmax, pbits, pbase,
+                                    list ? list + (size_t)first[blockIdx.x] * 32 : nullptr);
+    if (npass && threadIdx.x == 0) npass[blockIdx.x] = (unsigned)total;
+}
 
 // mode: 0 = kspace (shift required), 1 = soft(strength), 2 = sdss
 extern "C" __global__ void __launch_bounds__(SCL_THREADS)

@@ -322,115 +322,69 @@ __device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int 
 //   bt = by*3 + bx, by = 0 interior / 1 first row / 2 last row (bx likewise), built on the host in f64 with the
 //   reference's formula and rounded to f32 (operators_pybind11.cc:82-83) -- no arithmetic on weights here.
 // NT threads (tid = 0..NT-1, all of them must call) sweep the levels; `sync` separates levels.
-struct SclMonoLoc { int p; int ti; bool ok; };
-
-__device__ __forceinline__ SclMonoLoc scl_mono_locate(int v, int a, int amax, int oct, int Ny, int Nx, int cy, int cx) {
-    SclMonoLoc r;
-    r.ok = false; r.p = 0; r.ti = 0;
-    if (a > amax) return r;
-    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
-    const int bb = v - 2 * a;
-    if ((bb == 0 && sb) || (a == bb && sw)) return r;      // duplicate images of the same pixel
-    const int pa = sa ? -a : a, pb = sb ? -bb : bb;
-    const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
-    const int y = cy + Yo, x = cx + Xo;
-    if (y < 0 || y >= Ny || x < 0 || x >= Nx) return r;
-    const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
-    const int W2 = 2 * Nx - 1;
-    r.ti = (((by * 3 + bx) * (2 * Ny - 1) + (Yo + Ny - 1)) * W2 + (Xo + Nx - 1)) * 8;
-    r.p = y * Nx + x;
-    r.ok = true;
-    return r;
+// Neighbour values of pixel p.  All nine loads are issued together and unconditionally: X must be readable from
+// X[-Nx-1] to X[N+Nx] (a front pad, and whatever scratch follows X in shared memory); a tap outside the image
+// has zero weight and its value is never used.
+struct SclMonoNb { float x0, x1, x2, x3, x4, x5, x6, x7, cur; };
+__device__ __forceinline__ SclMonoNb scl_mono_load(const float* X, int Nx, int p) {
+    const float* q = X + p;
+    SclMonoNb n;
+    n.x0 = q[-Nx - 1]; n.x1 = q[-Nx]; n.x2 = q[-Nx + 1]; n.x3 = q[-1];
+    n.x4 = q[1]; n.x5 = q[Nx - 1]; n.x6 = q[Nx]; n.x7 = q[Nx + 1];
+    n.cur = q[0];
+    return n;
 }
-
-__device__ __forceinline__ void scl_mono_apply(float* X, int Nx, int p, const float4& w0, const float4& w1, float omt) {
-    // all eight neighbour loads are issued together (a tap with zero weight may lie outside the image: it reads
-    // the pixel itself instead); the sum then runs in tap order over the positive weights only
-    // (operators_pybind11.cc:39-47), un-fused so that it rounds like the reference
-    const float x0 = X[w0.x > 0.f ? p - Nx - 1 : p], x1 = X[w0.y > 0.f ? p - Nx : p];
-    const float x2 = X[w0.z > 0.f ? p - Nx + 1 : p], x3 = X[w0.w > 0.f ? p - 1 : p];
-    const float x4 = X[w1.x > 0.f ? p + 1 : p], x5 = X[w1.y > 0.f ? p + Nx - 1 : p];
-    const float x6 = X[w1.z > 0.f ? p + Nx : p], x7 = X[w1.w > 0.f ? p + Nx + 1 : p];
-    const float cur = X[p];
+// The sum runs in tap order over the positive weights only (operators_pybind11.cc:39-47), un-fused so that it
+// rounds like the reference; returns min(cur, ref (1 - thresh)).
+__device__ __forceinline__ float scl_mono_value(const SclMonoNb& n, const float4& w0, const float4& w1, float omt) {
     float ref = 0.f;
-    if (w0.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(x0, w0.x));
-    if (w0.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(x1, w0.y));
-    if (w0.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(x2, w0.z));
-    if (w0.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(x3, w0.w));
-    if (w1.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(x4, w1.x));
-    if (w1.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(x5, w1.y));
-    if (w1.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(x6, w1.z));
-    if (w1.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(x7, w1.w));
+    if (w0.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x0, w0.x));
+    if (w0.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x1, w0.y));
+    if (w0.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x2, w0.z));
+    if (w0.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x3, w0.w));
+    if (w1.x > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x4, w1.x));
+    if (w1.y > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x5, w1.y));
+    if (w1.z > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x6, w1.z));
+    if (w1.w > 0.f) ref = __fadd_rn(ref, __fmul_rn(n.x7, w1.w));
     const float r = __fmul_rn(ref, omt);
-    X[p] = (r < cur) ? r : cur;
+    return (r < n.cur) ? r : n.cur;
 }
 
-template <int NT>
-__device__ __forceinline__ void scl_mono_sync() {
-    if (NT == 32) __syncwarp();
-    else __syncthreads();
-}
-
-// Requires Ny, Nx >= 2 and blockDim.x == NT.
-template <int NT>
-__device__ void scl_monotonic_f32(float* X, int Ny, int Nx, int cy, int cx, const float* __restrict__ wt9, float thresh) {
-    const float omt = 1.f - thresh;
-    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
-    const int vmax = 2 * max(ay, ax) + min(ay, ax);
-    const int tid = threadIdx.x, slot = tid >> 3, oct = tid & 7;
-    constexpr int NSLOT = NT / 8;
-    scl_mono_sync<NT>();
-    // weights of the first pass of level v are fetched while level v-1 is being processed
-    SclMonoLoc nx = scl_mono_locate(1, 1 + slot, 0, oct, Ny, Nx, cy, cx);
-    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0;
-    if (nx.ok) { n0 = *reinterpret_cast<const float4*>(wt9 + nx.ti); n1 = *reinterpret_cast<const float4*>(wt9 + nx.ti + 4); }
-    for (int v = 1; v <= vmax; v++) {
-        const SclMonoLoc cur = nx;
-        const float4 c0 = n0, c1 = n1;
-        const int amin = (v + 2) / 3, amax = v / 2;
-        if (v < vmax) {
-            nx = scl_mono_locate(v + 1, (v + 3) / 3 + slot, (v + 1) / 2, oct, Ny, Nx, cy, cx);
-            if (nx.ok) { n0 = *reinterpret_cast<const float4*>(wt9 + nx.ti); n1 = *reinterpret_cast<const float4*>(wt9 + nx.ti + 4); }
-        }
-        if (cur.ok) scl_mono_apply(X, Nx, cur.p, c0, c1, omt);
-        for (int a = amin + slot + NSLOT; a <= amax; a += NSLOT) {
-            const SclMonoLoc e = scl_mono_locate(v, a, amax, oct, Ny, Nx, cy, cx);
-            if (e.ok) {
-                const float4 e0 = *reinterpret_cast<const float4*>(wt9 + e.ti);
-                const float4 e1 = *reinterpret_cast<const float4*>(wt9 + e.ti + 4);
-                scl_mono_apply(X, Nx, e.p, e0, e1, omt);
-            }
-        }
-        scl_mono_sync<NT>();
-    }
-}
-
-// ---- single-warp wavefront over a per-centre level list ----------------------
-// The sweep has ~2 max(H,W) + min(H,W) dependent levels with a few dozen pixels each.  The CTA first sorts the
-// image's pixels by level into a list in shared memory (counting sort; the order inside a level is irrelevant,
-// see above), then ONE warp walks the list, 32 pixels per pass, while the other warps wait at a barrier and
-// issue nothing.  The weights of a pass come from wt9 (L2, several hundred cycles away): each lane copies its
-// 32 bytes with cp.async into a ring of SCL_MONO_RING pass slots in shared memory, several passes ahead of
-// their use, so that the dependent chain of a level is shared memory only.
-#define SCL_MAX_LEVELS 480
+// ---- single-warp wavefront over a precomputed per-centre plan -----------------
+// The sweep has ~2 max(H,W) + min(H,W) dependent levels with a few dozen pixels each; the level a pixel belongs
+// to depends only on its offset from the centre.  When the tables of a shape are registered, a one-off kernel
+// sorts the pixels by level for EVERY possible centre (counting sort in shared memory; the order inside a level
+// is irrelevant, see above) and stores the result in global memory as "passes" of 32 entries
+//     entry = table_row << pbits | pixel,     0xffffffff = lane idle,
+// each level padded to whole passes (table_row = index of the pixel's eight weights in wt9, border type
+// included).  In the loop ONE warp per component streams its centre's passes: pass i's entries are copied to a
+// ring in shared memory (cp.async) 2R passes ahead, its weights (wt9, L2) R passes ahead, so that the dependent
+// chain of a level touches shared memory only and costs ~60 instructions per pass.  The other warps of the CTA
+// wait at a barrier and issue nothing.
 #define SCL_MONO_RING 6
 #ifndef SCL_EXP
 #define SCL_EXP 0
 #endif
-struct SclMonoWork {            // views into the scratch (aliases the symmetry step's Z buffer)
+struct SclMonoPlan {
+    const unsigned* list;       // all centres' passes, 32 entries each
+    const unsigned* first;      // [N + 1] first pass of centre cy * Nx + cx
+    int pbits;                  // bits of the pixel field; 0 = no plan for this shape (generic path)
+};
+// scratch of the streamed sweep: weights ring [R][2][32] float4, entry ring [2R][32]
+#define SCL_MONO_STREAM_BYTES (SCL_MONO_RING * 1024 + 2 * SCL_MONO_RING * 128)
+
+// Work areas of the plan builder (one CTA per centre)
+struct SclMonoWork {
     int* start;                 // [vmax + 3] first list index of each level
     int* fill;                  // [vmax + 3]
     unsigned short* list;       // [N] packed (y << 8 | x), level-ordered
-    float4* ring;               // [SCL_MONO_RING][32][2]
 };
 __host__ __device__ inline size_t scl_mono_work_bytes(int N, int vmax) {
-    return (((size_t)8 * (vmax + 3) + 2 * (size_t)N + 15) & ~(size_t)15) + (size_t)SCL_MONO_RING * 32 * 32;
+    return (((size_t)8 * (vmax + 3) + 2 * (size_t)N + 15) & ~(size_t)15);
 }
 __device__ __forceinline__ SclMonoWork scl_mono_work(void* base, int N, int vmax) {
     SclMonoWork w;
     unsigned char* b = reinterpret_cast<unsigned char*>(base);
-    w.ring = reinterpret_cast<float4*>(b);                               // 16-byte aligned first
-    b += (size_t)SCL_MONO_RING * 32 * 32;
     w.start = reinterpret_cast<int*>(b);
     w.fill = w.start + (vmax + 3);
     w.list = reinterpret_cast<unsigned short*>(w.fill + (vmax + 3));
@@ -490,55 +444,92 @@ __device__ void scl_mono_build(const SclMonoWork& wk, int Ny, int Nx, int cy, in
     __syncthreads();
 }
 
-// Called by the 32 lanes of ONE warp after scl_mono_build.  Ny, Nx >= 2.
-__device__ void scl_monotonic_f32_warp(float* X, int Ny, int Nx, int cy, int cx, const SclMonoWork& wk,
-                                       const float* __restrict__ wt9, float thresh, int vmax) {
+// Called by the 32 lanes of ONE warp.  X readable on [-Nx-1, N+Nx] (scl_mono_load); `passes` = this centre's
+// first entry, `scratch` = SCL_MONO_STREAM_BYTES of 16-byte aligned shared memory.
+__device__ void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __restrict__ passes, int npass, int pbits,
+                                         const float* __restrict__ wt9, float thresh, void* scratch) {
+    constexpr int R = SCL_MONO_RING;
     const float omt = 1.f - thresh;
     const int lane = threadIdx.x & 31;
-    const int H2 = 2 * Ny - 1, W2 = 2 * Nx - 1;
-    int cv = 2, cpos = wk.start[2], cend = wk.start[3];           // issue cursor (warp-uniform)
-    // one pass: bit 31 = pass exists, bit 30 = last pass of its level, bit 29 = this lane has a pixel, low bits = p
-    auto issue = [&](int slot) -> unsigned {
-        unsigned m = 0;
-        if (cv <= vmax) {
-            m = 0x80000000u;
-            const int idx = cpos + lane;
-            if (idx < cend) {
-                const int yx = wk.list[idx], y = yx >> 8, x = yx & 255;
-                const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
-                const float* wp = wt9 + ((size_t)((by * 3 + bx) * H2 + (y - cy + Ny - 1)) * W2 + (x - cx + Nx - 1)) * 8;
-                const unsigned dst = (unsigned)__cvta_generic_to_shared(wk.ring + (slot * 32 + lane) * 2);
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(dst), "l"(wp));
-                asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(dst + 16), "l"(wp + 4));
-                m |= 0x20000000u | (unsigned)(y * Nx + x);
-            }
-            cpos += 32;
-            if (cpos >= cend) { m |= 0x40000000u; cv++; cpos = wk.start[cv]; cend = wk.start[cv + 1]; }
-        }
-        asm volatile("cp.async.commit_group;\n" ::);
-        return m;
+    const unsigned pmask = (1u << pbits) - 1u;
+    float4* ringW = reinterpret_cast<float4*>(scratch);
+    unsigned* ringL = reinterpret_cast<unsigned*>(ringW + R * 64);
+    const unsigned aW = (unsigned)__cvta_generic_to_shared(ringW) + lane * 16;
+    const unsigned aL = (unsigned)__cvta_generic_to_shared(ringL) + lane * 4;
+    // `dep` makes the compiler keep the copy after the ring reads it overwrites (no memory clobber: the copies may
+    // otherwise be scheduled freely among the arithmetic)
+    auto copy_entries = [&](int pass, int slotL, unsigned dep) {
+        if (pass < npass)
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n"
+                         :: "r"(aL + slotL * 128), "l"(passes + (size_t)pass * 32 + lane), "r"(dep));
     };
-    // passes i .. i + RING - 2 are in flight while pass i is processed
-    unsigned meta[SCL_MONO_RING - 1];
-#pragma unroll
-    for (int d = 0; d < SCL_MONO_RING - 1; d++) meta[d] = issue(d);
-    int slot = 0;
-    while (meta[0] & 0x80000000u) {
-        const unsigned m = meta[0];
-#pragma unroll
-        for (int d = 0; d + 1 < SCL_MONO_RING - 1; d++) meta[d] = meta[d + 1];
-        int nslot = slot + SCL_MONO_RING - 1;
-        if (nslot >= SCL_MONO_RING) nslot -= SCL_MONO_RING;
-        meta[SCL_MONO_RING - 2] = issue(nslot);
-        asm volatile("cp.async.wait_group %0;\n" :: "n"(SCL_MONO_RING - 1));
-        if (m & 0x20000000u) {
-            const float4 w0 = wk.ring[(slot * 32 + lane) * 2], w1 = wk.ring[(slot * 32 + lane) * 2 + 1];
-            scl_mono_apply(X, Nx, (int)(m & 0xffffffu), w0, w1, omt);
+    auto copy_weights = [&](unsigned e, int slotW, float dep0, float dep1) {
+        if (e != 0xffffffffu) {
+            const float* wp = wt9 + (size_t)(e >> pbits) * 8;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024), "l"(wp), "f"(dep0));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024 + 512), "l"(wp + 4), "f"(dep1));
         }
-        if (m & 0x40000000u) __syncwarp();
-        slot = (slot + 1 == SCL_MONO_RING) ? 0 : slot + 1;
+    };
+    // prologue: entries of passes 0 .. 2R-1, then weights of passes 0 .. R-1
+#pragma unroll
+    for (int i = 0; i < 2 * R; i++) copy_entries(i, i, 0u);
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+        if (i < npass) copy_weights(ringL[i * 32 + lane], i, 0.f, 0.f);
+        asm volatile("cp.async.commit_group;\n" ::);
     }
-    asm volatile("cp.async.wait_group 0;\n" ::);
+    int sW = 0, sL = 0, sL2 = R;            // slots of pass j (weights, entries) and of pass j + R (entries)
+    for (int j = 0; j < npass; j++) {
+        // everything but the R-1 newest groups has landed: weights of pass j, entries of pass j + R
+        asm volatile("cp.async.wait_group %0;\n" :: "n"(R - 1) : "memory");
+        const unsigned e = ringL[sL * 32 + lane];
+        const float4 w0 = ringW[sW * 64 + lane], w1 = ringW[sW * 64 + 32 + lane];
+        const bool has = e != 0xffffffffu;
+        const int p = has ? (int)(e & pmask) : 0;           // idle lanes run on pixel 0 and store nothing
+        const SclMonoNb nb = scl_mono_load(X, Nx, p);
+        const unsigned e2 = (j + R < npass) ? ringL[sL2 * 32 + lane] : 0xffffffffu;
+        copy_weights(e2, sW, w0.x, w1.x);
+        copy_entries(j + 2 * R, sL, e);
+        asm volatile("cp.async.commit_group;\n" ::);
+        const float v = scl_mono_value(nb, w0, w1, omt);
+        if (has) X[p] = v;
+        __syncwarp();                       // a level may end here: its stores must be visible to the next pass
+        sW = (sW + 1 == R) ? 0 : sW + 1;
+        sL = (sL + 1 == 2 * R) ? 0 : sL + 1;
+        sL2 = (sL2 + 1 == 2 * R) ? 0 : sL2 + 1;
+    }
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+// Plan builder, all threads of the CTA after scl_mono_build(wk, ...) for centre (cy, cx): number of passes
+// (out == nullptr) or the passes themselves.  `pbase` = vmax + 3 ints of shared memory.
+__device__ int scl_mono_emit(const SclMonoWork& wk, int Ny, int Nx, int cy, int cx, int vmax, int pbits,
+                             int* pbase, unsigned* out) {
+    const int H2 = 2 * Ny - 1, W2 = 2 * Nx - 1;
+    if (threadIdx.x == 0) {
+        int run = 0;
+        for (int v = 0; v <= vmax; v++) { pbase[v] = run; run += (wk.start[v + 1] - wk.start[v] + 31) >> 5; }
+        pbase[vmax + 1] = run;
+    }
+    __syncthreads();
+    const int total = pbase[vmax + 1];
+    if (out) {
+        for (int v = 1; v <= vmax; v++) {
+            const int s0 = wk.start[v], cnt = wk.start[v + 1] - s0, np = pbase[v + 1] - pbase[v];
+            for (int s = threadIdx.x; s < np * 32; s += blockDim.x) {
+                unsigned e = 0xffffffffu;
+                if (s < cnt) {
+                    const int yx = wk.list[s0 + s], y = yx >> 8, x = yx & 255;
+                    const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
+                    const unsigned row = (unsigned)(((by * 3 + bx) * H2 + (y - cy + Ny - 1)) * W2 + (x - cx + Nx - 1));
+                    e = (row << pbits) | (unsigned)(y * Nx + x);
+                }
+                out[(size_t)pbase[v] * 32 + s] = e;
+            }
+        }
+    }
+    return total;
 }
 
 template <typename T, bool NEAREST>
