@@ -361,7 +361,12 @@ __device__ __forceinline__ float scl_mono_value(const SclMonoNb& n, const float4
 // ring in shared memory (cp.async) 2R passes ahead, its weights (wt9, L2) R passes ahead, so that the dependent
 // chain of a level touches shared memory only and costs ~60 instructions per pass.  The other warps of the CTA
 // wait at a barrier and issue nothing.
-#define SCL_MONO_RING 6
+#ifndef SCL_MONO_RING
+#define SCL_MONO_RING 8           // power of two
+#endif
+#ifndef SCL_STREAM_INLINE
+#define SCL_STREAM_INLINE __forceinline__
+#endif
 #ifndef SCL_EXP
 #define SCL_EXP 0
 #endif
@@ -446,8 +451,11 @@ __device__ void scl_mono_build(const SclMonoWork& wk, int Ny, int Nx, int cy, in
 
 // Called by the 32 lanes of ONE warp.  X readable on [-Nx-1, N+Nx] (scl_mono_load); `passes` = this centre's
 // first entry, `scratch` = SCL_MONO_STREAM_BYTES of 16-byte aligned shared memory.
-__device__ void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __restrict__ passes, int npass, int pbits,
-                                         const float* __restrict__ wt9, float thresh, void* scratch) {
+// (Processing the passes of one level two at a time -- two pixels per lane -- was measured and is not faster: the
+// warp is bound by its instruction count, not by the number of dependent steps.)
+#define SCL_MONO_IDLE 0xffffffffu
+__device__ SCL_STREAM_INLINE void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __restrict__ passes, int npass,
+                                                      int pbits, const float* __restrict__ wt9, float thresh, void* scratch) {
     constexpr int R = SCL_MONO_RING;
     const float omt = 1.f - thresh;
     const int lane = threadIdx.x & 31;
@@ -464,11 +472,20 @@ __device__ void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __res
                          :: "r"(aL + slotL * 128), "l"(passes + (size_t)pass * 32 + lane), "r"(dep));
     };
     auto copy_weights = [&](unsigned e, int slotW, float dep0, float dep1) {
-        if (e != 0xffffffffu) {
+        if (e != SCL_MONO_IDLE) {
             const float* wp = wt9 + (size_t)(e >> pbits) * 8;
             asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024), "l"(wp), "f"(dep0));
             asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024 + 512), "l"(wp + 4), "f"(dep1));
         }
+    };
+    // what a processed pass owes the pipeline: weights of pass + R into its weight slot, entries of pass + 2R into
+    // its entry slot, one commit group
+    auto refill = [&](int pass, int slotW, int slotL, unsigned e, float dep0, float dep1) {
+        const int sl = (slotL + R) & (2 * R - 1);
+        const unsigned eR = (pass + R < npass) ? ringL[sl * 32 + lane] : SCL_MONO_IDLE;
+        copy_weights(eR, slotW, dep0, dep1);
+        copy_entries(pass + 2 * R, slotL, e);
+        asm volatile("cp.async.commit_group;\n" ::);
     };
     // prologue: entries of passes 0 .. 2R-1, then weights of passes 0 .. R-1
 #pragma unroll
@@ -479,25 +496,21 @@ __device__ void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __res
         if (i < npass) copy_weights(ringL[i * 32 + lane], i, 0.f, 0.f);
         asm volatile("cp.async.commit_group;\n" ::);
     }
-    int sW = 0, sL = 0, sL2 = R;            // slots of pass j (weights, entries) and of pass j + R (entries)
+    unsigned e = ringL[lane];               // entry of the next pass, read one pass early
     for (int j = 0; j < npass; j++) {
+        const int sW = j & (R - 1), sL = j & (2 * R - 1);   // weight / entry slots of pass j
         // everything but the R-1 newest groups has landed: weights of pass j, entries of pass j + R
         asm volatile("cp.async.wait_group %0;\n" :: "n"(R - 1) : "memory");
-        const unsigned e = ringL[sL * 32 + lane];
         const float4 w0 = ringW[sW * 64 + lane], w1 = ringW[sW * 64 + 32 + lane];
-        const bool has = e != 0xffffffffu;
+        const bool has = e != SCL_MONO_IDLE;
         const int p = has ? (int)(e & pmask) : 0;           // idle lanes run on pixel 0 and store nothing
         const SclMonoNb nb = scl_mono_load(X, Nx, p);
-        const unsigned e2 = (j + R < npass) ? ringL[sL2 * 32 + lane] : 0xffffffffu;
-        copy_weights(e2, sW, w0.x, w1.x);
-        copy_entries(j + 2 * R, sL, e);
-        asm volatile("cp.async.commit_group;\n" ::);
+        const unsigned en = ringL[((j + 1) & (2 * R - 1)) * 32 + lane];   // landed long ago; stale past the end
+        refill(j, sW, sL, e, w0.x, w1.x);
         const float v = scl_mono_value(nb, w0, w1, omt);
         if (has) X[p] = v;
         __syncwarp();                       // a level may end here: its stores must be visible to the next pass
-        sW = (sW + 1 == R) ? 0 : sW + 1;
-        sL = (sL + 1 == 2 * R) ? 0 : sL + 1;
-        sL2 = (sL2 + 1 == 2 * R) ? 0 : sL2 + 1;
+        e = en;
     }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");
 }
@@ -518,7 +531,7 @@ __device__ int scl_mono_emit(const SclMonoWork& wk, int Ny, int Nx, int cy, int 
         for (int v = 1; v <= vmax; v++) {
             const int s0 = wk.start[v], cnt = wk.start[v + 1] - s0, np = pbase[v + 1] - pbase[v];
             for (int s = threadIdx.x; s < np * 32; s += blockDim.x) {
-                unsigned e = 0xffffffffu;
+                unsigned e = SCL_MONO_IDLE;
                 if (s < cnt) {
                     const int yx = wk.list[s0 + s], y = yx >> 8, x = yx & 255;
                     const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
