@@ -150,16 +150,24 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
             for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
         const float* xr = Xw + i0 * Nx;
         const float* tp = Tx + j0;
-        float t0 = tp[0], t1 = tp[1], t2 = tp[2];
+        // The two half-warps work on different row groups (same bank whenever Nx is a multiple of 32): the upper
+        // half runs its l loop rotated by one element, so that its broadcast load hits the neighbouring bank.
+        const int rot = (nx > 1) ? ((threadIdx.x >> 4) & 1) : 0;
+#pragma unroll 1
+        for (int seg = 0; seg < 2; seg++) {
+            const int lb = seg ? 0 : rot, le = seg ? rot : nx;
+            if (lb >= le) continue;
+            float t0 = tp[lb], t1 = tp[lb + 1], t2 = tp[lb + 2];
 #pragma unroll 4
-        for (int l = 0; l < nx; l++) {
-            const float t3 = tp[l + 3];
+            for (int l = lb; l < le; l++) {
+                const float t3 = tp[l + 3];
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                const float xv = xr[r * Nx + l];
-                acc[r][0] += xv * t0; acc[r][1] += xv * t1; acc[r][2] += xv * t2; acc[r][3] += xv * t3;
+                for (int r = 0; r < 8; r++) {
+                    const float xv = xr[r * Nx + l];
+                    acc[r][0] += xv * t0; acc[r][1] += xv * t1; acc[r][2] += xv * t2; acc[r][3] += xv * t3;
+                }
+                t0 = t1; t1 = t2; t2 = t3;
             }
-            t0 = t1; t1 = t2; t2 = t3;
         }
 #pragma unroll
         for (int r = 0; r < 8; r++)
