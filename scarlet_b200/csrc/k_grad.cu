@@ -10,58 +10,58 @@
 // Inputs produced by K1: loss_part[b,c], gram[b] = S S^T (double 8x8).
 // Both gradient steps (blend.py:91-96) are applied by K3 with the constants written here.
 //
-// lambda_max: cyclic Jacobi in f32 on the register-resident 8x8 matrix (zero padded) with the rotations
-// accumulated into V, then the Rayleigh quotient of the winning column in f64 against the f64 matrix:
-// the eigenvector error e ~ 1e-6 of the f32 sweep enters the eigenvalue as e^2.  (The reference's own
-// value comes from LAPACK sgeev on an f32 Gram matrix, i.e. is itself only f32-accurate.)
+// lambda_max: top eigenvector by repeated squaring in f32 on the register-resident 8x8 matrix (zero padded), then
+// the Rayleigh quotient of that vector in f64 against the f64 matrix: an eigenvector error e enters the eigenvalue
+// as e^2 (power8_top_vector has the bound).  (The reference's own value comes from LAPACK sgeev on an f32 Gram
+// matrix, i.e. is itself only f32-accurate.)
 #include "common.cuh"
 
 namespace {
 
 constexpr int JN = 8;      // padded matrix edge == max components per blend == SCL_MAX_BANDS
 
-// In: a (symmetric, full storage).  Out: v = eigenvector of the largest eigenvalue (unit norm up to f32 rounding).
-__device__ __forceinline__ void jacobi8_top_vector(float (&a)[JN][JN], float (&vec)[JN]) {
-    float v[JN][JN];
+// In: a (symmetric positive semi-definite, full storage).  Out: vec ~ eigenvector of the largest eigenvalue.
+// Repeated squaring, a <- a a / trace(a a): after s squarings a is proportional to sum_i (l_i / l_1)^(2^s) v_i v_i^T,
+// so any non-zero column is the top eigenvector up to e = (l_2 / l_1)^(2^s).  The caller's f64 Rayleigh quotient
+// then misses l_1 by at most (l_1 - l_2) e^2 <= l_1 max_g g exp(-2^(s+1) g) = l_1 / (e 2^(s+1)): 2.8e-6 l_1 for
+// s = 16, attained only when the two largest eigenvalues agree to 1e-5 (where either is as good a bound), and
+// far below that otherwise.  Unlike cyclic Jacobi (serial rotations, ~100 k dependent cycles per matrix) the 36
+// dot products of a squaring are independent, so a thread pipelines them at full rate.
+__device__ __forceinline__ void power8_top_vector(float (&a)[JN][JN], float (&vec)[JN]) {
+    float tr = 0.f;
 #pragma unroll
-    for (int i = 0; i < JN; i++)
+    for (int i = 0; i < JN; i++) tr += a[i][i];
+    if (!(tr > 0.f)) {
 #pragma unroll
-        for (int j = 0; j < JN; j++) v[i][j] = (i == j) ? 1.f : 0.f;
-    for (int sweep = 0; sweep < 10; sweep++) {
-        float off = 0.f, diag = 0.f;
+        for (int i = 0; i < JN; i++) vec[i] = (i == 0) ? 1.f : 0.f;
+        return;
+    }
+    {
+        const float s = 1.f / tr;
 #pragma unroll
-        for (int i = 0; i < JN; i++) {
-            diag += a[i][i] * a[i][i];
+        for (int i = 0; i < JN; i++)
 #pragma unroll
-            for (int j = i + 1; j < JN; j++) off += a[i][j] * a[i][j];
-        }
-        if (off <= 1e-14f * diag) break;
+            for (int j = 0; j < JN; j++) a[i][j] *= s;
+    }
+#pragma unroll 1
+    for (int it = 0; it < 16; it++) {
+        float b[JN][JN];
+        float t2 = 0.f;
 #pragma unroll
-        for (int p = 0; p < JN - 1; p++)
+        for (int i = 0; i < JN; i++)
 #pragma unroll
-            for (int q = p + 1; q < JN; q++) {
-                const float apq = a[p][q];
-                if (apq != 0.f) {
-                    const float theta = (a[q][q] - a[p][p]) / (2.f * apq);
-                    const float t = copysignf(1.f, theta) / (fabsf(theta) + sqrtf(theta * theta + 1.f));
-                    const float c = rsqrtf(t * t + 1.f), s = t * c;
+            for (int j = i; j < JN; j++) {
+                float d = 0.f;
 #pragma unroll
-                    for (int r = 0; r < JN; r++) {
-                        if (r != p && r != q) {
-                            const float arp = a[r][p], arq = a[r][q];
-                            const float np_ = c * arp - s * arq, nq_ = s * arp + c * arq;
-                            a[r][p] = np_; a[p][r] = np_;
-                            a[r][q] = nq_; a[q][r] = nq_;
-                        }
-                        const float vrp = v[r][p], vrq = v[r][q];
-                        v[r][p] = c * vrp - s * vrq;
-                        v[r][q] = s * vrp + c * vrq;
-                    }
-                    a[p][p] -= t * apq;
-                    a[q][q] += t * apq;
-                    a[p][q] = 0.f; a[q][p] = 0.f;
-                }
+                for (int k = 0; k < JN; k++) d += a[i][k] * a[j][k];
+                b[i][j] = d;
+                if (i == j) t2 += d;
             }
+        const float s = 1.f / t2;          // t2 = sum l_i^2 / (sum l_i)^2 >= 1/8 of the previous normalisation
+#pragma unroll
+        for (int i = 0; i < JN; i++)
+#pragma unroll
+            for (int j = i; j < JN; j++) { const float v = b[i][j] * s; a[i][j] = v; a[j][i] = v; }
     }
     int best = 0;
     float top = a[0][0];
@@ -70,9 +70,9 @@ __device__ __forceinline__ void jacobi8_top_vector(float (&a)[JN][JN], float (&v
         if (a[i][i] > top) { top = a[i][i]; best = i; }
 #pragma unroll
     for (int r = 0; r < JN; r++) {
-        float x = v[r][0];
+        float x = a[r][0];
 #pragma unroll
-        for (int j = 1; j < JN; j++) x = (best == j) ? v[r][j] : x;
+        for (int j = 1; j < JN; j++) x = (best == j) ? a[r][j] : x;
         vec[r] = x;
     }
 }
@@ -129,7 +129,7 @@ scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
                 }
             }
             float vec[JN];
-            jacobi8_top_vector(a, vec);
+            power8_top_vector(a, vec);
             // f64 Rayleigh quotient v^T M v / v^T v
             double num = 0.0, den = 0.0;
 #pragma unroll
