@@ -330,7 +330,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--blends", type=int, default=10000, help="blends per GPU")
     ap.add_argument("--check-every", type=int, default=8)
-    ap.add_argument("--streams", type=int, default=4, help="independently driven chunks per GPU (BlendBatch streams=)")
+    ap.add_argument("--streams", type=int, default=1, help="independently driven chunks per GPU (BlendBatch streams=)")
     ap.add_argument("--roofline-iters", type=int, default=40)
     ap.add_argument("--ref-per-worker", type=int, default=6)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
