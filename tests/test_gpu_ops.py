@@ -41,10 +41,12 @@ def test_monotonic_vs_reference_fixture(nat, golden, tag):
             assert_array_equal(x[0], golden["mono_%s_out_%s_t%d" % (tag, dt, t)])   # bit-exact
 
 
-@pytest.mark.parametrize("shape", [(64, 64), (69, 57), (40, 59), (7, 100)])
+# (90, 80) has streamed sweep plans with 13 pixel bits; (100, 100) and (128, 87) exceed the plan entry format and
+# take the generic level loop; (2, 3) is the smallest shape the sweep accepts
+@pytest.mark.parametrize("shape", [(64, 64), (69, 57), (40, 59), (7, 100), (90, 80), (100, 100), (128, 87), (2, 3)])
 def test_monotonic_random_centres_bit_exact(nat, shape):
     rng = np.random.default_rng(3)
-    n = 24
+    n = 24 if shape[0] * shape[1] < 8000 else 8
     centers = np.stack([rng.integers(0, shape[0], n), rng.integers(0, shape[1], n)], axis=1)
     centers[0] = (0, 0)
     centers[1] = (shape[0] - 1, shape[1] - 1)
@@ -57,6 +59,14 @@ def test_monotonic_random_centres_bit_exact(nat, shape):
             g = x[i].copy()
             ref_prox.build_monotonic(shape, tuple(centers[i]), 0.1 if dt == np.float64 else 0.0)(g)
             assert_array_equal(y[i], g)
+    # float32 with the threshold of source initialisation (source.py:165-166)
+    x = (rng.random((n,) + shape) - .2).astype(np.float32)
+    y = x.copy()
+    nat.prox_weighted_monotonic(y, centers, 0.1)
+    for i in range(n):
+        g = x[i].copy()
+        ref_prox.build_monotonic(shape, tuple(centers[i]), 0.1)(g)
+        assert_array_equal(y[i], g)
 
 
 @pytest.mark.parametrize("tag", ["a", "b", "c", "d", "e"])
