@@ -33,6 +33,9 @@ extern "C" {
 #define SCL_FIX_MORPH 8u    /* component.fix_morph (blend.py:94) */
 #define SCL_KSPACE 16u      /* owner has `.shift`: k-space symmetry; else soft symmetry, strength 1 (operator.py:337-339) */
 #define SCL_CONSTRAINED 32u /* owner runs PointSource.update (source.py:402-440); plain Component.update is a no-op */
+#define SCL_SHARED_CENTER 64u /* component of a MultiComponentSource (source.py:605-641): max_pixel / centroid are
+                               * measured once per source on sum_k morph_k * sum(sed_k) and shared by its components
+                               * (which carry no `.shift`: soft symmetry); needs scl_batch_desc.src_first */
 
 int scl_version(void);
 const char* scl_last_error(void);
@@ -104,6 +107,9 @@ typedef struct {
     const int32_t* cw_idx;          /* [B] */
     const int32_t* it0;             /* [B] Blend.it before this fit (len(mse)) */
     const double* prev_loss;        /* [B] mse[-1] before this fit (ignored where it0 == 0) */
+    const int32_t* src_first;       /* [Ktot] or NULL: index of the first component of the source that owns component
+                                     * k (the components of a source are contiguous, ComponentTree order); only read
+                                     * for components flagged SCL_SHARED_CENTER.  NULL = no such component */
 } scl_batch_desc;
 
 /* Allocate device state for `desc`'s sizes and upload it. */

@@ -14,7 +14,7 @@ LIB_PATH = os.environ.get("SCL_LIB") or os.path.join(_HERE, "lib", "libscarlet_b
 FFT_EDGE = 128
 SPEC_COLS = 65
 
-F_SYMMETRIC, F_MONOTONIC, F_FIX_SED, F_FIX_MORPH, F_KSPACE, F_CONSTRAINED = 1, 2, 4, 8, 16, 32
+F_SYMMETRIC, F_MONOTONIC, F_FIX_SED, F_FIX_MORPH, F_KSPACE, F_CONSTRAINED, F_SHARED_CENTER = 1, 2, 4, 8, 16, 32, 64
 
 _lib = None
 _lock = threading.Lock()
@@ -32,7 +32,7 @@ class BatchDesc(ctypes.Structure):
         ("n_ker", ctypes.c_int32), ("kernel_spec", c_void_p), ("ker_idx", c_void_p),
         ("n_cw", ctypes.c_int32), ("ph", ctypes.c_int32), ("pw", ctypes.c_int32),
         ("cw", c_void_p), ("cw_idx", c_void_p),
-        ("it0", c_void_p), ("prev_loss", c_void_p),
+        ("it0", c_void_p), ("prev_loss", c_void_p), ("src_first", c_void_p),
     ]
 
 
@@ -278,7 +278,7 @@ class Batch:
     (thin owner of a `scl_batch*`)."""
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
-                 kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, stream=None):
+                 kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None):
         require_device()
         monotonic_tables(Ny, Nx)
         self.C, self.Ny, self.Nx = int(C), int(Ny), int(Nx)
@@ -287,11 +287,11 @@ class Batch:
         self._keep = None
         self.max_iter = 0
         desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-                          cw, cw_idx, it0, prev_loss)
+                          cw, cw_idx, it0, prev_loss, src_first)
         _check(lib().scl_batch_create(ctypes.byref(desc), ctypes.byref(self._h), c_void_p(self.stream)))
 
     def _desc(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-              cw, cw_idx, it0, prev_loss):
+              cw, cw_idx, it0, prev_loss, src_first=None):
         N = self.Ny * self.Nx
         ca = np.ascontiguousarray
         comp_off = ca(comp_off, dtype=np.int32)
@@ -313,13 +313,14 @@ class Batch:
             cw_idx=ca(cw_idx, dtype=np.int32).reshape(B),
             it0=ca(np.zeros(B) if it0 is None else it0, dtype=np.int32).reshape(B),
             prev_loss=None if prev_loss is None else ca(prev_loss, dtype=np.float64).reshape(B),
+            src_first=None if src_first is None else ca(src_first, dtype=np.int32).reshape(K),
         )
         self._keep = a
         self.B, self.K = B, K
         d = BatchDesc()
         d.n_blends, d.n_comp, d.C, d.Ny, d.Nx = B, K, self.C, self.Ny, self.Nx
         for name in ("comp_off", "sed", "morph", "cflags", "center", "shift", "conv", "images", "weights",
-                     "kernel_spec", "ker_idx", "cw", "cw_idx", "it0", "prev_loss"):
+                     "kernel_spec", "ker_idx", "cw", "cw_idx", "it0", "prev_loss", "src_first"):
             setattr(d, name, _p(a[name]))
         d.n_ker = 0 if a["kernel_spec"] is None else len(a["kernel_spec"])
         if a["cw"] is None:
@@ -330,9 +331,9 @@ class Batch:
         return d
 
     def upload(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-               cw, cw_idx, it0=None, prev_loss=None):
+               cw, cw_idx, it0=None, prev_loss=None, src_first=None):
         desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-                          cw, cw_idx, it0, prev_loss)
+                          cw, cw_idx, it0, prev_loss, src_first)
         _check(lib().scl_batch_upload(self._h, ctypes.byref(desc), c_void_p(self.stream)))
 
     def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False):

@@ -60,6 +60,8 @@ class _Chunks:
                 out[key] = (np.asarray(v[b0:b1 + 1]) - k0).astype(np.int32)
             elif key == "ker_idx":
                 out[key] = v[b0 * self.C:b1 * self.C]
+            elif key == "src_first":
+                out[key] = (np.asarray(v[k0:k1]) - k0).astype(np.int32)
             elif key in _PER_COMP:
                 out[key] = v[k0:k1]
             else:                                   # per blend: images, weights, cw_idx, it0, prev_loss, n_iter, ...

@@ -14,7 +14,7 @@ import numpy as np
 from .component import ComponentTree, Component, BlendFlag
 from .observation import LowResObservation
 from . import _native
-from .source import PointSource, component_flags, _centroid_weight
+from .source import PointSource, MultiComponentSource, component_flags, _centroid_weight
 
 logger = logging.getLogger("scarlet.blend")
 
@@ -33,7 +33,7 @@ def _owner_of(blend):
 def pack_blends(blends):
     """Arrays for _native.Batch from Blend objects that share one frame shape."""
     C, Ny, Nx = blends[0].frame.shape
-    comp_off, sed, morph, cflags, center, shift, conv = [0], [], [], [], [], [], []
+    comp_off, sed, morph, cflags, center, shift, conv, src_first = [0], [], [], [], [], [], [], []
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
     spec_ids, cw_ids = {}, {}
     any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
@@ -47,14 +47,22 @@ def pack_blends(blends):
         obs = bl.observations[0]
         if isinstance(obs, LowResObservation) or obs._band_slice != slice(None):
             raise NotImplementedError("band-sliced / multi-resolution observations are not implemented yet")
+        last_src = None
         for s, c in _owner_of(bl):
             if c.prior is not None:
                 raise NotImplementedError("Prior callbacks cannot run inside the CUDA loop")
-            if isinstance(s, ComponentTree) and not isinstance(s, Component):
-                raise NotImplementedError("multi-component sources are not implemented in scarlet_b200 yet")
-            if not isinstance(s, PointSource) and type(s).update is not Component.update:
+            if isinstance(s, ComponentTree) and not isinstance(s, MultiComponentSource):
+                raise NotImplementedError("only MultiComponentSource trees can run inside the CUDA loop")
+            if isinstance(s, MultiComponentSource):
+                if type(s).update is not MultiComponentSource.update or type(c).update is not Component.update:
+                    raise NotImplementedError("custom Python update() overrides cannot run inside the CUDA loop")
+            elif not isinstance(s, PointSource) and type(s).update is not Component.update:
                 raise NotImplementedError("custom Python update() overrides cannot run inside the CUDA loop")
             cflags.append(component_flags(s, c))
+            if not (isinstance(s, ComponentTree) and len(sed) > comp_off[-1] and last_src is s):
+                first = len(sed)
+            last_src = s
+            src_first.append(first)
             sed.append(c._sed)
             morph.append(c._morph)
             center.append(getattr(s, "pixel_center", (Ny // 2, Nx // 2)))
@@ -87,7 +95,8 @@ def pack_blends(blends):
                 cflags=np.array(cflags), center=np.array(center), shift=np.array(shift, dtype=np.float64),
                 conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
-                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev))
+                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
+                src_first=np.array(src_first))
 
 
 def unpack_blends(blends, packed, out):
@@ -107,7 +116,7 @@ def unpack_blends(blends, packed, out):
                 c._last_sed, c._last_morph = c._sed.copy(), c._morph.copy()      # blend.py:180-182
             c.flags = (c.flags & ~(BlendFlag.SED_NOT_CONVERGED | BlendFlag.MORPH_NOT_CONVERGED)) | BlendFlag(int(out["conv"][k]))
             c.L_sed, c.L_morph = getattr(bl, "L_sed", 1), getattr(bl, "L_morph", 1)
-            if isinstance(s, PointSource):
+            if isinstance(s, (PointSource, MultiComponentSource)):
                 s.pixel_center = (int(out["center"][k, 0]), int(out["center"][k, 1]))
                 if s.symmetric:
                     s.shift = (float(out["shift"][k, 0]), float(out["shift"][k, 1]))

@@ -85,6 +85,7 @@ int ensure_globals() {
         CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         const int big = 200 * 1024;
         CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_source_center, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_symmetry, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_monotonic<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));

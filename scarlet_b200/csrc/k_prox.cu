@@ -83,32 +83,14 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
     }
 }
 
-extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
-scl_k_prox(SclProxArgs a)
-{
-    extern __shared__ __align__(16) float smem_f[];
-    const int k = a.comp_list[blockIdx.x];
-    const int b = a.comp_blend[k];
-    if (!a.active[b]) return;
-    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* X = smem_f + ((Nx + 4) & ~3);        // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
-    float* Z = X + ((N + 3) & ~3);
-    float* tab = Z + Ny * ((Nx + 3) & ~3);
-    __shared__ double red[32];
-    __shared__ int sc[2];
-    __shared__ double ss[2];
-    __shared__ float sm;
-    const unsigned fl = a.cflags[k];
-    long long tprev = a.phase_clk ? clock64() : 0;
-#define SCL_PHASE(i) do { if (a.phase_clk && threadIdx.x == 0) { long long t_ = clock64(); \
-        atomicAdd(a.phase_clk + (i), (unsigned long long)(t_ - tprev)); tprev = t_; } } while (0)
-    const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
-
-    // gradients of this component (chain rule through Component.get_model, component.py:166-167):
-    //   dS[p] = sum_c A[k,c] G[c,p]      dA[c] = sum_p G[c,p] S[k,p]
-    // and the morphology step (blend.py:94-96): S[k] -= (1/L_morph) dS
-    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
-    __shared__ float sAnew[SCL_MAX_BANDS];
+// Gradients of one component (chain rule through Component.get_model, component.py:166-167)
+//   dS[p] = sum_c A[k,c] G[c,p]      dA[c] = sum_p G[c,p] S[k,p]
+// and both gradient steps (blend.py:91-96): X = S[k] - (1/L_morph) dS, sAnew = A[k] - (1/L_sed) dA (honouring
+// fix_morph / fix_sed).  Without G (construction-time pass) X = S[k], sAnew = A[k].  All threads of the CTA;
+// the caller synchronises before reading sAnew.
+__device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, int b, unsigned fl, float* X,
+                                                   double (*sdA)[SCL_MAX_BANDS], float* sAnew) {
+    const int N = a.Ny * a.Nx, C = a.C;
     {
         const float* Sin = a.S + (size_t)k * N;
         if (a.G && !(SCL_EXP & 16)) {
@@ -143,6 +125,33 @@ scl_k_prox(SclProxArgs a)
             if (threadIdx.x < C) sAnew[threadIdx.x] = a.A[(size_t)k * C + threadIdx.x];
         }
     }
+}
+
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
+scl_k_prox(SclProxArgs a)
+{
+    extern __shared__ __align__(16) float smem_f[];
+    const int k = a.comp_list[blockIdx.x];
+    const int b = a.comp_blend[k];
+    if (!a.active[b]) return;
+    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
+    float* X = smem_f + ((Nx + 4) & ~3);        // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
+    float* Z = X + ((N + 3) & ~3);
+    float* tab = Z + Ny * ((Nx + 3) & ~3);
+    __shared__ double red[32];
+    __shared__ int sc[2];
+    __shared__ double ss[2];
+    __shared__ float sm;
+    const unsigned fl = a.cflags[k];
+    long long tprev = a.phase_clk ? clock64() : 0;
+#define SCL_PHASE(i) do { if (a.phase_clk && threadIdx.x == 0) { long long t_ = clock64(); \
+        atomicAdd(a.phase_clk + (i), (unsigned long long)(t_ - tprev)); tprev = t_; } } while (0)
+    const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
+
+    // gradient steps of this component
+    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
+    __shared__ float sAnew[SCL_MAX_BANDS];
+    scl_component_step(a, k, b, fl, X, sdA, sAnew);
     if (threadIdx.x == 0) {
         sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
         ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
@@ -151,10 +160,13 @@ scl_k_prox(SclProxArgs a)
     SCL_PHASE(0);      // gradient step
 
     if (fl & SCL_F_CONSTRAINED) {
-        scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
+        // components of a multi-component source: centre and shift were measured on the source's combined
+        // morphology by scl_k_source_center just before this launch
+        const bool own_center = !(fl & SCL_F_SHARED_CENTER);
+        if (own_center) scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
         __syncthreads();
         if (fl & SCL_F_SYMMETRIC) {
-            if (it % 5 == 0) {
+            if (own_center && it % 5 == 0) {
                 const float* psf = a.cw + (size_t)a.cw_idx[b] * a.ph * a.pw;
                 int cy = sc[0], cx = sc[1];
                 __syncthreads();
@@ -254,6 +266,64 @@ scl_k_prox(SclProxArgs a)
     }
     SCL_PHASE(4);      // positivity, normalisation, write-back, convergence
 #undef SCL_PHASE
+}
+
+// K2b: MultiComponentSource.update, first half (source.py:605-627).  One CTA per multi-component source:
+//   _morph = sum_k morph_k * sum(sed_k)  over the source's components, AFTER this iteration's gradient steps
+//   pixel_center = max_pixel(_morph, pixel_center);  every 5th iteration (symmetric sources):
+//   pixel_center, shift = psf_weighted_centroid(_morph, weight, pixel_center)
+// and writes (center, shift) to every component of the source, where K3 picks them up (SCL_F_SHARED_CENTER).
+// The stepped morphologies/SEDs are recomputed here with K3's own routine (same thread partition, same
+// reduction order, hence the same bits), since K3 keeps them in shared memory only.
+// dynamic smem: as scl_k_prox (M [N] in the X slot, the stepped component in the Z slot)
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
+scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
+{
+    extern __shared__ __align__(16) float smem_s[];
+    const int k0 = msrc[2 * blockIdx.x], n = msrc[2 * blockIdx.x + 1];
+    const int b = a.comp_blend[k0];
+    if (!a.active[b]) return;
+    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
+    float* M = smem_s + ((Nx + 4) & ~3);
+    float* Xk = M + ((N + 3) & ~3);
+    __shared__ double red[32];
+    __shared__ int sc[2];
+    __shared__ double ss[2];
+    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
+    __shared__ float sAnew[SCL_MAX_BANDS];
+    const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;
+    const unsigned fl0 = a.cflags[k0];
+    for (int j = 0; j < n; j++) {
+        const int k = k0 + j;
+        scl_component_step(a, k, b, a.cflags[k], Xk, sdA, sAnew);
+        __syncthreads();
+        float ssum = 0.f;                                    // c.sed.sum(), float32, band order
+        for (int c = 0; c < C; c++) ssum = __fadd_rn(ssum, sAnew[c]);
+        for (int p = threadIdx.x; p < N; p += blockDim.x) {
+            const float t = __fmul_rn(Xk[p], ssum);
+            M[p] = (j == 0) ? t : __fadd_rn(M[p], t);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        sc[0] = a.center[2 * k0]; sc[1] = a.center[2 * k0 + 1];
+        ss[0] = a.shift[2 * k0]; ss[1] = a.shift[2 * k0 + 1];
+    }
+    __syncthreads();
+    scl_max_pixel(M, Ny, Nx, sc[0], sc[1], sc);
+    __syncthreads();
+    if ((fl0 & SCL_F_SYMMETRIC) && it % 5 == 0) {
+        const float* psf = a.cw + (size_t)a.cw_idx[b] * a.ph * a.pw;
+        int cy = sc[0], cx = sc[1];
+        __syncthreads();
+        scl_centroid(M, Ny, Nx, psf, a.ph, a.pw, cy, cx, sc, ss, red);
+    }
+    __syncthreads();
+    if (threadIdx.x < n) {
+        const int k = k0 + threadIdx.x;
+        a.center[2 * k] = sc[0]; a.center[2 * k + 1] = sc[1];
+        a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
+    }
 }
 
 // K4: one thread per listed blend.  blend.py:157-176: never converged before it > 1.

@@ -166,6 +166,13 @@ def component_flags(source, component):
             f |= _native.F_SYMMETRIC
         if source.monotonic:
             f |= _native.F_MONOTONIC
+    elif isinstance(source, MultiComponentSource):
+        # source.py:605-641: one centre per source; its plain Components carry no `.shift` (soft symmetry)
+        f |= _native.F_CONSTRAINED | _native.F_SHARED_CENTER
+        if source.symmetric:
+            f |= _native.F_SYMMETRIC
+        if source.monotonic:
+            f |= _native.F_MONOTONIC
     if component.fix_sed:
         f |= _native.F_FIX_SED
     if component.fix_morph:
@@ -174,8 +181,9 @@ def component_flags(source, component):
 
 
 def constrain_sources(sources, it=0):
-    """Run `update()` (source.py:402-440) once on the device for a list of PointSource-like sources that share a
-    frame shape, and write the results back (used at construction, where it = 0)."""
+    """Run `update()` (source.py:402-440,605-641) once on the device for a list of PointSource-like or
+    multi-component sources that share a frame shape, and write the results back (used at construction,
+    where it = 0).  Every source is its own one-blend batch entry."""
     if not sources:
         return
     if it != 0:
@@ -185,21 +193,27 @@ def constrain_sources(sources, it=0):
     C, Ny, Nx = frame.shape
     n = len(sources)
     cw = np.asarray(_centroid_weight(frame), dtype=np.float32)
+    comps = [(s, c) for s in sources for c in (s.components if isinstance(s, ComponentTree) else [s])]
+    counts = [len(s.components) if isinstance(s, ComponentTree) else 1 for s in sources]
+    off = np.concatenate([[0], np.cumsum(counts)])
     bt = _native.Batch(
-        C, Ny, Nx, comp_off=np.arange(n + 1), sed=np.array([s._sed for s in sources]),
-        morph=np.array([s._morph for s in sources]), cflags=[component_flags(s, s) for s in sources],
-        center=[s.pixel_center for s in sources], shift=[getattr(s, "shift", (0., 0.)) for s in sources],
-        conv=[s.flags.value for s in sources], images=np.zeros((n, C, Ny, Nx), np.float32), weights=None,
-        kernel_spec=None, ker_idx=-np.ones(n * C), cw=cw[None], cw_idx=np.zeros(n))
+        C, Ny, Nx, comp_off=off, sed=np.array([c._sed for _, c in comps]),
+        morph=np.array([c._morph for _, c in comps]), cflags=[component_flags(s, c) for s, c in comps],
+        center=[s.pixel_center for s, _ in comps], shift=[getattr(s, "shift", (0., 0.)) for s, _ in comps],
+        conv=[c.flags.value for _, c in comps], images=np.zeros((n, C, Ny, Nx), np.float32), weights=None,
+        kernel_spec=None, ker_idx=-np.ones(n * C), cw=cw[None], cw_idx=np.zeros(n),
+        src_first=np.repeat(off[:-1], counts))
     bt.constrain()
     out = bt.download()
     bt.close()
     for i, s in enumerate(sources):
-        s._sed = out["sed"][i].astype(frame.dtype)
-        s._morph = out["morph"][i].astype(frame.dtype)
-        s.pixel_center = (int(out["center"][i, 0]), int(out["center"][i, 1]))
+        for j, c in enumerate(s.components if isinstance(s, ComponentTree) else [s]):
+            c._sed = out["sed"][off[i] + j].astype(frame.dtype)
+            c._morph = out["morph"][off[i] + j].astype(frame.dtype)
+        k = off[i]
+        s.pixel_center = (int(out["center"][k, 0]), int(out["center"][k, 1]))
         if s.symmetric:
-            s.shift = (float(out["shift"][i, 0]), float(out["shift"][i, 1]))
+            s.shift = (float(out["shift"][k, 0]), float(out["shift"][k, 1]))
 
 
 class RandomSource(Component):
@@ -313,9 +327,10 @@ class CombinedExtendedSource(PointSource):
 
 
 class MultiComponentSource(ComponentTree):
-    """Extended source with vertically layered components (source.py:551-641).
-    Initialisation matches the reference; its joint-centre update schedule is not yet available inside the
-    CUDA loop, so `Blend.fit` rejects it."""
+    """Extended source with vertically layered components (source.py:551-641).  The joint-centre update
+    schedule runs on the device: scl_k_source_center measures the centre on the flux-weighted sum of the
+    components, the constraint kernel applies symmetry / monotonicity / positivity / normalisation per
+    component with that centre (SCL_SHARED_CENTER)."""
 
     def __init__(self, frame, sky_coord, observation, bg_rms, thresh=1, flux_percentiles=None,
                  symmetric=True, monotonic=True, center_step=5, delay_thresh=10, **component_kwargs):
@@ -329,6 +344,10 @@ class MultiComponentSource(ComponentTree):
         super().__init__([Component(frame, seds[k], morphs[k]) for k in range(len(seds))])
         if self.symmetric:
             self._centroid_weight = _centroid_weight(self.frame)
+        # ensure adherence to constraints (source.py:600-601)
+        self.update()
 
     def update(self):
-        raise NotImplementedError("MultiComponentSource.update is not implemented in scarlet_b200 yet")
+        it = 0 if self._parent is None else self._parent.it
+        constrain_sources([self], it)
+        return self

@@ -26,6 +26,20 @@ def npz_blend(tag, dtype=np.float32):
     return frame, obs, srcs, rb.Blend(srcs, obs)
 
 
+def multi_blend(dtype=np.float32):
+    """config 1 with its first rows as MultiComponentSource (fixture ref_golden_multi.npz), oracle objects."""
+    d = np.load(os.path.join(GOLD, "hsc_cosmos_inputs.npz"))
+    g = np.load(os.path.join(GOLD, "ref_golden_multi.npz"))
+    images, psfs = d["images"], d["psfs"]
+    mpsf = rb.generate_psf_image(rb.gaussian, psfs[0].shape, sigma=.9)
+    frame = rb.Frame(images.shape, psfs=mpsf[None], dtype=dtype)
+    obs = rb.Observation(images, psfs=psfs).match(frame)
+    bg = np.ones(len(images), dtype=images.dtype) * float(d["bg_rms"])
+    srcs = [(rb.MultiComponentSource if i < int(g["n_multi"]) else rb.ExtendedSource)(frame, (y, x), obs, bg)
+            for i, (y, x) in enumerate(d["coords"])]
+    return g, frame, obs, srcs, rb.Blend(srcs, obs)
+
+
 def synthetic_blend(seed, C=5, Ny=64, Nx=64, kmin=2, kmax=8, psf_size=41, dtype=np.float32, _cache={}):
     """One synthetic blend of BASELINE config 3, oracle objects."""
     rng = np.random.default_rng(20260411 + seed)
@@ -74,13 +88,14 @@ def pack(blends):
     """Arrays for _native.Batch from oracle Blend objects sharing one frame shape."""
     from scarlet_b200 import _native as nat
     C, Ny, Nx = blends[0].frame.shape
-    comp_off, sed, morph, cflags, center, shift, conv = [0], [], [], [], [], [], []
+    comp_off, sed, morph, cflags, center, shift, conv, src_first = [0], [], [], [], [], [], [], []
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
     spec_cache, cw_cache = {}, {}
     any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
     for bl in blends:
         obs = bl.observations[0]
         for s in bl.sources:
+            first = len(sed)
             for c in s.components:
                 f = 0
                 if isinstance(s, rb.PointSource):
@@ -89,6 +104,13 @@ def pack(blends):
                         f |= nat.F_SYMMETRIC
                     if s.monotonic:
                         f |= nat.F_MONOTONIC
+                elif isinstance(s, rb.MultiComponentSource):
+                    f |= nat.F_CONSTRAINED | nat.F_SHARED_CENTER
+                    if s.symmetric:
+                        f |= nat.F_SYMMETRIC
+                    if s.monotonic:
+                        f |= nat.F_MONOTONIC
+                src_first.append(first)
                 if c.fix_sed:
                     f |= nat.F_FIX_SED
                 if c.fix_morph:
@@ -124,4 +146,5 @@ def pack(blends):
                 cflags=np.array(cflags), center=np.array(center), shift=np.array(shift, dtype=np.float64),
                 conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
-                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev))
+                cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
+                src_first=np.array(src_first))

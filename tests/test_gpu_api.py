@@ -60,6 +60,31 @@ def test_quickstart_workflow(scarlet, golden, tag):
     assert abs(obs.get_loss(blend.get_model()) / blend.mse[-1] - 1) < .2
 
 
+def test_multicomponent_source_workflow(scarlet):
+    """MultiComponentSource (source.py:537-641) through the drop-in surface: construction (init + update at it = 0)
+    and Blend.fit, against the reference's own run (tests/golden/make_golden_multi.py)."""
+    d = np.load(os.path.join(GOLD, "hsc_cosmos_inputs.npz"))
+    g = np.load(os.path.join(GOLD, "ref_golden_multi.npz"))
+    images, psfs = d["images"], d["psfs"]
+    mpsf = scarlet.psf.generate_psf_image(scarlet.psf.gaussian, psfs[0].shape, sigma=.9).image
+    frame = scarlet.Frame(images.shape, psfs=mpsf[None])
+    obs = scarlet.Observation(images, psfs=psfs).match(frame)
+    bg = np.ones(len(images), dtype=images.dtype) * float(d["bg_rms"])
+    srcs = [(scarlet.MultiComponentSource if i < int(g["n_multi"]) else scarlet.ExtendedSource)(frame, (y, x), obs, bg)
+            for i, (y, x) in enumerate(d["coords"])]
+    assert [getattr(s, "n_components", 1) for s in srcs] == list(g["n_comp"])
+    blend = scarlet.Blend(srcs, obs)
+    assert_allclose([c.sed for c in blend.components], g["init_seds"], rtol=2e-6)
+    assert_allclose([c.morph for c in blend.components], g["init_morphs"], rtol=0, atol=3e-6)
+    assert_array_equal([s.pixel_center for s in srcs], g["init_centers"])
+    blend.fit(int(g["max_iter"]))
+    assert blend.it == len(g["mse"])
+    assert blend.converged
+    assert_allclose(blend.mse, g["mse"], rtol=5e-5)
+    assert_array_equal([s.pixel_center for s in srcs], g["centers"])
+    assert_allclose(blend.get_model(), g["model"], rtol=0, atol=5e-5 * np.abs(g["model"]).max())
+
+
 def test_fit_again_continues(scarlet):
     frame, obs, srcs, blend = _scene(scarlet, "hsc")
     blend.fit(3)

@@ -35,7 +35,8 @@ def _lockstep(nat, blend, n_steps, e_rel=1e-2):
         assert_allclose(out["logL"][0, 0], blend.mse[-1], rtol=REL)
         assert_allclose(out["lipschitz"][0], [blend.L_sed, blend.L_morph], rtol=2e-6)
         ref_c = np.array([getattr(s, "pixel_center", (0, 0)) for s in blend.sources for _ in s.components])
-        con = np.array([isinstance(s, helpers.rb.PointSource) for s in blend.sources for _ in s.components])
+        con = np.array([isinstance(s, (helpers.rb.PointSource, helpers.rb.MultiComponentSource))
+                        for s in blend.sources for _ in s.components])
         assert_array_equal(out["center"][con], ref_c[con])                      # index work: exact
         ref_s = np.array([getattr(s, "shift", (0, 0)) for s in blend.sources for _ in s.components], dtype=np.float64)
         assert_allclose(out["shift"][con], ref_s[con], rtol=0, atol=5e-6)
@@ -54,6 +55,31 @@ def test_lockstep_npz(nat, tag):
     """configs 1 and 2, every iteration until the oracle converges"""
     _, _, _, blend = helpers.npz_blend(tag)
     _lockstep(nat, blend, 60)
+
+
+def test_lockstep_multicomponent(nat):
+    """MultiComponentSource.update inside the loop (source.py:605-641): the joint centre of a source is measured on
+    the flux-weighted sum of its stepped components (scl_k_source_center), every iteration vs the oracle."""
+    _, _, _, _, blend = helpers.multi_blend()
+    _lockstep(nat, blend, 40)
+
+
+def test_multicomponent_free_running_vs_reference(nat):
+    """The same scene free-running against the reference's own run (tests/golden/make_golden_multi.py)."""
+    g, _, _, srcs, blend = helpers.multi_blend()
+    p = helpers.pack([blend])
+    assert_allclose(p["morph"], g["init_morphs"], rtol=0, atol=2e-6)
+    bt = nat.Batch(**p)
+    bt.fit(int(g["max_iter"]), 1e-2)
+    out = bt.download()
+    bt.close()
+    n = int(out["n_iter"][0])
+    assert n == len(g["mse"])
+    assert_allclose(out["logL"][0, :n], g["mse"], rtol=5 * REL)
+    first = np.concatenate([[0], np.cumsum(g["n_comp"])])[:-1]
+    assert_array_equal(out["center"][first], g["centers"])
+    model = _model(out, 0, len(out["sed"]))
+    assert_allclose(model, g["model"], rtol=0, atol=5 * REL * np.abs(g["model"]).max())
 
 
 @pytest.mark.parametrize("seed", [0, 1, 2])

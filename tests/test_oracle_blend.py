@@ -88,6 +88,35 @@ def test_npz_fit_vs_reference(golden, tag):
                     atol=2e-5 * np.abs(golden[tag + "_model"]).max())
 
 
+def _multi_blend(dtype=np.float32):
+    """config 1 with the first rows as MultiComponentSource, like tests/golden/make_golden_multi.py"""
+    d = np.load(os.path.join(DATA, "hsc_cosmos_inputs.npz"))
+    g = np.load(os.path.join(DATA, "ref_golden_multi.npz"))
+    images, psfs = d["images"], d["psfs"]
+    mpsf = rb.generate_psf_image(rb.gaussian, psfs[0].shape, sigma=.9)
+    frame = rb.Frame(images.shape, psfs=mpsf[None], dtype=dtype)
+    obs = rb.Observation(images, psfs=psfs).match(frame)
+    bg = np.ones(len(images), dtype=images.dtype) * float(d["bg_rms"])
+    srcs = [(rb.MultiComponentSource if i < int(g["n_multi"]) else rb.ExtendedSource)(frame, (y, x), obs, bg)
+            for i, (y, x) in enumerate(d["coords"])]
+    return g, srcs, rb.Blend(srcs, obs)
+
+
+def test_multicomponent_fit_vs_reference():
+    """MultiComponentSource (source.py:537-641): init and the joint-centre update schedule inside the loop,
+    against the reference itself (fixture ref_golden_multi.npz)."""
+    g, srcs, blend = _multi_blend()
+    assert [len(s.components) for s in srcs] == list(g["n_comp"])
+    assert_allclose(np.array([c.sed for c in blend.components]), g["init_seds"], rtol=2e-6)
+    assert_allclose(np.array([c.morph for c in blend.components]), g["init_morphs"], rtol=0, atol=2e-6)
+    assert_array_equal(np.array([s.pixel_center for s in srcs]), g["init_centers"])
+    blend.fit(int(g["max_iter"]))
+    assert blend.it == len(g["mse"])
+    assert_allclose(np.array(blend.mse, dtype=np.float64), g["mse"], rtol=5e-6)
+    assert_array_equal(np.array([s.pixel_center for s in srcs]), g["centers"])
+    assert_allclose(blend.get_model(), g["model"], rtol=0, atol=2e-5 * np.abs(g["model"]).max())
+
+
 def test_adjoint_vs_torch_autograd(golden):
     """The analytic gradient that replaces autograd.grad(Blend._loss) (blend.py:44-45)."""
     import torch
