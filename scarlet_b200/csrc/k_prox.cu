@@ -86,10 +86,10 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
 // Gradients of one component (chain rule through Component.get_model, component.py:166-167)
 //   dS[p] = sum_c A[k,c] G[c,p]      dA[c] = sum_p G[c,p] S[k,p]
 // and both gradient steps (blend.py:91-96): X = S[k] - (1/L_morph) dS, sAnew = A[k] - (1/L_sed) dA (honouring
-// fix_morph / fix_sed).  Without G (construction-time pass) X = S[k], sAnew = A[k].  All threads of the CTA;
-// the caller synchronises before reading sAnew.
+// fix_morph / fix_sed); sAold = A[k] as read.  Without G (construction-time pass) X = S[k], sAnew = A[k].  All
+// threads of the CTA; the caller synchronises before reading sAnew / sAold.
 __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, int b, unsigned fl, float* X,
-                                                   double (*sdA)[SCL_MAX_BANDS], float* sAnew) {
+                                                   double (*sdA)[SCL_MAX_BANDS], float* sAnew, float* sAold) {
     const int N = a.Ny * a.Nx, C = a.C;
     {
         const float* Sin = a.S + (size_t)k * N;
@@ -117,12 +117,13 @@ __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, 
                 double v = 0.0;
                 for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][threadIdx.x];
                 float an = a.A[(size_t)k * C + threadIdx.x];
+                sAold[threadIdx.x] = an;
                 if (!(fl & SCL_F_FIX_SED)) an = an - (1.0f / a.lips[2 * b]) * (float)v;
                 sAnew[threadIdx.x] = an;
             }
         } else {
             for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
-            if (threadIdx.x < C) sAnew[threadIdx.x] = a.A[(size_t)k * C + threadIdx.x];
+            if (threadIdx.x < C) sAnew[threadIdx.x] = sAold[threadIdx.x] = a.A[(size_t)k * C + threadIdx.x];
         }
     }
 }
@@ -150,8 +151,8 @@ scl_k_prox(SclProxArgs a)
 
     // gradient steps of this component
     __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
-    __shared__ float sAnew[SCL_MAX_BANDS];
-    scl_component_step(a, k, b, fl, X, sdA, sAnew);
+    __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
+    scl_component_step(a, k, b, fl, X, sdA, sAnew, sAold);
     if (threadIdx.x == 0) {
         sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
         ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
@@ -241,28 +242,37 @@ scl_k_prox(SclProxArgs a)
     }
     d2 = block_sum<double>(d2, red);
     n2 = block_sum<double>(n2, red);
-    if (threadIdx.x == 0) {
-        double ad2 = 0.0, an2 = 0.0;
-        for (int c = 0; c < C; c++) {
+    if (threadIdx.x < 32) {
+        // SED: positivity + morph_max normalisation (update.py:27-32,62-65) and its convergence sums, one lane per
+        // band (the previous SED is still in shared memory); lane 0 adds the bands in band order
+        const int c = threadIdx.x;
+        double ad = 0.0, an = 0.0;
+        if (c < C) {
             float v = sAnew[c];
             if (constrained) {
                 if (v < 0.f) v = 0.f;
                 v = v * norm;
             }
-            float old = a.A[(size_t)k * C + c];
-            double df = (double)old - (double)v;
-            ad2 += df * df;
-            an2 += (double)v * (double)v;
+            const double df = (double)sAold[c] - (double)v;
+            ad = df * df;
+            an = (double)v * (double)v;
             a.A[(size_t)k * C + c] = v;
         }
-        if (it > 1) {
-            int f = 0;
-            if (!(ad2 <= a.e_rel2 * an2)) f |= SCL_SED_NOT_CONVERGED;
-            if (!(d2 <= a.e_rel2 * n2)) f |= SCL_MORPH_NOT_CONVERGED;
-            a.conv[k] = f;
+        double ad2 = 0.0, an2 = 0.0;
+        for (int cc = 0; cc < C; cc++) {
+            ad2 += __shfl_sync(0xffffffffu, ad, cc);
+            an2 += __shfl_sync(0xffffffffu, an, cc);
         }
-        a.center[2 * k] = sc[0]; a.center[2 * k + 1] = sc[1];
-        a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
+        if (threadIdx.x == 0) {
+            if (it > 1) {
+                int f = 0;
+                if (!(ad2 <= a.e_rel2 * an2)) f |= SCL_SED_NOT_CONVERGED;
+                if (!(d2 <= a.e_rel2 * n2)) f |= SCL_MORPH_NOT_CONVERGED;
+                a.conv[k] = f;
+            }
+            a.center[2 * k] = sc[0]; a.center[2 * k + 1] = sc[1];
+            a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
+        }
     }
     SCL_PHASE(4);      // positivity, normalisation, write-back, convergence
 #undef SCL_PHASE
@@ -290,12 +300,12 @@ scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
     __shared__ int sc[2];
     __shared__ double ss[2];
     __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
-    __shared__ float sAnew[SCL_MAX_BANDS];
+    __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;
     const unsigned fl0 = a.cflags[k0];
     for (int j = 0; j < n; j++) {
         const int k = k0 + j;
-        scl_component_step(a, k, b, a.cflags[k], Xk, sdA, sAnew);
+        scl_component_step(a, k, b, a.cflags[k], Xk, sdA, sAnew, sAold);
         __syncthreads();
         float ssum = 0.f;                                    // c.sed.sum(), float32, band order
         for (int c = 0; c < C; c++) ssum = __fadd_rn(ssum, sAnew[c]);
