@@ -60,7 +60,7 @@ def _cpu_worker(args):
     return nb, tot_it, tot_t
 
 
-def cpu_baseline(per_worker=6, max_workers=32, first_index=0):
+def cpu_baseline(per_worker=24, max_workers=32, first_index=0):
     """Oracle Blend.fit on a bounded sample of the same workload, one process per host core."""
     import multiprocessing as mp
     from scarlet_b200 import synth
@@ -332,7 +332,7 @@ def main():
     ap.add_argument("--check-every", type=int, default=8)
     ap.add_argument("--streams", type=int, default=1, help="independently driven chunks per GPU (BlendBatch streams=)")
     ap.add_argument("--roofline-iters", type=int, default=40)
-    ap.add_argument("--ref-per-worker", type=int, default=6)
+    ap.add_argument("--ref-per-worker", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
