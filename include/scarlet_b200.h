@@ -92,7 +92,7 @@ typedef struct {
     int32_t C, Ny, Nx;              /* frame shape shared by the batch */
     const int32_t* comp_off;        /* [B+1] component range of each blend */
     const float* sed;               /* [Ktot][C] */
-    const float* morph;             /* [Ktot][Ny*Nx] */
+    const float* morph;             /* [Ktot][Ny*Nx]; NULL = zeros (morphologies come from scl_batch_init_extended) */
     const uint32_t* cflags;         /* [Ktot] SCL_* flags */
     const int32_t* center;          /* [Ktot][2] pixel_center (y, x) */
     const double* shift;            /* [Ktot][2] (dy, dx) */
@@ -128,6 +128,13 @@ int scl_batch_fit(scl_batch* batch, int max_iter, double e_rel, int approximate_
 /* The constraint pass every source runs once at construction (`self.update()` with it = 0, source.py:400,492):
  * max_pixel, centroid + shift, symmetry, monotonicity, positivity, normalisation on the batch's current state. */
 int scl_batch_constrain(scl_batch* batch, void* stream);
+/* init_extended_source (source.py:139-180) for every component of the batch, on the device, from the batch's own
+ * images and centres, in float32: detection coadd with per-component band weights cw [Ktot][C] (sed/bg_rms^2 on the
+ * bands with sed > 0, else 0) and jacobian jac [Ktot] (source.py:101-136), sdss symmetry, monotonicity (thresh .1),
+ * noise cut at cutoff [Ktot] and peak normalisation; overwrites the batch's morphologies.  ok [Ktot] (host, out):
+ * 0 where no pixel survives the cut (the reference raises SourceInitError, source.py:171-173). */
+int scl_batch_init_extended(scl_batch* batch, const float* cw, const float* jac, const float* cutoff,
+                            int symmetric, int monotonic, int32_t* ok, void* stream);
 /* Copy results back.  Any pointer may be NULL.  logL: [B][max_iter of the last fit] (Blend.mse entries appended
  * by that fit; n_iter[b] of them valid); active[b] == 0 <=> blend b converged. */
 int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* center, double* shift, int32_t* conv,

@@ -300,7 +300,7 @@ class Batch:
         a = dict(
             comp_off=comp_off,
             sed=ca(sed, dtype=np.float32).reshape(K, self.C),
-            morph=ca(morph, dtype=np.float32).reshape(K, N),
+            morph=None if morph is None else ca(morph, dtype=np.float32).reshape(K, N),
             cflags=ca(cflags, dtype=np.uint32).reshape(K),
             center=ca(center, dtype=np.int32).reshape(K, 2),
             shift=ca(shift, dtype=np.float64).reshape(K, 2),
@@ -345,6 +345,17 @@ class Batch:
                                    ctypes.byref(nl), c_void_p(self.stream)))
         self.max_iter = int(max_iter)
         return dict(device_ms=ms.value, kernel_ms=[float(v) for v in k1], steps=nk1.value, launches=nl.value)
+
+    def init_extended(self, cw, jac, cutoff, symmetric=True, monotonic=True):
+        """init_extended_source on the device for every component (see include/scarlet_b200.h); returns ok [K] bool."""
+        ca = np.ascontiguousarray
+        cw = ca(cw, dtype=np.float32).reshape(self.K, self.C)
+        jac = ca(jac, dtype=np.float32).reshape(self.K)
+        cutoff = ca(cutoff, dtype=np.float32).reshape(self.K)
+        ok = np.zeros(self.K, np.int32)
+        _check(lib().scl_batch_init_extended(self._h, _p(cw), _p(jac), _p(cutoff), int(bool(symmetric)),
+                                             int(bool(monotonic)), _p(ok), c_void_p(self.stream)))
+        return ok.astype(bool)
 
     def constrain(self):
         """One `update()` pass with it = 0 on every component (what sources run at construction)."""

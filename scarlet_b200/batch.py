@@ -2,7 +2,8 @@
 
 The reference has no batch notion (`Blend.fit` handles one scene, blend.py:65-102); this is the additive entry
 point for BASELINE configs 3-4: the scene catalogue goes in as arrays, every source is initialised exactly as
-`ExtendedSource.__init__` would (source.py:139-180,444-492) with the array operators batched on the device,
+`ExtendedSource.__init__` would (source.py:139-180,444-492) on the device (`scl_batch_init_extended`: coadd, sdss
+symmetry, monotonicity, noise cut, normalisation; only the [K, C] SED / weight arithmetic stays on the host),
 and `fit` runs `Blend.fit` for all blends in one launch sequence through the C ABI.
 """
 from concurrent.futures import ThreadPoolExecutor
@@ -10,15 +11,8 @@ from concurrent.futures import ThreadPoolExecutor
 import numpy as np
 
 from . import _native, fft
-from .source import build_detection_coadd, init_extended_morphs
 
 _FLAGS_EXTENDED = (_native.F_CONSTRAINED | _native.F_KSPACE | _native.F_SYMMETRIC | _native.F_MONOTONIC)
-
-
-class _Images:
-    """What build_detection_coadd reads from an Observation."""
-    def __init__(self, images):
-        self.images = images
 
 
 _PER_COMP = ("sed", "morph", "cflags", "center", "shift", "conv")
@@ -155,53 +149,74 @@ class BlendBatch:
         peak_obs = obs_psfs.max(axis=(1, 2))
         peak_mod = mod_psfs[0].max()
 
-        # ---- per-source SED + detection coadd (source.py:41-71,101-136), host
-        seds, detects, cutoffs, ctrs, owner = [], [], [], [], []
-        for b in range(B):
-            ob = _Images(images[b])
-            for (y, x) in np.asarray(centers[b]).reshape(-1, 2):
-                sed = images[b, :, int(y), int(x)].copy()
-                sed /= peak_obs
-                sed = sed * peak_mod
-                d, cut = build_detection_coadd(sed, bg_rms, ob, thresh)
-                seds.append(sed); detects.append(d); cutoffs.append(cut); ctrs.append((int(y), int(x))); owner.append(b)
-        # ---- sdss symmetry, monotonic(thresh=.1) on the device, noise cut, peak normalisation (source.py:160-179)
-        morphs = np.empty((len(seds), Ny, Nx), np.float32)
-        ok = np.zeros(len(seds), bool)
-        step = 8192
-        for s in range(0, len(seds), step):
-            m, o = init_extended_morphs(np.array(detects[s:s + step]), cutoffs[s:s + step], ctrs[s:s + step], True, monotonic)
-            morphs[s:s + step] = m
-            ok[s:s + step] = o
-        self.n_failed = int((~ok).sum())
-        owner = np.array(owner)
-        keep_src = np.nonzero(ok)[0]
-        counts = np.bincount(owner[keep_src], minlength=B)
-        self.kept = np.nonzero(counts > 0)[0]
-        comp_off = np.concatenate([[0], np.cumsum(counts[self.kept])]).astype(np.int32)
-        K = len(keep_src)
+        # ---- per-source SED and coadd weights (source.py:41-71,101-136): [K, C] arrays, vectorised over all
+        # sources in the dtypes the reference's scalar code produces for float32 images / bg_rms
+        counts0 = np.array([len(np.asarray(c).reshape(-1, 2)) for c in centers], dtype=np.int64)
+        owner = np.repeat(np.arange(B), counts0)
+        ctr = (np.concatenate([np.asarray(c).reshape(-1, 2) for c in centers]).astype(np.int32)
+               if counts0.sum() else np.zeros((0, 2), np.int32))
+        sed = images[owner, :, ctr[:, 0], ctr[:, 1]].astype(np.float32)
+        sed /= np.asarray(peak_obs, dtype=np.float32)
+        sed = sed * np.float32(peak_mod)
+        if np.any(bg_rms <= 0):
+            raise ValueError("bg_rms must be greater than zero in all channels")
+        pos = sed > 0
+        bg2 = bg_rms ** 2
+        cwt = np.where(pos, sed / bg2, np.float32(0)).astype(np.float32)
+        jterm = np.where(pos, sed ** 2 / bg2, np.float32(0)).astype(np.float32)
+        cterm = (cwt ** 2 * bg2).astype(np.float32)
+        jac = np.zeros(len(sed), np.float32)
+        csum = np.zeros(len(sed), np.float32)
+        for c in range(C):                                  # band-order float32 sums, like np.array([...]).sum()
+            jac = jac + jterm[:, c]
+            csum = csum + cterm[:, c]
+        with np.errstate(divide="ignore", invalid="ignore"):
+            cutoff = (np.float32(thresh) * np.sqrt(csum) / jac).astype(np.float32)
+        # ---- morphologies on the device (source.py:139-180): coadd, sdss symmetry, monotonic(thresh=.1), noise cut,
+        # peak normalisation -- one CTA per candidate source on the batch's own images (scl_batch_init_extended)
+        Kc = len(sed)
         flags = _FLAGS_EXTENDED
         if not symmetric:
             flags &= ~_native.F_SYMMETRIC
         if not monotonic:
             flags &= ~_native.F_MONOTONIC
-        Bk = len(self.kept)
-        self.host = dict(
-            C=C, Ny=Ny, Nx=Nx, comp_off=comp_off,
-            sed=np.array(seds, dtype=np.float32).reshape(-1, C)[keep_src],
-            morph=morphs[keep_src],
-            cflags=np.full(K, flags, np.uint32),
-            center=np.array(ctrs, dtype=np.int32).reshape(-1, 2)[keep_src],
-            shift=np.zeros((K, 2), np.float64),
-            conv=np.full(K, 3, np.int32),
-            images=images if Bk == B else images[self.kept],
-            weights=None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)[self.kept],
-            kernel_spec=spec, ker_idx=np.tile(np.arange(C, dtype=np.int32), Bk),
-            cw=np.asarray(mod_psfs[0].image, dtype=np.float32)[None], cw_idx=np.zeros(Bk, np.int32),
-            it0=np.zeros(Bk, np.int32), prev_loss=np.zeros(Bk, np.float64))
+        wts = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+
+        def host_dict(keep_src, kept, morph):
+            cnt = np.bincount(owner[keep_src], minlength=B)[kept]
+            return dict(
+                C=C, Ny=Ny, Nx=Nx, comp_off=np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32),
+                sed=sed[keep_src], morph=morph, cflags=np.full(len(keep_src), flags, np.uint32),
+                center=ctr[keep_src], shift=np.zeros((len(keep_src), 2), np.float64),
+                conv=np.full(len(keep_src), 3, np.int32),
+                images=images if len(kept) == B else images[kept],
+                weights=None if wts is None else (wts if len(kept) == B else wts[kept]),
+                kernel_spec=spec, ker_idx=np.tile(np.arange(C, dtype=np.int32), len(kept)),
+                cw=np.asarray(mod_psfs[0].image, dtype=np.float32)[None], cw_idx=np.zeros(len(kept), np.int32),
+                it0=np.zeros(len(kept), np.int32), prev_loss=np.zeros(len(kept), np.float64))
+
+        has = np.nonzero(counts0 > 0)[0]
+        cand = host_dict(np.arange(Kc), has, None)
+        dev = _native.Batch(stream=stream, **cand)
+        ok = dev.init_extended(cwt, jac, cutoff, True, monotonic) if Kc else np.zeros(0, bool)
+        self.n_failed = int((~ok).sum())
+        keep_src = np.nonzero(ok)[0]
+        self.kept = np.nonzero(np.bincount(owner[keep_src], minlength=B) > 0)[0]
+        if self.n_failed == 0 and streams <= 1:
+            self.host = cand
+            self._dev = dev
+        else:
+            # sources without a pixel above the noise cut are dropped (source.py:171-173), and with them blends left
+            # without a source: rebuild the batch from the surviving candidates
+            morphs = dev.download(morph=True)["morph"]
+            dev.close()
+            self.host = host_dict(keep_src, self.kept, morphs[keep_src])
+            self._dev = None
+        Bk, K = len(self.kept), len(keep_src)
         self.B, self.K = Bk, K
         self.mse = [[] for _ in range(Bk)]
-        self._dev = _Chunks(streams, self.host) if streams > 1 else _native.Batch(stream=stream, **self.host)
+        if self._dev is None:
+            self._dev = _Chunks(streams, self.host) if streams > 1 else _native.Batch(stream=stream, **self.host)
         # first constraint pass, it = 0 (source.py:492)
         self._dev.constrain()
         self._pull(self._dev.download())

@@ -443,6 +443,69 @@ scl_k_mono_plan(int Ny, int Nx, int pbits, unsigned* __restrict__ npass, const u
     if (npass && threadIdx.x == 0) npass[blockIdx.x] = (unsigned)total;
 }
 
+// N1: init_extended_source on the device (source.py:101-180), one CTA per candidate source, in the frame's
+// float32 (what the reference computes in when images, sed and bg_rms are float32):
+//   detect = sum_c w[k,c] images[b,c] / jacobian[k]       (build_detection_coadd, source.py:101-136; w = sed/bg^2 on
+//            the bands with sed > 0 and 0 elsewhere; bands added in order, un-fused like np.einsum's loop)
+//   detect = min(detect, flip(detect)) on the largest window centred on the source      (prox_sdss_symmetry)
+//   monotonic sweep with thresh 0.1                                                      (source.py:165-166)
+//   morph = detect where detect > cutoff[k], else 0; no pixel left -> ok[k] = 0 (SourceInitError, source.py:171-173)
+//   morph /= morph[centre]                                                               (source.py:177-179)
+// and writes the morphology into S[k].  dynamic smem: as scl_k_prox
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
+scl_k_init_extended(const float* __restrict__ images, const int* __restrict__ comp_blend,
+                    const int* __restrict__ center, const float* __restrict__ cw, const float* __restrict__ jac,
+                    const float* __restrict__ cutoff, float* __restrict__ S, int* __restrict__ ok,
+                    int C, int Ny, int Nx, int symmetric, int monotonic,
+                    const float* __restrict__ wtab, const double* __restrict__ ctab, SclMonoPlan plan)
+{
+    extern __shared__ __align__(16) float smem_i[];
+    const int k = blockIdx.x, b = comp_blend[k], N = Ny * Nx;
+    float* X = smem_i + ((Nx + 4) & ~3);
+    float* Z = X + ((N + 3) & ~3);
+    __shared__ int any;
+    const int cy = center[2 * k], cx = center[2 * k + 1];
+    const float* img = images + (size_t)b * C * N;
+    float w[SCL_MAX_BANDS];
+#pragma unroll
+    for (int c = 0; c < SCL_MAX_BANDS; c++) w[c] = (c < C) ? cw[(size_t)k * C + c] : 0.f;
+    const float j = jac[k];
+    if (threadIdx.x == 0) any = 0;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        float d = 0.f;
+#pragma unroll
+        for (int c = 0; c < SCL_MAX_BANDS; c++)
+            if (c < C && w[c] != 0.f) d = __fadd_rn(d, __fmul_rn(w[c], img[(size_t)c * N + p]));
+        X[p] = __fdiv_rn(d, j);
+    }
+    __syncthreads();
+    if (symmetric) scl_flip_symmetry(X, Nx, scl_window(Ny, Nx, cy, cx), 1, 0.f);
+    if (monotonic) {
+        if (plan.pbits) {
+            if (threadIdx.x < 32) {
+                const unsigned f0 = plan.first[cy * Nx + cx], f1 = plan.first[cy * Nx + cx + 1];
+                scl_monotonic_f32_stream(X, Nx, plan.list + (size_t)f0 * 32, (int)(f1 - f0), plan.pbits, wtab, 0.1f, Z);
+            }
+            __syncthreads();
+        } else {
+            scl_monotonic<float, false>(X, Ny, Nx, cy, cx, wtab, ctab, 0.1f);
+        }
+    }
+    __syncthreads();
+    const float cut = cutoff[k];
+    int mine = 0;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) mine |= (X[p] > cut);
+    if (mine) any = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) ok[k] = any;
+    const float peak = (X[cy * Nx + cx] > cut) ? X[cy * Nx + cx] : 0.f;
+    float* out = S + (size_t)k * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        const float v = (X[p] > cut) ? X[p] : 0.f;
+        out[p] = any ? __fdiv_rn(v, peak) : 0.f;
+    }
+}
+
 // mode: 0 = kspace (shift required), 1 = soft(strength), 2 = sdss
 extern "C" __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_symmetry(float* __restrict__ imgs, const int* __restrict__ centers, const double* __restrict__ shifts,

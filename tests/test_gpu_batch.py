@@ -153,3 +153,35 @@ def test_chunked_streams_equal_single_batch():
     assert a["steps"] == 3
     one.close()
     many.close()
+
+
+def test_failed_sources_are_dropped_like_source_init_error():
+    """A catalogue position with no pixel above the noise cut raises SourceInitError in the reference
+    (source.py:171-173); the batch drops such sources (and blends left empty) and reports them, and the surviving
+    sources are initialised exactly as in a batch that never contained the bad ones."""
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    from oracle import ref_blend as rb
+    d = synth.make_blends(range(4), device="cpu")
+    images = d["images"].copy()
+    centers = [np.asarray(c).copy() for c in d["centers"]]
+    images[3] = 0.0                                            # blend 3: S/N << 1 at every catalogue position
+    images[3][:, centers[3][:, 0], centers[3][:, 1]] = 1e-3
+    # blend 1 gets one extra catalogue row on a faint corner pixel: monotonicity from there leaves nothing above the cut
+    images[1, :, 2, 2] = 1e-3
+    centers[1] = np.concatenate([centers[1], [[2, 2]]])
+    args = (d["psfs"], d["model_psf"])
+    bb = BlendBatch(images, *args, centers, d["bg_rms"], weights=d["weights"])
+    assert bb.n_failed == 1 + len(centers[3])
+    assert list(bb.kept) == [0, 1, 2]
+    # oracle: the bad row raises, the others build
+    frame = rb.Frame(images[1].shape, psfs=np.asarray(d["model_psf"]), dtype=np.float32)
+    obs = rb.Observation(images[1], psfs=np.asarray(d["psfs"])).match(frame)
+    with pytest.raises(rb.SourceInitError):
+        rb.ExtendedSource(frame, (2, 2), obs, np.asarray(d["bg_rms"], dtype=np.float32))
+    ref = BlendBatch(images[:3], *args, [centers[0], centers[1][:-1], centers[2]], d["bg_rms"], weights=d["weights"][:3])
+    assert ref.n_failed == 0
+    for k in ("comp_off", "sed", "morph", "center", "shift"):
+        assert_array_equal(bb.host[k], ref.host[k])
+    bb.close()
+    ref.close()
