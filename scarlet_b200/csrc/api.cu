@@ -132,7 +132,7 @@ int build_plans(int Ny, int Nx, Tables* t) {
     first[N] = (unsigned)run;
     if (run * 128 > kPlanBudget || run >= (1ull << 32)) return SCL_OK;
     CK(cudaMalloc(&t->pfirst, (N + 1) * sizeof(unsigned)));
-    CK(cudaMalloc(&t->plist, (size_t)(run ? run : 1) * 128));
+    CK(cudaMalloc(&t->plist, (size_t)(run + 4) * 128));          // + 4 passes: the sweep copies entries four passes at a time
     CK(cudaMemcpy(t->pfirst, first.data(), (N + 1) * sizeof(unsigned), cudaMemcpyHostToDevice));
     scl_k_mono_plan<<<N, SCL_THREADS, smem>>>(Ny, Nx, pbits, nullptr, t->pfirst, t->plist);
     CK(cudaGetLastError());

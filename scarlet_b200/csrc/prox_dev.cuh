@@ -383,8 +383,9 @@ struct SclMonoPlan {
     const unsigned* first;      // [N + 1] first pass of centre cy * Nx + cx
     int pbits;                  // bits of the pixel field; 0 = no plan for this shape (generic path)
 };
-// scratch of the streamed sweep: weights ring [R][2][32] float4, entry ring [2R][32]
-#define SCL_MONO_STREAM_BYTES (SCL_MONO_RING * 1024 + 2 * SCL_MONO_RING * 128)
+// scratch of the streamed sweep: weights ring [R][2][32] float4, entry ring [SCL_MONO_ENTRIES][32]
+#define SCL_MONO_ENTRIES 32     // passes of plan entries held in shared memory (power of two, multiple of 4, > R + 4)
+#define SCL_MONO_STREAM_BYTES (SCL_MONO_RING * 1024 + SCL_MONO_ENTRIES * 128)
 
 // Work areas of the plan builder (one CTA per centre)
 struct SclMonoWork {
@@ -464,40 +465,35 @@ __device__ void scl_mono_build(const SclMonoWork& wk, int Ny, int Nx, int cy, in
 #define SCL_MONO_IDLE 0xffffffffu
 __device__ SCL_STREAM_INLINE void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __restrict__ passes, int npass,
                                                       int pbits, const float* __restrict__ wt9, float thresh, void* scratch) {
-    constexpr int R = SCL_MONO_RING;
+    constexpr int R = SCL_MONO_RING, RL = SCL_MONO_ENTRIES;
     const float omt = 1.f - thresh;
     const int lane = threadIdx.x & 31;
     const unsigned pmask = (1u << pbits) - 1u;
     float4* ringW = reinterpret_cast<float4*>(scratch);
     unsigned* ringL = reinterpret_cast<unsigned*>(ringW + R * 64);
     const unsigned aW = (unsigned)__cvta_generic_to_shared(ringW) + lane * 16;
-    const unsigned aL = (unsigned)__cvta_generic_to_shared(ringL) + lane * 4;
+    const unsigned aL = (unsigned)__cvta_generic_to_shared(ringL) + lane * 16;
+    // Entries of passes q .. q+3 (q a multiple of 4) as ONE 16-byte copy per lane: the plan stores passes back to back,
+    // so the 512 bytes of four passes map 1:1 onto four consecutive ring slots.  (A copy instruction costs the warp
+    // ~100 cycles whatever it moves, so fewer, wider copies; .cg = past L1, measurably cheaper than .ca here.)  The
+    // quad may reach up to 3 passes beyond npass: the next centre's plan or the slack at the end of the list.
+    auto copy_entries4 = [&](int q) {
+        if (q < npass)
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n"
+                         :: "r"(aL + (q & (RL - 1)) * 128), "l"(passes + (size_t)q * 32 + lane * 4));
+    };
     // `dep` makes the compiler keep the copy after the ring reads it overwrites (no memory clobber: the copies may
     // otherwise be scheduled freely among the arithmetic)
-    auto copy_entries = [&](int pass, int slotL, unsigned dep) {
-        if (pass < npass)
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n"
-                         :: "r"(aL + slotL * 128), "l"(passes + (size_t)pass * 32 + lane), "r"(dep));
-    };
     auto copy_weights = [&](unsigned e, int slotW, float dep0, float dep1) {
         if (e != SCL_MONO_IDLE) {
             const float* wp = wt9 + (size_t)(e >> pbits) * 8;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024), "l"(wp), "f"(dep0));
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024 + 512), "l"(wp + 4), "f"(dep1));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024), "l"(wp), "f"(dep0));
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" :: "r"(aW + slotW * 1024 + 512), "l"(wp + 4), "f"(dep1));
         }
     };
-    // what a processed pass owes the pipeline: weights of pass + R into its weight slot, entries of pass + 2R into
-    // its entry slot, one commit group
-    auto refill = [&](int pass, int slotW, int slotL, unsigned e, float dep0, float dep1) {
-        const int sl = (slotL + R) & (2 * R - 1);
-        const unsigned eR = (pass + R < npass) ? ringL[sl * 32 + lane] : SCL_MONO_IDLE;
-        copy_weights(eR, slotW, dep0, dep1);
-        copy_entries(pass + 2 * R, slotL, e);
-        asm volatile("cp.async.commit_group;\n" ::);
-    };
-    // prologue: entries of passes 0 .. 2R-1, then weights of passes 0 .. R-1
+    // prologue: entries of passes 0 .. RL-1, then weights of passes 0 .. R-1
 #pragma unroll
-    for (int i = 0; i < 2 * R; i++) copy_entries(i, i, 0u);
+    for (int q = 0; q < RL; q += 4) copy_entries4(q);
     asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
 #pragma unroll
     for (int i = 0; i < R; i++) {
@@ -506,15 +502,20 @@ __device__ SCL_STREAM_INLINE void scl_monotonic_f32_stream(float* X, int Nx, con
     }
     unsigned e = ringL[lane];               // entry of the next pass, read one pass early
     for (int j = 0; j < npass; j++) {
-        const int sW = j & (R - 1), sL = j & (2 * R - 1);   // weight / entry slots of pass j
-        // everything but the R-1 newest groups has landed: weights of pass j, entries of pass j + R
+        const int sW = j & (R - 1);         // weight slot of pass j
+        // everything but the R-1 newest groups has landed: weights of pass j (entries land >= 20 passes early)
         asm volatile("cp.async.wait_group %0;\n" :: "n"(R - 1) : "memory");
         const float4 w0 = ringW[sW * 64 + lane], w1 = ringW[sW * 64 + 32 + lane];
         const bool has = e != SCL_MONO_IDLE;
         const int p = has ? (int)(e & pmask) : 0;           // idle lanes run on pixel 0 and store nothing
         const SclMonoNb nb = scl_mono_load(X, Nx, p);
-        const unsigned en = ringL[((j + 1) & (2 * R - 1)) * 32 + lane];   // landed long ago; stale past the end
-        refill(j, sW, sL, e, w0.x, w1.x);
+        const unsigned en = ringL[((j + 1) & (RL - 1)) * 32 + lane];      // stale past the end, unused then
+        // what a processed pass owes the pipeline: the weights of pass j + R into its weight slot, every fourth
+        // pass the entries of four passes into the slots of the four just consumed, one commit group
+        const unsigned eR = (j + R < npass) ? ringL[((j + R) & (RL - 1)) * 32 + lane] : SCL_MONO_IDLE;
+        copy_weights(eR, sW, w0.x, w1.x);
+        if ((j & 3) == 0 && j >= 4) copy_entries4(j + RL - 4);
+        asm volatile("cp.async.commit_group;\n" ::);
         const float v = scl_mono_value(nb, w0, w1, omt);
         if (has) X[p] = v;
         __syncwarp();                       // a level may end here: its stores must be visible to the next pass
