@@ -24,6 +24,48 @@
 #define SCL_SED_NOT_CONVERGED 1
 #define SCL_MORPH_NOT_CONVERGED 2
 
+// Complex arithmetic on the packed-f32x2 instructions of sm_100 (FADD2 / FMUL2 / FFMA2: one issue slot for both
+// halves; ptxas folds scalar broadcasts and half swaps into operand modifiers).  add/sub round exactly like the
+// scalar forms; the products use the same mul-then-fma pairing the compiler contracted the scalar forms to.
+#ifndef SCL_PACKED
+#define SCL_PACKED 1
+#endif
+__device__ __forceinline__ unsigned long long scl_pk(float a, float b) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ float2 scl_upk(unsigned long long v) {
+    float2 r;
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+    return r;
+}
+#if SCL_PACKED
+// a * b = a.x (b.x, b.y) + a.y (-b.y, b.x)
+__device__ __forceinline__ float2 cmul(float2 a, float2 b) {
+    unsigned long long t, r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(scl_pk(a.x, a.x)), "l"(scl_pk(b.x, b.y)));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(scl_pk(a.y, a.y)), "l"(scl_pk(-b.y, b.x)), "l"(t));
+    return scl_upk(r);
+}
+// a * conj(b) = a.x (b.x, -b.y) + a.y (b.y, b.x)
+__device__ __forceinline__ float2 cmulc(float2 a, float2 b) {
+    unsigned long long t, r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(t) : "l"(scl_pk(a.y, a.y)), "l"(scl_pk(b.y, b.x)));
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(scl_pk(a.x, a.x)), "l"(scl_pk(b.x, -b.y)), "l"(t));
+    return scl_upk(r);
+}
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) {
+    unsigned long long r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(scl_pk(a.x, a.y)), "l"(scl_pk(b.x, b.y)));
+    return scl_upk(r);
+}
+__device__ __forceinline__ float2 csub(float2 a, float2 b) {
+    unsigned long long r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(scl_pk(a.x, a.y)), "l"(scl_pk(b.x, b.y)));
+    return scl_upk(r);
+}
+#else
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {
     return make_float2(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x);
 }
@@ -32,6 +74,7 @@ __device__ __forceinline__ float2 cmulc(float2 a, float2 b) {   // a * conj(b)
 }
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+#endif
 __device__ __forceinline__ float2 cswap(float2 a) { return make_float2(a.y, a.x); }
 
 template <typename T>
