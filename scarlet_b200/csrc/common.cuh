@@ -40,6 +40,11 @@ __device__ __forceinline__ float2 scl_upk(unsigned long long v) {
     asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
     return r;
 }
+__device__ __forceinline__ unsigned long long scl_fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
 #if SCL_PACKED
 // a * b = a.x (b.x, b.y) + a.y (-b.y, b.x)
 __device__ __forceinline__ float2 cmul(float2 a, float2 b) {

@@ -143,11 +143,12 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
     const int nty = (ny + 7) / 8, ntx = Zs / 4;
     for (int tile = threadIdx.x; tile < nty * ntx; tile += blockDim.x) {
         const int i0 = (tile / ntx) * 8, j0 = (tile % ntx) * 4;
-        float acc[8][4];
+        // accumulators as packed pairs over two rows: one FFMA2 updates (row 2q, row 2q+1) of a column
+        unsigned long long acc2[4][4];
 #pragma unroll
-        for (int r = 0; r < 8; r++)
+        for (int q = 0; q < 4; q++)
 #pragma unroll
-            for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
+            for (int c = 0; c < 4; c++) acc2[q][c] = 0ull;
         const float* xr = Xw + i0 * Nx;
         const float* tp = Tx + j0;
         // The two half-warps work on different row groups (same bank whenever Nx is a multiple of 32): the upper
@@ -162,17 +163,24 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
             for (int l = lb; l < le; l++) {
                 const float t3 = tp[l + 3];
 #pragma unroll
-                for (int r = 0; r < 8; r++) {
-                    const float xv = xr[r * Nx + l];
-                    acc[r][0] += xv * t0; acc[r][1] += xv * t1; acc[r][2] += xv * t2; acc[r][3] += xv * t3;
+                for (int q = 0; q < 4; q++) {
+                    const unsigned long long xp = scl_pk(xr[(2 * q) * Nx + l], xr[(2 * q + 1) * Nx + l]);
+                    acc2[q][0] = scl_fma2(xp, scl_pk(t0, t0), acc2[q][0]);
+                    acc2[q][1] = scl_fma2(xp, scl_pk(t1, t1), acc2[q][1]);
+                    acc2[q][2] = scl_fma2(xp, scl_pk(t2, t2), acc2[q][2]);
+                    acc2[q][3] = scl_fma2(xp, scl_pk(t3, t3), acc2[q][3]);
                 }
                 t0 = t1; t1 = t2; t2 = t3;
             }
         }
 #pragma unroll
-        for (int r = 0; r < 8; r++)
-            if (i0 + r < ny)
-                *reinterpret_cast<float4*>(Z + (i0 + r) * Zs + j0) = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+        for (int q = 0; q < 4; q++) {
+            const float2 c0 = scl_upk(acc2[q][0]), c1 = scl_upk(acc2[q][1]), c2 = scl_upk(acc2[q][2]), c3 = scl_upk(acc2[q][3]);
+            if (i0 + 2 * q < ny)
+                *reinterpret_cast<float4*>(Z + (i0 + 2 * q) * Zs + j0) = make_float4(c0.x, c1.x, c2.x, c3.x);
+            if (i0 + 2 * q + 1 < ny)
+                *reinterpret_cast<float4*>(Z + (i0 + 2 * q + 1) * Zs + j0) = make_float4(c0.y, c1.y, c2.y, c3.y);
+        }
     }
     const bool nyq = (Fy % 2 == 0);
     const int oy = (Fy - ny + 1) / 2 - Fy / 2;
@@ -199,11 +207,10 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
     // Y[i][j] = sum_l Ty[i + l] Z[l][j];  X <- (X <= 0) ? 0 : (X + Y)/2       (8x4 tiles, eight sliding table values)
     for (int tile = threadIdx.x; tile < nty * ntx; tile += blockDim.x) {
         const int i0 = (tile / ntx) * 8, j0 = (tile % ntx) * 4;
-        float acc[8][4];
+        // accumulators as packed pairs over two columns
+        unsigned long long acc2[8][2];
 #pragma unroll
-        for (int r = 0; r < 8; r++)
-#pragma unroll
-            for (int c = 0; c < 4; c++) acc[r][c] = 0.f;
+        for (int r = 0; r < 8; r++) { acc2[r][0] = 0ull; acc2[r][1] = 0ull; }
         const float* tp = Ty + i0;
         float t[8];
 #pragma unroll
@@ -212,12 +219,21 @@ __device__ void scl_kspace_symmetry(float* X, int Nx, SclWindow w, double dy, do
         for (int l = 0; l < ny; l++) {
             t[7] = tp[l + 7];
             const float4 zv = *reinterpret_cast<const float4*>(Z + l * Zs + j0);
+            const unsigned long long z01 = scl_pk(zv.x, zv.y), z23 = scl_pk(zv.z, zv.w);
 #pragma unroll
             for (int r = 0; r < 8; r++) {
-                acc[r][0] += t[r] * zv.x; acc[r][1] += t[r] * zv.y; acc[r][2] += t[r] * zv.z; acc[r][3] += t[r] * zv.w;
+                const unsigned long long tt = scl_pk(t[r], t[r]);
+                acc2[r][0] = scl_fma2(tt, z01, acc2[r][0]);
+                acc2[r][1] = scl_fma2(tt, z23, acc2[r][1]);
             }
 #pragma unroll
             for (int r = 0; r < 7; r++) t[r] = t[r + 1];
+        }
+        float acc[8][4];
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+            const float2 a = scl_upk(acc2[r][0]), b = scl_upk(acc2[r][1]);
+            acc[r][0] = a.x; acc[r][1] = a.y; acc[r][2] = b.x; acc[r][3] = b.y;
         }
 #pragma unroll
         for (int r = 0; r < 8; r++)
