@@ -312,6 +312,12 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     const float* wgt = weights ? weights + ((size_t)b * C + c) * N : nullptr;
     float* gout = G + ((size_t)b * C + c) * N;
 
+    // the residual pass reads the band's image and weights one whole transform later: start them towards L2 now
+    for (int i = threadIdx.x * 32; i < N; i += blockDim.x * 32) {
+        asm volatile("prefetch.global.L2 [%0];\n" :: "l"(img + i));
+        if (wgt) asm volatile("prefetch.global.L2 [%0];\n" :: "l"(wgt + i));
+    }
+
     fill_twiddles_reg(tw);
     if (threadIdx.x < SCL_MAX_COMP) sA[threadIdx.x] = (threadIdx.x < K) ? A[(size_t)(k0 + threadIdx.x) * C + c] : 0.f;
     __syncthreads();

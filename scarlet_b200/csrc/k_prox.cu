@@ -185,6 +185,13 @@ scl_k_prox(SclProxArgs a)
         if (fl & SCL_F_MONOTONIC) {
             if (a.plan.pbits) {
                 // Z and the tables are dead after the symmetry step: scratch of the streamed sweep
+                if (threadIdx.x >= 32) {
+                    // the waiting warps pull the previous morphology (read again by the convergence sums below)
+                    // back into L2 while the sweep runs
+                    const float* So = a.S + (size_t)k * N;
+                    for (int i = (threadIdx.x - 32) * 32; i < N; i += (blockDim.x - 32) * 32)
+                        asm volatile("prefetch.global.L2 [%0];\n" :: "l"(So + i));
+                }
                 if (threadIdx.x < 32) {
                     const int ctr = sc[0] * Nx + sc[1];
                     const unsigned f0 = a.plan.first[ctr], f1 = a.plan.first[ctr + 1];
