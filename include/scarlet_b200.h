@@ -97,11 +97,11 @@ typedef struct {
     const int32_t* center;          /* [Ktot][2] pixel_center (y, x) */
     const double* shift;            /* [Ktot][2] (dy, dx) */
     const int32_t* conv;            /* [Ktot] BlendFlag bits (component.py:32-36) */
-    const float* images;            /* [B][C][Ny*Nx] */
-    const float* weights;           /* [B][C][Ny*Nx] or NULL (weights = 1, observation.py:148-151) */
+    const float* images;            /* [B][P][Ny*Nx]; P = n_planes (C when n_planes == 0) */
+    const float* weights;           /* [B][P][Ny*Nx] or NULL (weights = 1, observation.py:148-151) */
     int32_t n_ker;                  /* number of distinct kernel spectra */
     const float* kernel_spec;       /* complex64 [n_ker][128][65] */
-    const int32_t* ker_idx;         /* [B*C] index into kernel_spec, -1 = identical PSFs (observation.py:191-194) */
+    const int32_t* ker_idx;         /* [B*P] index into kernel_spec, -1 = identical PSFs (observation.py:191-194) */
     int32_t n_cw, ph, pw;           /* centroid weight images (source.py:389-397) */
     const float* cw;                /* [n_cw][ph][pw] */
     const int32_t* cw_idx;          /* [B] */
@@ -110,6 +110,13 @@ typedef struct {
     const int32_t* src_first;       /* [Ktot] or NULL: index of the first component of the source that owns component
                                      * k (the components of a source are contiguous, ComponentTree order); only read
                                      * for components flagged SCL_SHARED_CENTER.  NULL = no such component */
+    /* Several observations per blend (Blend._loss sums them, blend.py:135-139; each sees the model bands of its
+     * `_band_slice`, observation.py:184-189,216): the image planes of all observations are stacked, plane p of
+     * every blend looks at model band plane_band[p].  n_planes == 0: one observation covering all C bands
+     * (P = C, plane_band[p] = p, n_obs = 1).  n_obs scales both Lipschitz constants (blend.py:214-218). */
+    int32_t n_planes;               /* P <= 8 */
+    const int32_t* plane_band;      /* [P] model band of each plane */
+    int32_t n_obs;                  /* number of observations the planes come from (>= 1) */
 } scl_batch_desc;
 
 /* Allocate device state for `desc`'s sizes and upload it. */

@@ -33,6 +33,7 @@ class BatchDesc(ctypes.Structure):
         ("n_cw", ctypes.c_int32), ("ph", ctypes.c_int32), ("pw", ctypes.c_int32),
         ("cw", c_void_p), ("cw_idx", c_void_p),
         ("it0", c_void_p), ("prev_loss", c_void_p), ("src_first", c_void_p),
+        ("n_planes", ctypes.c_int32), ("plane_band", c_void_p), ("n_obs", ctypes.c_int32),
     ]
 
 
@@ -278,10 +279,16 @@ class Batch:
     (thin owner of a `scl_batch*`)."""
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
-                 kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None):
+                 kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None,
+                 plane_band=None, n_obs=1):
+        """plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
+        all observations stacked as P planes, plane p seeing model band plane_band[p] (include/scarlet_b200.h)."""
         require_device()
         monotonic_tables(Ny, Nx)
         self.C, self.Ny, self.Nx = int(C), int(Ny), int(Nx)
+        self.plane_band = None if plane_band is None else np.ascontiguousarray(plane_band, dtype=np.int32)
+        self.P = self.C if plane_band is None else len(self.plane_band)
+        self.n_obs = int(n_obs)
         self.stream = stream
         self._h = c_void_p()
         self._keep = None
@@ -305,10 +312,10 @@ class Batch:
             center=ca(center, dtype=np.int32).reshape(K, 2),
             shift=ca(shift, dtype=np.float64).reshape(K, 2),
             conv=ca(conv, dtype=np.int32).reshape(K),
-            images=ca(images, dtype=np.float32).reshape(B, self.C, N),
-            weights=None if weights is None else ca(weights, dtype=np.float32).reshape(B, self.C, N),
+            images=ca(images, dtype=np.float32).reshape(B, self.P, N),
+            weights=None if weights is None else ca(weights, dtype=np.float32).reshape(B, self.P, N),
             kernel_spec=None if kernel_spec is None else ca(kernel_spec, dtype=np.complex64),
-            ker_idx=ca(ker_idx, dtype=np.int32).reshape(B * self.C),
+            ker_idx=ca(ker_idx, dtype=np.int32).reshape(B * self.P),
             cw=None if cw is None else ca(cw, dtype=np.float32),
             cw_idx=ca(cw_idx, dtype=np.int32).reshape(B),
             it0=ca(np.zeros(B) if it0 is None else it0, dtype=np.int32).reshape(B),
@@ -322,6 +329,8 @@ class Batch:
         for name in ("comp_off", "sed", "morph", "cflags", "center", "shift", "conv", "images", "weights",
                      "kernel_spec", "ker_idx", "cw", "cw_idx", "it0", "prev_loss", "src_first"):
             setattr(d, name, _p(a[name]))
+        if self.plane_band is not None:
+            d.n_planes, d.plane_band, d.n_obs = self.P, _p(self.plane_band), self.n_obs
         d.n_ker = 0 if a["kernel_spec"] is None else len(a["kernel_spec"])
         if a["cw"] is None:
             d.n_cw, d.ph, d.pw = 0, 0, 0

@@ -36,17 +36,30 @@ def pack_blends(blends):
     comp_off, sed, morph, cflags, center, shift, conv, src_first = [0], [], [], [], [], [], [], []
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
     spec_ids, cw_ids = {}, {}
-    any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
+    any_w = any(isinstance(o.weights, np.ndarray) for b in blends for o in b.observations)
+    # image planes: the bands of every observation stacked, each looking at one model band (observation.py:184-189)
+    plane_band = None
     for bl in blends:
         if bl.frame.shape != (C, Ny, Nx):
             raise ValueError("all blends of a batch must share the frame shape")
         if bl.frame.dtype != np.float32:
             raise NotImplementedError("the CUDA loop computes in float32; use Frame(dtype=np.float32)")
-        if len(bl.observations) != 1:
-            raise NotImplementedError("multiple observations per blend are not implemented in scarlet_b200 yet")
-        obs = bl.observations[0]
-        if isinstance(obs, LowResObservation) or obs._band_slice != slice(None):
-            raise NotImplementedError("band-sliced / multi-resolution observations are not implemented yet")
+        pb = []
+        for obs in bl.observations:
+            if isinstance(obs, LowResObservation):
+                raise NotImplementedError("multi-resolution observations are not implemented yet")
+            if obs.images.shape[1:] != (Ny, Nx):
+                raise ValueError("observation and model frame differ in shape")
+            sl = obs._band_slice
+            pb += list(range(C))[sl]
+            if len(list(range(C))[sl]) != obs.images.shape[0]:
+                raise ValueError("observation bands do not match its slice of the model channels")
+        if plane_band is None:
+            plane_band = pb
+        elif pb != plane_band:
+            raise ValueError("all blends of a batch must share the layout of their observations")
+        if len(pb) > 8:
+            raise NotImplementedError("at most 8 image planes (bands summed over observations) per blend")
         last_src = None
         for s, c in _owner_of(bl):
             if c.prior is not None:
@@ -69,20 +82,21 @@ def pack_blends(blends):
             shift.append(getattr(s, "shift", (0., 0.)))
             conv.append(c.flags.value & 3)
         comp_off.append(len(sed))
-        images.append(obs.images)
-        if any_w:
-            weights.append(obs.weights if isinstance(obs.weights, np.ndarray)
-                           else np.ones(obs.images.shape, np.float32) * obs.weights)
-        spec = obs.kernel_spectrum()
-        if spec is None:
-            ker_idx += [-1] * C
-        else:
-            key = id(obs._diff_kernels.image) if len(blends) > 64 else obs._diff_kernels.image.tobytes()
-            if key not in spec_ids:
-                spec_ids[key] = len(specs)
-                specs.append(spec)
-            base = spec_ids[key] * C
-            ker_idx += [base + c for c in range(C)]
+        for obs in bl.observations:
+            Co = obs.images.shape[0]
+            images.extend(obs.images)
+            if any_w:
+                weights.extend(obs.weights if isinstance(obs.weights, np.ndarray)
+                               else np.ones(obs.images.shape, np.float32) * obs.weights)
+            spec = obs.kernel_spectrum()
+            if spec is None:
+                ker_idx += [-1] * Co
+            else:
+                key = id(obs._diff_kernels.image) if len(blends) > 64 else obs._diff_kernels.image.tobytes()
+                if key not in spec_ids:
+                    spec_ids[key] = sum(len(sp) for sp in specs)
+                    specs.append(spec)
+                ker_idx += [spec_ids[key] + c for c in range(Co)]
         cw = np.asarray(_centroid_weight(bl.frame), dtype=np.float32)
         key = id(bl.frame.psfs) if len(blends) > 64 else cw.tobytes()
         if key not in cw_ids:
@@ -96,7 +110,8 @@ def pack_blends(blends):
                 conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
-                src_first=np.array(src_first))
+                src_first=np.array(src_first), plane_band=np.array(plane_band, dtype=np.int32),
+                n_obs=len(blends[0].observations))
 
 
 def unpack_blends(blends, packed, out):
@@ -127,9 +142,10 @@ def fit_many(blends, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=
     Returns the list of timing dicts (one per frame-shape group)."""
     groups = {}
     for bl in blends:
-        groups.setdefault(bl.frame.shape, []).append(bl)
+        layout = tuple((o._band_slice.start, o._band_slice.stop, o.images.shape[0]) for o in bl.observations)
+        groups.setdefault((bl.frame.shape, layout), []).append(bl)
     infos = []
-    for shape, group in groups.items():
+    for (shape, _), group in groups.items():
         packed = pack_blends(group)
         bt = _native.Batch(stream=stream, **packed)
         try:

@@ -20,6 +20,13 @@
 #define SCL_F_SHARED_CENTER 64u  // component of a multi-component source: centre + shift come from the source's
                                  // flux-weighted morphology (MultiComponentSource.update, source.py:605-627)
 
+// Image planes of a blend: the bands of all its observations stacked; plane p sees model band band[p]
+// (Observation._band_slice, observation.py:184-189).  Passed to the kernels by value.
+struct SclPlanes {
+    int P;                       // planes per blend (<= SCL_MAX_BANDS)
+    int band[SCL_MAX_BANDS];
+};
+
 // BlendFlag bits (component.py:32-36)
 #define SCL_SED_NOT_CONVERGED 1
 #define SCL_MORPH_NOT_CONVERGED 2

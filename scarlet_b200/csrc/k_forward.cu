@@ -271,7 +271,7 @@ __device__ __forceinline__ void column_phase_reg(float2* buf, const float2* tw, 
 
 }  // namespace
 
-// grid: (C * n_listed_blends); block: SCL_THREADS; dynamic smem: kFwdSmem (api.cu)
+// grid: (P * n_listed_blends), P = pl.P image planes per blend (one per band of every observation); block: SCL_THREADS; dynamic smem: kFwdSmem (api.cu)
 //   buf [128][65] float2 | tw [256] float2 | dummy line [130] float2 | red [32] double
 // HALF: Nx <= 64 and Ny <= 64 -- the zero-padded halves of every line are pruned from the transforms.
 template <bool HALF>
@@ -279,16 +279,16 @@ __global__ void __launch_bounds__(SCL_THREADS, 2)
 scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const float* __restrict__ S,        // [Ktot, N]
                       const int* __restrict__ comp_off,   // [B+1]
-                      const float* __restrict__ images,   // [B, C, N]
-                      const float* __restrict__ weights,  // [B, C, N] or nullptr (W = 1)
+                      const float* __restrict__ images,   // [B, P, N]
+                      const float* __restrict__ weights,  // [B, P, N] or nullptr (W = 1)
                       const float2* __restrict__ Dhat_t,  // [n_ker, 65, 128] transposed kernel spectra
-                      const int* __restrict__ ker_idx,    // [B*C], -1 = identity (no PSF matching)
+                      const int* __restrict__ ker_idx,    // [B*P], -1 = identity (no PSF matching)
                       const int* __restrict__ active,     // [B]
-                      const int* __restrict__ blend_list, // [gridDim.x / C] blends to process (compacted active list)
-                      float* __restrict__ G,              // [B, C, N]
-                      double* __restrict__ loss_part,     // [B, C]
-                      double* __restrict__ gram,          // [B, 8, 8]  rows r = c, c+C, .. of S S^T
-                      int C, int Ny, int Nx)
+                      const int* __restrict__ blend_list, // [gridDim.x / P] blends to process (compacted active list)
+                      float* __restrict__ G,              // [B, P, N]  adjoint image of every plane
+                      double* __restrict__ loss_part,     // [B, P]
+                      double* __restrict__ gram,          // [B, 8, 8]  rows r = plane, plane+P, .. of S S^T
+                      int Cm, SclPlanes pl, int Ny, int Nx)
 {
     extern __shared__ __align__(16) unsigned char smem_fwd[];
     float2* buf = reinterpret_cast<float2*>(smem_fwd);
@@ -298,7 +298,9 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     __shared__ float sA[SCL_MAX_COMP];
     __shared__ double sred[SCL_THREADS / 32][2 * SCL_MAX_COMP];
 
-    const int c = blockIdx.x % C, b = blend_list[blockIdx.x / C];
+    // c: this CTA's plane; C: planes per blend (work split of the Gram rows); cm: the model band the plane sees
+    const int C = pl.P, c = blockIdx.x % C, b = blend_list[blockIdx.x / C];
+    const int cm = pl.band[c];
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const int N = Ny * Nx;
@@ -319,7 +321,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     }
 
     fill_twiddles_reg(tw);
-    if (threadIdx.x < SCL_MAX_COMP) sA[threadIdx.x] = (threadIdx.x < K) ? A[(size_t)(k0 + threadIdx.x) * C + c] : 0.f;
+    if (threadIdx.x < SCL_MAX_COMP) sA[threadIdx.x] = (threadIdx.x < K) ? A[(size_t)(k0 + threadIdx.x) * Cm + cm] : 0.f;
     __syncthreads();
 
     double loss = 0.0;
@@ -509,7 +511,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
 }
 
 #define SCL_FWD_ARGS const float*, const float*, const int*, const float*, const float*, const float2*, const int*, \
-    const int*, const int*, float*, double*, double*, int, int, int
+    const int*, const int*, float*, double*, double*, int, SclPlanes, int, int
 template __global__ void scl_k_forward_adjoint<true>(SCL_FWD_ARGS);
 template __global__ void scl_k_forward_adjoint<false>(SCL_FWD_ARGS);
 

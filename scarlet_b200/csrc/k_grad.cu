@@ -84,14 +84,14 @@ extern "C" __global__ void __launch_bounds__(128)
 scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
                 const int* __restrict__ comp_off,     // [B+1]
                 const double* __restrict__ gram,      // [B, 8, 8]  S S^T (K1), rows/cols >= K unspecified
-                const double* __restrict__ loss_part, // [B, C]
+                const double* __restrict__ loss_part, // [B, P]  one entry per image plane
                 const int* __restrict__ active,       // [B]
                 const int* __restrict__ blend_list,   // [nB] compacted active list
                 const int* __restrict__ it0,          // [B] iterations done before this fit call
                 const double* __restrict__ prev_loss, // [B] last loss of an earlier fit call (if it0 > 0)
                 double* __restrict__ logL,            // [B, logL_cap] loss of step s of THIS fit call
                 float* __restrict__ lips,             // [B, 2] (L_sed, L_morph)
-                int nB, int C, int step, int logL_cap, int n_obs, int approximate_L)
+                int nB, int C, int P, int step, int logL_cap, int n_obs, int approximate_L)
 {
     const int gt = blockIdx.x * blockDim.x + threadIdx.x;
     const int which = gt & 1;
@@ -162,7 +162,7 @@ scl_k_lipschitz(const float* __restrict__ A,          // [Ktot, C]  current SEDs
     if (!live) return;
     double LA = which ? other : lam, LS = which ? lam : other;
     double total = 0.0;
-    for (int c = 0; c < C; c++) total += loss_part[b * C + c];
+    for (int c = 0; c < P; c++) total += loss_part[b * P + c];      // Blend._loss: sum over observations
     if (approximate_L) {
         const int it = it0[b] + step;              // index of this loss in Blend.mse
         if (it >= 1) {

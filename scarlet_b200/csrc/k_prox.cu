@@ -11,7 +11,7 @@
 #include "prox_dev.cuh"
 
 struct SclProxArgs {
-    const float* G;           // [B, C, N]  d loss / d model (K1); nullptr: no gradient step (construction pass)
+    const float* G;           // [B, P, N]  adjoint image of every plane (K1); nullptr: no gradient step (construction pass)
     const float* lips;        // [B, 2]     (L_sed, L_morph) (K2)
     float* A;                 // [Ktot, C]  in: previous iterate; out: new iterate
     float* S;                 // [Ktot, N]  in: previous iterate; out: new iterate
@@ -31,6 +31,7 @@ struct SclProxArgs {
     const int* nfl;           // next_fast_len tables
     const int* nfl_even;
     int C, Ny, Nx, ph, pw, step;
+    SclPlanes pl;             // image planes -> model bands (d loss / d model[c] = sum of G over the planes of band c)
     int it_override;          // >= 0: the iteration number update() sees (0 = source construction)
     double e_rel2;
     unsigned long long* phase_clk;   // optional [8]: summed clock64 per phase over all CTAs (profiling; nullptr = off)
@@ -90,17 +91,18 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
 // threads of the CTA; the caller synchronises before reading sAnew / sAold.
 __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, int b, unsigned fl, float* X,
                                                    double (*sdA)[SCL_MAX_BANDS], float* sAnew, float* sAold) {
-    const int N = a.Ny * a.Nx, C = a.C;
+    const int N = a.Ny * a.Nx, C = a.C, P = a.pl.P;
     {
         const float* Sin = a.S + (size_t)k * N;
         if (a.G && !(SCL_EXP & 16)) {
             const bool fixm = fl & SCL_F_FIX_MORPH;
             const float step_morph = 1.0f / a.lips[2 * b + 1];
-            const float* Gb = a.G + (size_t)b * C * N;
+            const float* Gb = a.G + (size_t)b * P * N;
+            // per plane: the SED entry of the band it sees; dAc[p] = sum_px G_p S, folded per band below
             float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
-            for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < C) ? a.A[(size_t)k * C + c] : 0.f; dAc[c] = 0.f; }
-            switch (C) {
+            for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < P) ? a.A[(size_t)k * C + a.pl.band[c]] : 0.f; dAc[c] = 0.f; }
+            switch (P) {
 #define SCL_STEP_CASE(CC) case CC: scl_step_loop<CC>(Sin, Gb, X, N, ak, dAc, fixm, step_morph); break;
                 SCL_STEP_CASE(1) SCL_STEP_CASE(2) SCL_STEP_CASE(3) SCL_STEP_CASE(4)
                 SCL_STEP_CASE(5) SCL_STEP_CASE(6) SCL_STEP_CASE(7) SCL_STEP_CASE(8)
@@ -115,7 +117,9 @@ __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, 
             if (threadIdx.x < C) {
                 // SED step (blend.py:91-93): A[k] -= (1/L_sed) dA
                 double v = 0.0;
-                for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][threadIdx.x];
+                for (int p = 0; p < P; p++)
+                    if (a.pl.band[p] == (int)threadIdx.x)
+                        for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][p];
                 float an = a.A[(size_t)k * C + threadIdx.x];
                 sAold[threadIdx.x] = an;
                 if (!(fl & SCL_F_FIX_SED)) an = an - (1.0f / a.lips[2 * b]) * (float)v;

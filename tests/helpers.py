@@ -84,6 +84,26 @@ def synthetic_blend(seed, C=5, Ny=64, Nx=64, kmin=2, kmax=8, psf_size=41, dtype=
     return frame, obs, srcs, rb.Blend(srcs, obs)
 
 
+def multi_obs_blend(seed, split=((0, 3), (1, 5)), **kw):
+    """A synthetic blend seen by several band-sliced observations (Blend._loss sums them, blend.py:135-139;
+    Observation._band_slice, observation.py:184-189): observation i holds model channels split[i][0]..split[i][1]-1,
+    the later ones with wider PSFs and their own noise.  Sources are initialised on the full-band observation."""
+    frame, obs, srcs, _ = synthetic_blend(seed, **kw)
+    C, Ny, Nx = frame.shape
+    chan = tuple("b%d" % c for c in range(C))
+    frame.channels = chan
+    rng = np.random.default_rng(777 + seed)
+    ps = obs.frame.psfs.shape[-1]
+    many = []
+    for i, (lo, hi) in enumerate(split):
+        psfs = np.array([rb.generate_psf_image(rb.gaussian, (ps, ps), sigma=1.2 + .15 * b + .2 * i) for b in range(lo, hi)])
+        # the full-band images re-blurred is not needed for a parity test: reuse the bands, add fresh noise
+        img = (obs.images[lo:hi] + rng.normal(0, .5 * i, (hi - lo, Ny, Nx))).astype(frame.dtype)
+        w = None if i % 2 else np.full(img.shape, 1. / (1 + i), dtype=frame.dtype)
+        many.append(rb.Observation(img, psfs=psfs.astype(frame.dtype), weights=w, channels=chan[lo:hi]).match(frame))
+    return frame, many, srcs, rb.Blend(srcs, many)
+
+
 def pack(blends):
     """Arrays for _native.Batch from oracle Blend objects sharing one frame shape."""
     from scarlet_b200 import _native as nat
@@ -91,9 +111,9 @@ def pack(blends):
     comp_off, sed, morph, cflags, center, shift, conv, src_first = [0], [], [], [], [], [], [], []
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
     spec_cache, cw_cache = {}, {}
-    any_w = any(isinstance(b.observations[0].weights, np.ndarray) for b in blends)
+    any_w = any(isinstance(o.weights, np.ndarray) for b in blends for o in b.observations)
+    plane_band = [c for o in blends[0].observations for c in range(C)[o.band_slice]]
     for bl in blends:
-        obs = bl.observations[0]
         for s in bl.sources:
             first = len(sed)
             for c in s.components:
@@ -122,18 +142,19 @@ def pack(blends):
                 shift.append(getattr(s, "shift", (0., 0.)))
                 conv.append(c.flags)
         comp_off.append(len(sed))
-        images.append(obs.images)
-        if any_w:
-            weights.append(obs.weights if isinstance(obs.weights, np.ndarray) else np.ones_like(obs.images))
-        if obs.diff_kernels is None:
-            ker_idx += [-1] * C
-        else:
-            key = obs.diff_kernels.tobytes()
-            if key not in spec_cache:
-                spec_cache[key] = len(specs)
-                specs.append(nat.kernel_spectrum(obs.diff_kernels, Ny, Nx))
-            base = spec_cache[key] * C
-            ker_idx += [base + c for c in range(C)]
+        for obs in bl.observations:
+            Co = len(obs.images)
+            images.extend(obs.images)
+            if any_w:
+                weights.extend(obs.weights if isinstance(obs.weights, np.ndarray) else np.ones_like(obs.images))
+            if obs.diff_kernels is None:
+                ker_idx += [-1] * Co
+            else:
+                key = obs.diff_kernels.tobytes()
+                if key not in spec_cache:
+                    spec_cache[key] = sum(len(sp) for sp in specs)
+                    specs.append(nat.kernel_spectrum(obs.diff_kernels, Ny, Nx))
+                ker_idx += [spec_cache[key] + c for c in range(Co)]
         cw = rb._centroid_weight(bl.frame).astype(np.float32)
         key = cw.tobytes()
         if key not in cw_cache:
@@ -147,4 +168,6 @@ def pack(blends):
                 conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
-                src_first=np.array(src_first))
+                src_first=np.array(src_first),
+                **(dict(plane_band=np.array(plane_band, dtype=np.int32), n_obs=len(blends[0].observations))
+                   if len(blends[0].observations) > 1 or plane_band != list(range(C)) else {}))

@@ -175,6 +175,37 @@ def test_update_surface(scarlet):
     assert_almost_equal(c.morph[1, 3:], [7.242640687, 5.806841831], decimal=5)
 
 
+def test_two_observations_workflow(scarlet):
+    """Blend(sources, [obs_a, obs_b]) with band-sliced observations (channels), as scarlet's multi-observation
+    use: the fit through the Python surface follows the oracle's own two-observation loop."""
+    rb = helpers.rb
+    frame_o, many_o, srcs_o, blend_o = helpers.multi_obs_blend(7, kmin=3, kmax=4)
+    C, Ny, Nx = frame_o.shape
+    frame = scarlet.Frame(frame_o.shape, psfs=frame_o.psfs, channels=frame_o.channels)
+    many = [scarlet.Observation(o.images, psfs=o.frame.psfs, weights=o.weights if isinstance(o.weights, np.ndarray) else None,
+                                channels=o.frame.channels).match(frame) for o in many_o]
+    assert [o._band_slice for o in many] == [o.band_slice for o in many_o]
+    for a, b in zip(many, many_o):
+        assert_allclose(a._diff_kernels.image, b.diff_kernels, rtol=0, atol=1e-7)
+    srcs = []
+    for so in srcs_o:
+        s = scarlet.ExtendedSource(frame, so.pixel_center, None, None, _init=(so.sed.copy(), so.morph.copy()),
+                                   _defer_update=True)
+        s.pixel_center, s.shift = so.pixel_center, so.shift
+        srcs.append(s)
+    blend = scarlet.Blend(srcs, many)
+    blend.fit(15, e_rel=0)
+    for _ in range(15):
+        blend_o.step(0.0)
+    assert_allclose(blend.mse, blend_o.mse, rtol=2e-4)
+    assert_array_equal([s.pixel_center for s in srcs], [s.pixel_center for s in srcs_o])
+    gm = blend_o.get_model()
+    assert_allclose(blend.get_model(), gm, rtol=0, atol=2e-4 * np.abs(gm).max())
+    # per-observation post-fit products
+    for o, oo in zip(many, many_o):
+        assert_allclose(o.render(blend.get_model()), oo.render(gm), rtol=0, atol=3e-4 * np.abs(gm).max())
+
+
 def test_unsupported_paths_are_loud(scarlet):
     with pytest.raises(NotImplementedError):
         scarlet.LowResObservation(np.zeros((1, 4, 4)))

@@ -64,6 +64,30 @@ def test_lockstep_multicomponent(nat):
     _lockstep(nat, blend, 40)
 
 
+@pytest.mark.parametrize("split", [((0, 3), (1, 5)), ((0, 4), (1, 5)), ((2, 5), (0, 2), (1, 4))])
+def test_lockstep_multiple_observations(nat, split):
+    """Several band-sliced observations of one blend (Blend._loss sums their losses and gradients, blend.py:135-139;
+    both Lipschitz constants scale with len(observations), blend.py:219-220): stacked image planes on the device."""
+    if sum(hi - lo for lo, hi in split) > 8:
+        pytest.skip("more than 8 planes")
+    _, obs, _, blend = helpers.multi_obs_blend(3, split=split, kmin=3, kmax=5)
+    assert len(blend.observations) == len(split)
+    _lockstep(nat, blend, 12)
+
+
+def test_multiple_observations_approximate_L(nat):
+    """approximate_L with two observations: free-running logL against the oracle"""
+    _, _, _, blend = helpers.multi_obs_blend(5, kmin=2, kmax=4)
+    p = helpers.pack([blend])
+    bt = nat.Batch(**p)
+    bt.fit(10, 0.0, approximate_L=True)
+    out = bt.download()
+    bt.close()
+    for _ in range(10):
+        blend.step(0.0, approximate_L=True)
+    assert_allclose(out["logL"][0, :10], blend.mse, rtol=2e-4)
+
+
 def test_multicomponent_free_running_vs_reference(nat):
     """The same scene free-running against the reference's own run (tests/golden/make_golden_multi.py)."""
     g, _, _, srcs, blend = helpers.multi_blend()
