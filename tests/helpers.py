@@ -104,6 +104,43 @@ def multi_obs_blend(seed, split=((0, 3), (1, 5)), **kw):
     return frame, many, srcs, rb.Blend(srcs, many)
 
 
+def lowres_scene(gold, tag, dtype=np.float32):
+    """Oracle objects of the multi-resolution fixture (tests/golden/make_golden_lowres.py): model frame,
+    high-resolution Observation, LowResObservation."""
+    sys_path_golden()
+    from wcs_stub import make_pair
+    from oracle import ref_lowres as rl
+    hr_img, lr_img = gold[tag + "hr_img"], gold[tag + "lr_img"]
+    whr, wlr = make_pair(hr_img.shape[1:], lr_img.shape[1:], scale=4.0, lr_offset=tuple(gold[tag + "offset"]))
+    chan = ["h0", "h1", "h2", "l0", "l1", "l2", "l3", "l4"]
+    frame = rb.Frame((8,) + hr_img.shape[1:], psfs=gold[tag + "mpsf"][None], channels=chan, dtype=dtype)
+    frame.wcs = whr
+    ohr = rb.Observation(hr_img, psfs=gold[tag + "hr_psfs"], channels=chan[:3])
+    ohr.frame.wcs = whr
+    ohr.match(frame)
+    olr = rl.LowResObservation(lr_img, wcs=wlr, psfs=gold[tag + "lr_psfs"], weights=gold[tag + "w_lr"],
+                               channels=chan[3:]).match(frame)
+    return frame, ohr, olr
+
+
+def lowres_blend(gold, frame, ohr, olr):
+    """CombinedExtendedSource per true centre of fixture A + the two-observation Blend (oracle objects)."""
+    from oracle import ref_lowres as rl
+    HY, HX = frame.shape[1:]
+    bg = [np.ones(3, np.float32), np.ones(5, np.float32)]
+    srcs = []
+    for (cy, cx) in [(HY * .35, HX * .4), (HY * .6, HX * .62), (HY * .3, HX * .72)]:
+        sky = (round(cy) - HY / 2, round(cx) - HX / 2)
+        srcs.append(rl.CombinedExtendedSource(frame, sky, [ohr, olr], bg, obs_idx=0))
+    return srcs, rb.Blend(srcs, [ohr, olr])
+
+
+def sys_path_golden():
+    import sys
+    if GOLD not in sys.path:
+        sys.path.insert(0, GOLD)
+
+
 def pack(blends):
     """Arrays for _native.Batch from oracle Blend objects sharing one frame shape."""
     from scarlet_b200 import _native as nat
