@@ -80,6 +80,10 @@ int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, dou
  * with its centre tap at index 0); ker_idx int32 [n*C] (-1 = identity).  adjoint != 0 applies the transpose. */
 int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int Nx, const float* spec, int n_ker,
                      const int32_t* ker_idx, int adjoint, void* stream);
+/* LowResObservation._render (observation.py:524-558) as its matrix: out[i][c][q] = sum_p op[c][q][p] model[i][c][p].
+ * model float32 [n][C][N] (the observation's bands of the model, N = Ny*Nx); op float32 [C][n_lr][N], the
+ * resample-and-convolve operator of one geometry (built once by LowResObservation.match); out float32 [n][C][n_lr]. */
+int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, int n_lr, const float* op, void* stream);
 /* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
  * exported for symbol parity, returns SCL_E_LIMIT. */
 int scl_apply_filter_f32(void);
@@ -117,6 +121,16 @@ typedef struct {
     int32_t n_planes;               /* P <= 8 */
     const int32_t* plane_band;      /* [P] model band of each plane */
     int32_t n_obs;                  /* number of observations the planes come from (>= 1) */
+    /* Planes of low-resolution observations (LowResObservation, observation.py:242-599), after the n_planes
+     * full-resolution ones: plane_band then has n_planes + n_lr_planes entries (<= 8 together; at least one
+     * full-resolution plane).  Each sees its model band through a linear resample-and-convolve operator. */
+    int32_t n_lr_planes;            /* Plr (0 = none) */
+    int32_t lr_n;                   /* pixels of the low-resolution window, n_lr */
+    const float* lr_images;         /* [B][Plr][n_lr] */
+    const float* lr_weights;        /* [B][Plr][n_lr] or NULL */
+    int32_t n_lr_op;                /* distinct geometries */
+    const float* lr_op;             /* [n_lr_op][Plr][n_lr][Ny*Nx] */
+    const int32_t* lr_op_idx;       /* [B] */
 } scl_batch_desc;
 
 /* Allocate device state for `desc`'s sizes and upload it. */

@@ -34,6 +34,8 @@ class BatchDesc(ctypes.Structure):
         ("cw", c_void_p), ("cw_idx", c_void_p),
         ("it0", c_void_p), ("prev_loss", c_void_p), ("src_first", c_void_p),
         ("n_planes", ctypes.c_int32), ("plane_band", c_void_p), ("n_obs", ctypes.c_int32),
+        ("n_lr_planes", ctypes.c_int32), ("lr_n", ctypes.c_int32), ("lr_images", c_void_p), ("lr_weights", c_void_p),
+        ("n_lr_op", ctypes.c_int32), ("lr_op", c_void_p), ("lr_op_idx", c_void_p),
     ]
 
 
@@ -273,6 +275,18 @@ def convolve(model, spec, ker_idx, adjoint=False):
     return out
 
 
+def lowres_render(model, op):
+    """LowResObservation._render as its matrix: model float32 [n, C, N]; op float32 [C, n_lr, N] -> [n, C, n_lr]."""
+    require_device()
+    model = np.ascontiguousarray(model, dtype=np.float32)
+    op = np.ascontiguousarray(op, dtype=np.float32)
+    n, C, N = model.shape
+    assert op.shape[0] == C and op.shape[2] == N
+    out = np.empty((n, C, op.shape[1]), np.float32)
+    _check(lib().scl_lowres_render_f32(_p(model), _p(out), n, C, N, op.shape[1], _p(op), None))
+    return out
+
+
 # --------------------------------------------------------------------------- batch fit
 class Batch:
     """Device-resident state of B independent blends sharing one frame shape
@@ -280,14 +294,18 @@ class Batch:
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
                  kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None,
-                 plane_band=None, n_obs=1):
+                 plane_band=None, n_obs=1, lr=None):
         """plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
         all observations stacked as P planes, plane p seeing model band plane_band[p] (include/scarlet_b200.h)."""
         require_device()
         monotonic_tables(Ny, Nx)
         self.C, self.Ny, self.Nx = int(C), int(Ny), int(Nx)
         self.plane_band = None if plane_band is None else np.ascontiguousarray(plane_band, dtype=np.int32)
-        self.P = self.C if plane_band is None else len(self.plane_band)
+        # lr: dict(images [B, Plr, n_lr], weights or None, op [n_op, Plr, n_lr, N], op_idx [B]) -- the planes of
+        # low-resolution observations; plane_band then lists the full-resolution planes first, these after
+        self.lr = lr
+        self.Plr = 0 if lr is None else int(np.shape(lr["images"])[1])
+        self.P = self.C if plane_band is None else len(self.plane_band) - self.Plr
         self.n_obs = int(n_obs)
         self.stream = stream
         self._h = c_void_p()
@@ -331,6 +349,15 @@ class Batch:
             setattr(d, name, _p(a[name]))
         if self.plane_band is not None:
             d.n_planes, d.plane_band, d.n_obs = self.P, _p(self.plane_band), self.n_obs
+        if self.lr is not None:
+            lr = dict(images=ca(self.lr["images"], dtype=np.float32),
+                      weights=None if self.lr.get("weights") is None else ca(self.lr["weights"], dtype=np.float32),
+                      op=ca(self.lr["op"], dtype=np.float32), op_idx=ca(self.lr["op_idx"], dtype=np.int32))
+            assert lr["images"].shape[:2] == (B, self.Plr) and lr["op"].shape[1:] == (self.Plr, lr["images"].shape[2], N)
+            a.update({"lr_" + k: v for k, v in lr.items()})
+            d.n_lr_planes, d.lr_n, d.n_lr_op = self.Plr, lr["images"].shape[2], len(lr["op"])
+            d.lr_images, d.lr_weights, d.lr_op, d.lr_op_idx = (_p(lr["images"]), _p(lr["weights"]), _p(lr["op"]),
+                                                               _p(lr["op_idx"]))
         d.n_ker = 0 if a["kernel_spec"] is None else len(a["kernel_spec"])
         if a["cw"] is None:
             d.n_cw, d.ph, d.pw = 0, 0, 0

@@ -35,7 +35,8 @@ def pack_blends(blends):
     C, Ny, Nx = blends[0].frame.shape
     comp_off, sed, morph, cflags, center, shift, conv, src_first = [0], [], [], [], [], [], [], []
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
-    spec_ids, cw_ids = {}, {}
+    spec_ids, cw_ids, lr_ids = {}, {}, {}
+    lr_images, lr_weights, lr_ops, lr_op_idx = [], [], [], []
     any_w = any(isinstance(o.weights, np.ndarray) for b in blends for o in b.observations)
     # image planes: the bands of every observation stacked, each looking at one model band (observation.py:184-189)
     plane_band = None
@@ -44,16 +45,23 @@ def pack_blends(blends):
             raise ValueError("all blends of a batch must share the frame shape")
         if bl.frame.dtype != np.float32:
             raise NotImplementedError("the CUDA loop computes in float32; use Frame(dtype=np.float32)")
-        pb = []
+        pb, pb_lr = [], []
         for obs in bl.observations:
             if isinstance(obs, LowResObservation):
-                raise NotImplementedError("multi-resolution observations are not implemented yet")
+                if obs._lr_op is None:
+                    raise ValueError("LowResObservation.match(frame) has not been called")
+                pb_lr += list(range(C))[obs._band_slice]
+                continue
             if obs.images.shape[1:] != (Ny, Nx):
                 raise ValueError("observation and model frame differ in shape")
             sl = obs._band_slice
             pb += list(range(C))[sl]
             if len(list(range(C))[sl]) != obs.images.shape[0]:
                 raise ValueError("observation bands do not match its slice of the model channels")
+        n_lr_planes = len(pb_lr)
+        if n_lr_planes and len([o for o in bl.observations if isinstance(o, LowResObservation)]) > 1:
+            raise NotImplementedError("one LowResObservation per blend")
+        pb = pb + pb_lr                      # full-resolution planes first, low-resolution planes after
         if plane_band is None:
             plane_band = pb
         elif pb != plane_band:
@@ -83,6 +91,18 @@ def pack_blends(blends):
             conv.append(c.flags.value & 3)
         comp_off.append(len(sed))
         for obs in bl.observations:
+            if isinstance(obs, LowResObservation):
+                ys, xs = obs._window()
+                sub = obs.images[:, ys, xs]
+                lr_images.append(sub.reshape(len(sub), -1))
+                w = obs.weights if isinstance(obs.weights, np.ndarray) else np.float32(obs.weights)
+                lr_weights.append(np.broadcast_to(w, sub.shape).reshape(len(sub), -1))
+                key = id(obs._lr_op)
+                if key not in lr_ids:
+                    lr_ids[key] = len(lr_ops)
+                    lr_ops.append(obs._lr_op)
+                lr_op_idx.append(lr_ids[key])
+                continue
             Co = obs.images.shape[0]
             images.extend(obs.images)
             if any_w:
@@ -111,7 +131,9 @@ def pack_blends(blends):
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
                 src_first=np.array(src_first), plane_band=np.array(plane_band, dtype=np.int32),
-                n_obs=len(blends[0].observations))
+                n_obs=len(blends[0].observations),
+                lr=dict(images=np.array(lr_images), weights=np.array(lr_weights), op=np.array(lr_ops),
+                        op_idx=np.array(lr_op_idx)) if lr_images else None)
 
 
 def unpack_blends(blends, packed, out):
@@ -142,7 +164,8 @@ def fit_many(blends, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=
     Returns the list of timing dicts (one per frame-shape group)."""
     groups = {}
     for bl in blends:
-        layout = tuple((o._band_slice.start, o._band_slice.stop, o.images.shape[0]) for o in bl.observations)
+        layout = tuple((o._band_slice.start, o._band_slice.stop, o.images.shape[0], getattr(o, "lr_shape", None))
+                       for o in bl.observations)
         groups.setdefault((bl.frame.shape, layout), []).append(bl)
     infos = []
     for (shape, _), group in groups.items():

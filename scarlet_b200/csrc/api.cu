@@ -12,6 +12,7 @@
 #include "k_forward.cu"
 #include "k_grad.cu"
 #include "k_prox.cu"
+#include "k_lowres.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
@@ -339,5 +340,21 @@ int scl_apply_filter_f32(void) {
 }
 
 }  // extern "C"
+
+int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, int n_lr, const float* op, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!model || !out || !op || n < 0 || C < 1 || N < 1 || n_lr < 1) return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<float> dm, dop, dout;
+    CK(dm.alloc((size_t)n * C * N)); CK(dop.alloc((size_t)C * n_lr * N)); CK(dout.alloc((size_t)n * C * n_lr));
+    CK(dm.up(model, s)); CK(dop.up(op, s));
+    scl_k_lowres_render<<<dim3(n_lr, C, n), 128, 0, s>>>(dm.p, dop.p, dout.p, C, N, n_lr);
+    CK(cudaGetLastError());
+    CK(dout.down(out, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
 
 #include "api_batch.inc"

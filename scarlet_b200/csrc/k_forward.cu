@@ -285,10 +285,11 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
                       const int* __restrict__ ker_idx,    // [B*P], -1 = identity (no PSF matching)
                       const int* __restrict__ active,     // [B]
                       const int* __restrict__ blend_list, // [gridDim.x / P] blends to process (compacted active list)
-                      float* __restrict__ G,              // [B, P, N]  adjoint image of every plane
-                      double* __restrict__ loss_part,     // [B, P]
+                      float* __restrict__ G,              // [B, PG, N]  adjoint image of every plane (PG >= P: the planes
+                                                          //             of low-resolution observations follow, k_lowres.cu)
+                      double* __restrict__ loss_part,     // [B, PG]
                       double* __restrict__ gram,          // [B, 8, 8]  rows r = plane, plane+P, .. of S S^T
-                      int Cm, SclPlanes pl, int Ny, int Nx)
+                      int Cm, SclPlanes pl, int PG, int Ny, int Nx)
 {
     extern __shared__ __align__(16) unsigned char smem_fwd[];
     float2* buf = reinterpret_cast<float2*>(smem_fwd);
@@ -312,7 +313,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
     const float2* Dt = Dhat_t + (size_t)(kid < 0 ? 0 : kid) * RS * F;
     const float* img = images + ((size_t)b * C + c) * N;
     const float* wgt = weights ? weights + ((size_t)b * C + c) * N : nullptr;
-    float* gout = G + ((size_t)b * C + c) * N;
+    float* gout = G + ((size_t)b * PG + c) * N;
 
     // the residual pass reads the band's image and weights one whole transform later: start them towards L2 now
     for (int i = threadIdx.x * 32; i < N; i += blockDim.x * 32) {
@@ -481,7 +482,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
         }
     }
     double tot = block_sum<double>(loss, red);
-    if (threadIdx.x == 0) loss_part[b * C + c] = 0.5 * tot;
+    if (threadIdx.x == 0) loss_part[b * PG + c] = 0.5 * tot;
 
     // ---- remaining rows r = c + 2C, ... (K > 2C only)
     for (int r = c + 2 * C; r < K; r += C) {
@@ -511,7 +512,7 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
 }
 
 #define SCL_FWD_ARGS const float*, const float*, const int*, const float*, const float*, const float2*, const int*, \
-    const int*, const int*, float*, double*, double*, int, SclPlanes, int, int
+    const int*, const int*, float*, double*, double*, int, SclPlanes, int, int, int
 template __global__ void scl_k_forward_adjoint<true>(SCL_FWD_ARGS);
 template __global__ void scl_k_forward_adjoint<false>(SCL_FWD_ARGS);
 

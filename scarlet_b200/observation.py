@@ -135,7 +135,152 @@ class Observation():
 
 
 class LowResObservation(Observation):
-    """Multi-resolution observation (observation.py:242-599): SURVEY 8(a) row A14, not built yet."""
+    """Observation at a coarser pixel scale than the model (observation.py:242-599).
 
-    def __init__(self, *args, **kwargs):
-        raise NotImplementedError("LowResObservation (multi-resolution rendering) is not implemented in scarlet_b200 yet")
+    `match` does the geometry on the host, once: pixel correspondence through the two WCS (resampling.match_patches),
+    the difference kernel between the sinc-resampled observation PSFs and the model PSF, the difference kernel
+    sinc-shifted to every low-resolution row (`_resconv_op`, as the reference stores it) -- and then folds the
+    reference's whole `_render` (pad, FFT along x, per-column phase shift + its "sinc" mask, inverse FFT, contraction
+    with `_resconv_op`, final flip) into one matrix per band, `_lr_op[c]`: [n_lr, Ny*Nx].  `_render`, `get_loss` and
+    the loop apply that matrix on the device (scl_lowres_render_f32 / scl_k_lowres).  Unrotated square frames only,
+    the geometry on which the reference's own code runs (resampling.py:90-92).
+    """
+
+    def __init__(self, images, wcs=None, psfs=None, weights=None, channels=None, padding=3, operator='exact'):
+        assert wcs is not None, "WCS is necessary for LowResObservation"
+        assert psfs is not None, "PSFs are necessary for LowResObservation"
+        assert operator in ['exact', 'bilinear', 'SVD']
+        super().__init__(images, wcs=wcs, psfs=psfs, weights=weights, channels=channels, padding=padding)
+        self._lr_op = None
+
+    @staticmethod
+    def _centred_wcs(wcs, ny, nx):
+        w = wcs.deepcopy()
+        if w.naxis == 2:
+            w.wcs.crval = 0., 0.
+            w.wcs.crpix = ny / 2. + 1, nx / 2. + 1
+        elif w.naxis == 3:
+            w.wcs.crval = 0., 0., 0.
+            w.wcs.crpix = ny / 2. + 1, nx / 2. + 1, 0.
+        return w
+
+    def match_psfs(self, psf_hr, wcs_hr, angle):
+        """Model PSF and observation PSFs on one grid at the model's resolution (observation.py:252-317)."""
+        from . import resampling, interpolation
+        psf_lr = self.frame.psfs.image
+        ny_hr, nx_hr = psf_hr.shape
+        _, ny_lr, nx_lr = psf_lr.shape
+        w_hr = self._centred_wcs(wcs_hr, ny_hr, nx_hr)
+        w_lr = self._centred_wcs(self.frame.wcs, ny_lr, nx_lr)
+        at_lr, at_hr, over_hr = resampling.match_patches(psf_hr.shape, psf_lr.shape[1:], w_hr, w_lr, isrot=False, psf=True)
+        # the reference ends the row slice at the column maximum (observation.py:305)
+        lo_y, lo_x, hi = at_lr[0].min(), at_lr[1].min(), at_lr[1].max() + 1
+        resampled = interpolation.sinc_interp(psf_lr[:, lo_y:hi, lo_x:hi], over_hr, at_hr, angle=angle)
+        target = psf_hr[over_hr[0].min():over_hr[0].max() + 1, over_hr[1].min():over_hr[1].max() + 1]
+        assert resampled[0].shape == target.shape
+        # one normalisation over all bands together, like the reference (observation.py:315-316)
+        return (target / target.sum())[None], resampled / resampled.sum()
+
+    def build_diffkernel(self, model_frame, angle):
+        """observation.py:319-343"""
+        target, observed = self.match_psfs(model_frame.psfs.image[0], model_frame.wcs, angle)
+        return fft.match_psfs(fft.Fourier(observed), fft.Fourier(target))
+
+    def _shift_kernels(self, shifts, n):
+        """Real circular kernels k_s[n] of the reference's 1-D "sinc shift" (observation.py:345-403): phase ramp
+        to the power s on the rfft frequencies, the band [m//4, -m//4) of that HALF spectrum (m = n//2+1) zeroed
+        (observation.py:381-385 as written), inverse real transform."""
+        from . import interpolation
+        ramp = interpolation.mk_shifter((n, n), real=True)[0]
+        spec = ramp[None, :] ** np.asarray(shifts, dtype=np.float64)[:, None]
+        m = spec.shape[1]
+        spec[:, m // 4:-m // 4] = 0
+        return np.fft.irfft(spec, n, axis=1)
+
+    def match(self, model_frame):
+        from . import resampling
+        if self.frame.dtype != model_frame.dtype:
+            msg = "Dtypes of model and observation different. Casting observation to {}"
+            logger.warning(msg.format(model_frame.dtype))
+            self.frame.dtype = model_frame.dtype
+            self.images = self.images.astype(model_frame.dtype)
+            if type(self.weights) is np.ndarray:
+                self.weights = self.weights.astype(model_frame.dtype)
+            self.frame.psfs.update_dtype(model_frame.dtype)
+        self._band_slice = slice(None)
+        if self.frame.channels is not model_frame.channels:
+            bmin = list(model_frame.channels).index(self.frame.channels[0])
+            bmax = list(model_frame.channels).index(self.frame.channels[-1])
+            self._band_slice = slice(bmin, bmax + 1)
+
+        def affine(w):
+            try:
+                return np.asarray(w.wcs.pc)
+            except AttributeError:
+                return np.asarray(w.cd)
+        ma, sa = affine(model_frame.wcs), affine(self.frame.wcs)
+        model_pix = np.sqrt(np.abs(ma[0, 0]) * np.abs(ma[1, 1] - ma[0, 1] * ma[1, 0]))
+        self_pix = np.sqrt(np.abs(sa[0, 0]) * np.abs(sa[1, 1] - sa[0, 1] * sa[1, 0]))
+        sv, mv = np.sum(sa, axis=0)[:2] / self_pix, np.sum(ma, axis=0)[:2] / model_pix
+        sv, mv = sv / np.sum(sv ** 2) ** .5, mv / np.sum(mv ** 2) ** .5
+        self.sin_rot, self.cos_rot = sv[0] * mv[1] - sv[1] * mv[0], np.dot(sv, mv)
+        self.isrot = np.abs(self.sin_rot) ** 2 > np.finfo(float).eps
+        if self.isrot:
+            raise NotImplementedError("rotated low-resolution frames are not supported (see the class docstring)")
+        self.sin_rot, self.cos_rot = 0, 1
+        coord_lr, coord_hr, _ = resampling.match_patches(model_frame.shape, self.frame.shape, model_frame.wcs,
+                                                        self.frame.wcs, isrot=False)
+        self.lr_shape = (int(coord_lr[0].max() - coord_lr[0].min() + 1), int(coord_lr[1].max() - coord_lr[1].min() + 1))
+        self._coord_lr, self._coord_hr = coord_lr, coord_hr
+        self.frame_coord = (np.arange(model_frame.Ny), np.arange(model_frame.Nx))
+        center_y = (coord_hr[0].max() - coord_hr[0].min() + 1) / 2
+        center_x = (coord_hr[1].max() - coord_hr[1].min() + 1) / 2
+        diff_psf = self.build_diffkernel(model_frame, None)
+        self.small_axis = self.frame.Nx <= self.frame.Ny          # always True on square frames
+        self._fft_shape = fft._get_fft_shape(model_frame.psfs, np.zeros(model_frame.shape), padding=3,
+                                             axes=[-2, -1], max=True)
+        Fy, Fx = self._fft_shape
+        self.shifts = np.array(coord_hr, dtype=np.float64)
+        self.shifts[0] -= center_y
+        self.shifts[1] -= center_x
+        self.other_shifts = np.copy(self.shifts)
+        # _resconv_op[c, j] = difference kernel shifted along y to low-resolution row j  (observation.py:516-519)
+        dpad = fft._pad(np.asarray(diff_psf.image, dtype=np.float64), self._fft_shape, axes=(1, 2))
+        ky = self._shift_kernels(self.shifts[0], Fy)                             # [n_y, Fy]
+        rows = (np.arange(Fy)[:, None] - np.arange(Fy)[None, :]) % Fy
+        resconv = np.einsum("juw,cwv->cjuv", ky[:, rows], dpad) * (self_pix / model_pix) ** 2
+        self._resconv_op = resconv.reshape(resconv.shape[0], resconv.shape[1], -1).astype(self.frame.dtype)
+        # fold `_render` into one matrix per band:
+        #   out[c, j, i'] = sum_{u,v} (model shifted along x to column i)[u, v] * resconv[c, j, u, v],  i = n_x-1-i'
+        Ny, Nx = model_frame.Ny, model_frame.Nx
+        py, px = (Fy - Ny + 1) // 2, (Fx - Nx + 1) // 2                          # fft._pad offsets
+        kx = self._shift_kernels(self.other_shifts[1], Fx)                       # [n_x, Fx]
+        cols = (np.arange(Fx)[:, None] - (np.arange(Nx)[None, :] + px)) % Fx
+        KX = kx[::-1][:, cols]                                                   # [n_x (flipped), Fx, Nx]
+        op = np.einsum("cjyv,ivx->cjiyx", resconv[:, :, py:py + Ny, :], KX)
+        C_lr, n_y, n_x = op.shape[:3]
+        assert (n_y, n_x) == self.lr_shape
+        self._lr_op = np.ascontiguousarray(op.reshape(C_lr, n_y * n_x, Ny * Nx), dtype=np.float32)
+        return self
+
+    def _window(self):
+        y0, x0 = int(self._coord_lr[0].min()), int(self._coord_lr[1].min())
+        return slice(y0, y0 + self.lr_shape[0]), slice(x0, x0 + self.lr_shape[1])
+
+    def _render(self, model):
+        """The model resampled and convolved into the low-resolution window (observation.py:524-558), on the device."""
+        m = np.asarray(model[self._band_slice], dtype=np.float32)
+        out = _native.lowres_render(m.reshape(1, m.shape[0], -1), self._lr_op)[0]
+        return out.reshape((m.shape[0],) + self.lr_shape).astype(self.frame.dtype, copy=False)
+
+    def render(self, model):
+        """For display: the window inside an otherwise empty observation frame (observation.py:560-578)."""
+        img = np.zeros(self.frame.shape)
+        ys, xs = self._window()
+        img[:, ys, xs] = self._render(model)
+        return img
+
+    def get_loss(self, model):
+        """observation.py:580-599"""
+        ys, xs = self._window()
+        return 0.5 * np.sum((self.weights * (self._render(model) - self.images[:, ys, xs])) ** 2)

@@ -318,12 +318,46 @@ def extended_sources(frame, sky_coords, observation, bg_rms, thresh=1, symmetric
     return out
 
 
-class CombinedExtendedSource(PointSource):
-    """Extended source initialised from several observations (source.py:495-548): needs the multi-resolution
-    path (LowResObservation), which is not built yet."""
+def init_combined_extended_source(sky_coord, frame, observations, bg_rms, obs_idx=0, thresh=1.,
+                                  symmetric=True, monotonic=True):
+    """SED from every observation (its own WCS and PSF heights), morphology from the detection coadd of
+    observations[obs_idx], which must live on the model's pixel grid (source.py:183-240)."""
+    try:
+        iter(observations)
+    except TypeError:
+        observations = [observations]
+    seds = [get_psf_sed(sky_coord, obs, frame) for obs in observations]
+    sed = np.concatenate(seds).flatten()
+    if np.any(sed <= 0):
+        msg = "Zero or negative SED {} at y={}, x={}".format(sed, *sky_coord)
+        (logger.warning if np.all(sed <= 0) else logger.info)(msg)
+    detect, bg_cutoff = build_detection_coadd(seds[obs_idx], bg_rms[obs_idx], observations[obs_idx], thresh)
+    center = frame.get_pixel(sky_coord)
+    morphs, ok = init_extended_morphs(detect[None], [bg_cutoff], [center], symmetric, monotonic)
+    if not ok[0]:
+        msg = "No flux above threshold={2} for source at y={0} x={1}"
+        raise SourceInitError(msg.format(*center, bg_cutoff))
+    return sed, morphs[0]
 
-    def __init__(self, *args, **kwargs):
-        raise NotImplementedError("CombinedExtendedSource needs LowResObservation, not implemented in scarlet_b200 yet")
+
+class CombinedExtendedSource(PointSource):
+    """Extended source initialised from several observations, e.g. a high- and a low-resolution one
+    (source.py:495-535): symmetric defaults to False, the initialisation always symmetrises, and -- like the
+    reference -- the constructor does not run `update()`."""
+
+    def __init__(self, frame, sky_coord, observations, bg_rms, obs_idx=0, thresh=1,
+                 symmetric=False, monotonic=True, center_step=5, delay_thresh=0, **component_kwargs):
+        self.symmetric = symmetric
+        self.monotonic = monotonic
+        self.coords = sky_coord
+        self.pixel_center = frame.get_pixel(sky_coord)
+        self.center_step = center_step
+        self.delay_thresh = delay_thresh
+        sed, morph = init_combined_extended_source(sky_coord, frame, observations, bg_rms, obs_idx,
+                                                   thresh, True, monotonic)
+        Component.__init__(self, frame, sed, morph, **component_kwargs)
+        if self.symmetric:
+            self._centroid_weight = _centroid_weight(self.frame)
 
 
 class MultiComponentSource(ComponentTree):

@@ -149,7 +149,10 @@ def pack(blends):
     images, weights, specs, ker_idx, cws, cw_idx, it0, prev = [], [], [], [], [], [], [], []
     spec_cache, cw_cache = {}, {}
     any_w = any(isinstance(o.weights, np.ndarray) for b in blends for o in b.observations)
-    plane_band = [c for o in blends[0].observations for c in range(C)[o.band_slice]]
+    is_lr = lambda o: hasattr(o, "dense_operator")       # oracle.ref_lowres.LowResObservation
+    plane_band = [c for o in blends[0].observations if not is_lr(o) for c in range(C)[o.band_slice]]
+    plane_band += [c for o in blends[0].observations if is_lr(o) for c in range(C)[o.band_slice]]
+    lr_images, lr_weights, lr_ops, lr_op_idx, lr_cache = [], [], [], [], {}
     for bl in blends:
         for s in bl.sources:
             first = len(sed)
@@ -180,6 +183,20 @@ def pack(blends):
                 conv.append(c.flags)
         comp_off.append(len(sed))
         for obs in bl.observations:
+            if not is_lr(obs):
+                continue
+            ys, xs = obs._window()
+            sub = obs.images[:, ys, xs]
+            lr_images.append(sub.reshape(len(sub), -1))
+            w = obs.weights if isinstance(obs.weights, np.ndarray) else np.ones_like(sub)
+            lr_weights.append(np.broadcast_to(w, sub.shape).reshape(len(sub), -1))
+            if id(obs) not in lr_cache:
+                lr_cache[id(obs)] = len(lr_ops)
+                lr_ops.append(obs.dense_operator(bl.frame.shape).astype(np.float32))
+            lr_op_idx.append(lr_cache[id(obs)])
+        for obs in bl.observations:
+            if is_lr(obs):
+                continue
             Co = len(obs.images)
             images.extend(obs.images)
             if any_w:
@@ -207,4 +224,6 @@ def pack(blends):
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
                 src_first=np.array(src_first),
                 **(dict(plane_band=np.array(plane_band, dtype=np.int32), n_obs=len(blends[0].observations))
-                   if len(blends[0].observations) > 1 or plane_band != list(range(C)) else {}))
+                   if len(blends[0].observations) > 1 or plane_band != list(range(C)) else {}),
+                **(dict(lr=dict(images=np.array(lr_images), weights=np.array(lr_weights), op=np.array(lr_ops),
+                                op_idx=np.array(lr_op_idx))) if lr_images else {}))

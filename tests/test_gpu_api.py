@@ -206,9 +206,53 @@ def test_two_observations_workflow(scarlet):
         assert_allclose(o.render(blend.get_model()), oo.render(gm), rtol=0, atol=3e-4 * np.abs(gm).max())
 
 
+def test_multiresolution_workflow(scarlet):
+    """Frame(wcs) + Observation + LowResObservation + CombinedExtendedSource + Blend.fit, as in the reference's
+    multi-resolution use, against the reference's own run of the same scene (tests/golden/make_golden_lowres.py)."""
+    gold = np.load(os.path.join(GOLD, "ref_golden_lowres.npz"))
+    helpers.sys_path_golden()
+    from wcs_stub import make_pair
+    for tag in ("A_", "B_"):
+        hr_img, lr_img = gold[tag + "hr_img"], gold[tag + "lr_img"]
+        whr, wlr = make_pair(hr_img.shape[1:], lr_img.shape[1:], scale=4.0, lr_offset=tuple(gold[tag + "offset"]))
+        chan = ["h0", "h1", "h2", "l0", "l1", "l2", "l3", "l4"]
+        frame = scarlet.Frame((8,) + hr_img.shape[1:], wcs=whr, psfs=gold[tag + "mpsf"][None], channels=chan)
+        ohr = scarlet.Observation(hr_img, psfs=gold[tag + "hr_psfs"], wcs=whr, channels=chan[:3]).match(frame)
+        olr = scarlet.LowResObservation(lr_img, wcs=wlr, psfs=gold[tag + "lr_psfs"], weights=gold[tag + "w_lr"],
+                                        channels=chan[3:]).match(frame)
+        assert list(olr._fft_shape) == list(gold[tag + "fft_shape"]) and olr.lr_shape == tuple(gold[tag + "lr_shape"])
+        assert_array_equal(olr._coord_lr[0], gold[tag + "coord_lr0"])
+        ref = gold[tag + "resconv_op"]
+        assert_allclose(olr._resconv_op, ref, rtol=0, atol=2e-6 * np.abs(ref).max())
+        ref = gold[tag + "render"]
+        assert_allclose(olr._render(gold[tag + "model"]), ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+        assert_allclose(olr.get_loss(gold[tag + "model"]), gold[tag + "loss"], rtol=1e-5)
+        assert olr.render(gold[tag + "model"]).shape == lr_img.shape
+    # tag A: sources + fit
+    tag = "A_"
+    hr_img, lr_img = gold[tag + "hr_img"], gold[tag + "lr_img"]
+    whr, wlr = make_pair(hr_img.shape[1:], lr_img.shape[1:], scale=4.0, lr_offset=tuple(gold[tag + "offset"]))
+    frame = scarlet.Frame((8,) + hr_img.shape[1:], wcs=whr, psfs=gold[tag + "mpsf"][None], channels=chan)
+    ohr = scarlet.Observation(hr_img, psfs=gold[tag + "hr_psfs"], wcs=whr, channels=chan[:3]).match(frame)
+    olr = scarlet.LowResObservation(lr_img, wcs=wlr, psfs=gold[tag + "lr_psfs"], weights=gold[tag + "w_lr"],
+                                    channels=chan[3:]).match(frame)
+    HY, HX = hr_img.shape[1:]
+    bg = [np.ones(3, np.float32), np.ones(5, np.float32)]
+    srcs = [scarlet.CombinedExtendedSource(frame, (round(cy) - HY / 2, round(cx) - HX / 2), [ohr, olr], bg, obs_idx=0)
+            for (cy, cx) in [(HY * .35, HX * .4), (HY * .6, HX * .62), (HY * .3, HX * .72)]]
+    blend = scarlet.Blend(srcs, [ohr, olr])
+    assert_array_equal([s.pixel_center for s in srcs], gold["A_init_centers"])
+    assert_allclose(np.array([c.sed for c in blend.components]), gold["A_init_seds"], rtol=2e-6)
+    assert_allclose(np.array([c.morph for c in blend.components]), gold["A_init_morphs"], rtol=0, atol=3e-6)
+    ref = gold["A_mse"]
+    blend.fit(len(ref), e_rel=1e-9)
+    assert_allclose(blend.mse, ref, rtol=1e-4)
+    assert_array_equal([s.pixel_center for s in srcs], gold["A_centers"])
+    gm = gold["A_fit_model"]
+    assert_allclose(blend.get_model(), gm, rtol=0, atol=1e-4 * np.abs(gm).max())
+
+
 def test_unsupported_paths_are_loud(scarlet):
-    with pytest.raises(NotImplementedError):
-        scarlet.LowResObservation(np.zeros((1, 4, 4)))
     frame, obs, srcs, blend = _scene(scarlet, "sim")
     f64 = scarlet.Frame(obs.images.shape, psfs=frame.psfs.image.astype(np.float64), dtype=np.float64)
     c = scarlet.Component(f64, np.ones(6), np.ones((40, 59)))

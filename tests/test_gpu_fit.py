@@ -88,6 +88,34 @@ def test_multiple_observations_approximate_L(nat):
     assert_allclose(out["logL"][0, :10], blend.mse, rtol=2e-4)
 
 
+def test_lockstep_low_resolution_observation(nat):
+    """A high-resolution Observation + a LowResObservation of other bands (observation.py:242-599, row A14): the
+    low-resolution planes go through scl_k_lowres (resample-and-convolve operator, residual, transpose), every
+    iteration against the oracle's restated _render and its adjoint."""
+    import os
+    gold = np.load(os.path.join(helpers.GOLD, "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "A_")
+    srcs, blend = helpers.lowres_blend(gold, frame, ohr, olr)
+    _lockstep(nat, blend, 10, e_rel=1e-9)
+
+
+def test_low_resolution_free_running_vs_reference(nat):
+    """The same scene free-running against the reference's own 12 iterations (make_golden_lowres.py)."""
+    import os
+    gold = np.load(os.path.join(helpers.GOLD, "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "A_")
+    srcs, blend = helpers.lowres_blend(gold, frame, ohr, olr)
+    ref = gold["A_mse"]
+    bt = nat.Batch(**helpers.pack([blend]))
+    bt.fit(len(ref), 1e-9)
+    out = bt.download()
+    bt.close()
+    assert_allclose(out["logL"][0, :len(ref)], ref, rtol=1e-4)
+    gm = gold["A_fit_model"]
+    assert_allclose(_model(out, 0, len(srcs)), gm, rtol=0, atol=1e-4 * np.abs(gm).max())
+    assert_array_equal(out["center"], gold["A_centers"])
+
+
 def test_multicomponent_free_running_vs_reference(nat):
     """The same scene free-running against the reference's own run (tests/golden/make_golden_multi.py)."""
     g, _, _, srcs, blend = helpers.multi_blend()
