@@ -131,6 +131,13 @@ typedef struct {
     int32_t n_lr_op;                /* distinct geometries */
     const float* lr_op;             /* [n_lr_op][Plr][n_lr][Ny*Nx] */
     const int32_t* lr_op_idx;       /* [B] */
+    /* Scene mode: frames larger than one 128x128 convolution tile, or blends with more than 8 components
+     * (BASELINE config 4).  The model and the residual go through HBM, the convolution runs as overlap-save tiles of
+     * 128 - 2*ker_half pixels, and the constraint kernels keep their working copies in an HBM scratch.  Chosen
+     * automatically when the shape or a component count needs it; scene_mode = 1 forces it (tests).  Needs
+     * ker_half when any ker_idx >= 0; only approximate_L fits (blend.py:189-202) and no low-resolution planes yet. */
+    int32_t ker_half;               /* half-width (k/2) of the truncated difference kernels; 0 = not given */
+    int32_t scene_mode;             /* 0 = automatic, 1 = force scene mode */
 } scl_batch_desc;
 
 /* Allocate device state for `desc`'s sizes and upload it. */

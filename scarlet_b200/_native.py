@@ -36,6 +36,7 @@ class BatchDesc(ctypes.Structure):
         ("n_planes", ctypes.c_int32), ("plane_band", c_void_p), ("n_obs", ctypes.c_int32),
         ("n_lr_planes", ctypes.c_int32), ("lr_n", ctypes.c_int32), ("lr_images", c_void_p), ("lr_weights", c_void_p),
         ("n_lr_op", ctypes.c_int32), ("lr_op", c_void_p), ("lr_op_idx", c_void_p),
+        ("ker_half", ctypes.c_int32), ("scene_mode", ctypes.c_int32),
     ]
 
 
@@ -182,6 +183,14 @@ def monotonic_tables_host(Ny, Nx):
     return _tables[key]
 
 
+def kernel_half(ky, kx, Ny, Nx):
+    """Reach of a ky x kx difference kernel on either side of a pixel, as placed by kernel_spectrum."""
+    Fy, Fx = conv_fft_shape(Ny, ky, False), conv_fft_shape(Nx, kx, True)
+    offy = (Fy - ky + 1) // 2 - Fy // 2
+    offx = (Fx - kx + 1) // 2 - Fx // 2
+    return int(max(-offy, ky - 1 + offy, -offx, kx - 1 + offx))
+
+
 def kernel_spectrum(kernels, Ny, Nx):
     """rfft2 of real-space difference kernels [n, ky, kx] on the 128x128 periodic grid.
 
@@ -194,8 +203,9 @@ def kernel_spectrum(kernels, Ny, Nx):
     Fy, Fx = conv_fft_shape(Ny, ky, False), conv_fft_shape(Nx, kx, True)
     offy = (Fy - ky + 1) // 2 - Fy // 2
     offx = (Fx - kx + 1) // 2 - Fx // 2
-    if Ny - offy > FFT_EDGE or Ny + ky - 1 + offy > FFT_EDGE or Nx - offx > FFT_EDGE or Nx + kx - 1 + offx > FFT_EDGE:
-        raise NotImplementedError("frame + PSF half-width exceeds the 128x128 convolution tile")
+    # frames that do not fit one tile together with the kernel's reach run as overlap-save tiles (scene mode)
+    if 2 * kernel_half(ky, kx, Ny, Nx) >= FFT_EDGE - 8:
+        raise NotImplementedError("difference kernel too wide for the 128-point convolution tile")
     grid = np.zeros((n, FFT_EDGE, FFT_EDGE), dtype=np.float64)
     iy = (np.arange(ky) + offy) % FFT_EDGE
     ix = (np.arange(kx) + offx) % FFT_EDGE
@@ -294,7 +304,7 @@ class Batch:
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
                  kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None,
-                 plane_band=None, n_obs=1, lr=None):
+                 plane_band=None, n_obs=1, lr=None, ker_half=0, scene_mode=0):
         """plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
         all observations stacked as P planes, plane p seeing model band plane_band[p] (include/scarlet_b200.h)."""
         require_device()
@@ -307,6 +317,9 @@ class Batch:
         self.Plr = 0 if lr is None else int(np.shape(lr["images"])[1])
         self.P = self.C if plane_band is None else len(self.plane_band) - self.Plr
         self.n_obs = int(n_obs)
+        # scene mode (frames beyond one convolution tile / > 8 components per blend): needs the half-width of the
+        # difference kernels for its overlap-save tiles
+        self.ker_half, self.scene_mode = int(ker_half), int(scene_mode)
         self.stream = stream
         self._h = c_void_p()
         self._keep = None
@@ -347,6 +360,7 @@ class Batch:
         for name in ("comp_off", "sed", "morph", "cflags", "center", "shift", "conv", "images", "weights",
                      "kernel_spec", "ker_idx", "cw", "cw_idx", "it0", "prev_loss", "src_first"):
             setattr(d, name, _p(a[name]))
+        d.ker_half, d.scene_mode = self.ker_half, self.scene_mode
         if self.plane_band is not None:
             d.n_planes, d.plane_band, d.n_obs = self.P, _p(self.plane_band), self.n_obs
         if self.lr is not None:

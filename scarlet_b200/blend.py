@@ -132,6 +132,8 @@ def pack_blends(blends):
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
                 src_first=np.array(src_first), plane_band=np.array(plane_band, dtype=np.int32),
                 n_obs=len(blends[0].observations),
+                ker_half=max([_native.kernel_half(*o._diff_kernels.image.shape[1:], Ny, Nx) for b in blends for o in b.observations
+                              if not isinstance(o, LowResObservation) and o._diff_kernels is not None] + [0]),
                 lr=dict(images=np.array(lr_images), weights=np.array(lr_weights), op=np.array(lr_ops),
                         op_idx=np.array(lr_op_idx)) if lr_images else None)
 

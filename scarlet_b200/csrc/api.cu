@@ -13,6 +13,7 @@
 #include "k_grad.cu"
 #include "k_prox.cu"
 #include "k_lowres.cu"
+#include "k_scene.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
@@ -60,9 +61,9 @@ struct Tables {
 constexpr size_t kPlanBudget = (size_t)768 << 20;    // bytes of sweep plans per shape
 std::mutex g_mu;
 std::map<std::pair<int, int>, Tables> g_tables;
-int* g_nfl = nullptr;        // device [1024]
-int* g_nfl_even = nullptr;   // device [1024]
-constexpr int kNflN = 1024;
+int* g_nfl = nullptr;        // device [kNflN]
+int* g_nfl_even = nullptr;   // device [kNflN]
+constexpr int kNflN = 4096;
 bool g_attr_done = false;
 
 int ensure_globals() {
@@ -84,6 +85,8 @@ int ensure_globals() {
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_scene_conv<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_scene_conv<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         const int big = 200 * 1024;
         CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_source_center, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -112,9 +115,11 @@ struct DevBuf {
 
 // Sweep plans of every centre of the shape (prox_dev.cuh "precomputed per-centre plan"): count, prefix on the
 // host, emit.  Shapes whose plans would not fit the entry format or the budget keep pbits = 0.
+size_t prox_smem(int Ny, int Nx);
 int build_plans(int Ny, int Nx, Tables* t) {
     const int N = Ny * Nx;
     if (Ny < 2 || Nx < 2 || Ny > 256 || Nx > 256) return SCL_OK;
+    if (prox_smem(Ny, Nx) > 200 * 1024) return SCL_OK;       // scene-mode shapes: generic level loop
     int pbits = 1;
     while ((1 << pbits) < N) pbits++;
     const unsigned long long rows = 9ull * (2 * Ny - 1) * (2 * Nx - 1);
@@ -160,9 +165,23 @@ size_t prox_smem(int Ny, int Nx) {
     return (((Nx + 4) & ~3) + n4) * sizeof(float) + zt;
 }
 
-int check_shape(int Ny, int Nx) {
+// shared memory of the constraint kernels in scene mode: the symmetry tables only
+size_t prox_smem_scene(int Ny, int Nx) {
+    int mx = Ny > Nx ? Ny : Nx;
+    return (size_t)(3 * (2 * mx - 1) + 2 * Nx + 32) * sizeof(float);
+}
+// floats of HBM scratch per CTA in scene mode (layout of prox_smem without the tables, + a back pad)
+size_t prox_scratch_floats(int Ny, int Nx) {
+    size_t n4 = ((size_t)Ny * Nx + 3) & ~(size_t)3;
+    return (size_t)((Nx + 4) & ~3) + n4 + (size_t)Ny * ((Nx + 3) & ~3) + (size_t)((Nx + 8) & ~3);
+}
+bool fits_smem(int Ny, int Nx) { return prox_smem(Ny, Nx) <= 200 * 1024; }
+
+int check_shape(int Ny, int Nx, bool allow_big = false) {
     if (Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "empty image shape%s%s");
-    if (prox_smem(Ny, Nx) > 200 * 1024 || 2 * Ny + 10 >= kNflN || 2 * Nx + 10 >= kNflN)
+    if (2 * Ny + 10 >= kNflN || 2 * Nx + 10 >= kNflN) return fail(SCL_E_LIMIT, "image edge above 2042 pixels%s%s");
+    if (allow_big) return SCL_OK;
+    if (prox_smem(Ny, Nx) > 200 * 1024)
         return fail(SCL_E_LIMIT, "image shape exceeds the shared-memory resident limit%s%s");
     return SCL_OK;
 }
@@ -221,7 +240,7 @@ int scl_stream_destroy(void* stream) {
 }
 
 int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab) {
-    int rc = check_shape(Ny, Nx);
+    int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
     if (!wtab || !ctab) return fail(SCL_E_ARG, "null table%s%s");
     size_t n = (size_t)(2 * Ny - 1) * (2 * Nx - 1) * 8;

@@ -35,6 +35,11 @@ struct SclProxArgs {
     int it_override;          // >= 0: the iteration number update() sees (0 = source construction)
     double e_rel2;
     unsigned long long* phase_clk;   // optional [8]: summed clock64 per phase over all CTAs (profiling; nullptr = off)
+    // Frames too large for shared memory (scene mode, DESIGN "large frames"): the working copy X and the symmetry
+    // scratch Z of CTA i live at xscratch + i * xstride in HBM/L2 (same layout as the shared-memory one); only the
+    // symmetry tables stay in shared memory.  nullptr: everything in shared memory.
+    float* xscratch;
+    size_t xstride;
 };
 
 // dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
@@ -140,9 +145,10 @@ scl_k_prox(SclProxArgs a)
     const int b = a.comp_blend[k];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* X = smem_f + ((Nx + 4) & ~3);        // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
+    float* xbase = a.xscratch ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_f;
+    float* X = xbase + ((Nx + 4) & ~3);         // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
     float* Z = X + ((N + 3) & ~3);
-    float* tab = Z + Ny * ((Nx + 3) & ~3);
+    float* tab = a.xscratch ? smem_f : Z + Ny * ((Nx + 3) & ~3);
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
@@ -305,7 +311,8 @@ scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
     const int b = a.comp_blend[k0];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* M = smem_s + ((Nx + 4) & ~3);
+    float* xbase = a.xscratch ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_s;
+    float* M = xbase + ((Nx + 4) & ~3);
     float* Xk = M + ((N + 3) & ~3);
     __shared__ double red[32];
     __shared__ int sc[2];

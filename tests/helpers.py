@@ -153,6 +153,8 @@ def pack(blends):
     plane_band = [c for o in blends[0].observations if not is_lr(o) for c in range(C)[o.band_slice]]
     plane_band += [c for o in blends[0].observations if is_lr(o) for c in range(C)[o.band_slice]]
     lr_images, lr_weights, lr_ops, lr_op_idx, lr_cache = [], [], [], [], {}
+    ker_half = max([nat.kernel_half(*o.diff_kernels.shape[1:], Ny, Nx) for b in blends for o in b.observations
+                    if not is_lr(o) and o.diff_kernels is not None] + [0])
     for bl in blends:
         for s in bl.sources:
             first = len(sed)
@@ -222,7 +224,7 @@ def pack(blends):
                 conv=np.array(conv), images=np.array(images), weights=np.array(weights) if any_w else None,
                 kernel_spec=np.concatenate(specs) if specs else None, ker_idx=np.array(ker_idx),
                 cw=np.array(cws), cw_idx=np.array(cw_idx), it0=np.array(it0), prev_loss=np.array(prev),
-                src_first=np.array(src_first),
+                src_first=np.array(src_first), ker_half=ker_half,
                 **(dict(plane_band=np.array(plane_band, dtype=np.int32), n_obs=len(blends[0].observations))
                    if len(blends[0].observations) > 1 or plane_band != list(range(C)) else {}),
                 **(dict(lr=dict(images=np.array(lr_images), weights=np.array(lr_weights), op=np.array(lr_ops),

@@ -22,16 +22,17 @@ def _model(out, k0, k1):
     return np.einsum("kc,kyx->cyx", out["sed"][k0:k1].astype(np.float64), out["morph"][k0:k1].astype(np.float64))
 
 
-def _lockstep(nat, blend, n_steps, e_rel=1e-2):
+def _lockstep(nat, blend, n_steps, e_rel=1e-2, approximate_L=False, **batch_kw):
     """Each iteration: start the GPU from the oracle's state, run one iteration on both,
     compare everything the iteration produces."""
     for step in range(n_steps):
         p = helpers.pack([blend])
+        p.update(batch_kw)
         bt = nat.Batch(**p)
-        bt.fit(1, e_rel)
+        bt.fit(1, e_rel, approximate_L=approximate_L)
         out = bt.download()
         bt.close()
-        conv = blend.step(e_rel)
+        conv = blend.step(e_rel, approximate_L=approximate_L)
         assert_allclose(out["logL"][0, 0], blend.mse[-1], rtol=REL)
         assert_allclose(out["lipschitz"][0], [blend.L_sed, blend.L_morph], rtol=2e-6)
         ref_c = np.array([getattr(s, "pixel_center", (0, 0)) for s in blend.sources for _ in s.components])
@@ -114,6 +115,52 @@ def test_low_resolution_free_running_vs_reference(nat):
     gm = gold["A_fit_model"]
     assert_allclose(_model(out, 0, len(srcs)), gm, rtol=0, atol=1e-4 * np.abs(gm).max())
     assert_array_equal(out["center"], gold["A_centers"])
+
+
+# ---------------------------------------------------------------- scene mode (k_scene.cu)
+def test_scene_mode_equals_fused_mode(nat):
+    """The three-kernel K1 (render, overlap-save convolution tiles, adjoint) + HBM-scratch constraint kernels against
+    the fused shared-memory path on the same blends (approximate_L, 20 iterations)."""
+    blends = [helpers.synthetic_blend(s, kmin=3, kmax=6)[3] for s in (11, 12, 13)]
+    outs = []
+    for mode in (0, 1):
+        bt = nat.Batch(scene_mode=mode, **helpers.pack(blends))
+        bt.fit(20, 0.0, approximate_L=True)
+        outs.append(bt.download())
+        bt.close()
+    a, b = outs
+    assert_allclose(b["logL"], a["logL"], rtol=2e-5)         # 20 free-running fp32 iterations
+    assert_array_equal(b["center"], a["center"])
+    assert_allclose(b["sed"], a["sed"], rtol=0, atol=1e-5 * np.abs(a["sed"]).max())
+    assert_allclose(b["morph"], a["morph"], rtol=0, atol=1e-5)
+
+
+@pytest.mark.parametrize("tag", ["hsc", "sim"])
+def test_scene_lockstep_npz(nat, tag):
+    """configs 1 and 2 forced through scene mode, approximate_L (blend.py:189-202), every iteration vs the oracle"""
+    _, _, _, blend = helpers.npz_blend(tag)
+    _lockstep(nat, blend, 12, approximate_L=True, scene_mode=1)
+
+
+def test_scene_lockstep_multicomponent(nat):
+    _, _, _, _, blend = helpers.multi_blend()
+    _lockstep(nat, blend, 8, approximate_L=True, scene_mode=1)
+
+
+def test_scene_lockstep_large_frame(nat):
+    """A 5-band 150x140 frame with 10-12 sources: beyond one convolution tile, beyond the shared-memory resident
+    constraint kernels and beyond 8 components -- scene mode chosen automatically; every iteration vs the oracle."""
+    _, _, srcs, blend = helpers.synthetic_blend(21, Ny=150, Nx=140, kmin=10, kmax=12)
+    assert len(blend.components) > 8
+    _lockstep(nat, blend, 6, approximate_L=True)
+
+
+def test_scene_mode_needs_approximate_L(nat):
+    _, _, _, blend = helpers.npz_blend("sim")
+    bt = nat.Batch(scene_mode=1, **helpers.pack([blend]))
+    with pytest.raises(NotImplementedError):
+        bt.fit(2, 1e-2)
+    bt.close()
 
 
 def test_multicomponent_free_running_vs_reference(nat):

@@ -155,6 +155,7 @@ def test_errors(nat):
     with pytest.raises(TypeError):
         nat.prox_weighted_monotonic(x.astype(np.int32), [(2, 2)])
     with pytest.raises(NotImplementedError):
-        nat.kernel_spectrum(np.zeros((1, 41, 41)), 120, 64)
+        nat.kernel_spectrum(np.zeros((1, 125, 125)), 64, 64)      # kernel wider than a convolution tile
+    assert nat.kernel_spectrum(np.zeros((1, 41, 41)), 512, 512).shape == (1, 128, 65)     # big frames: tiled
     y = np.zeros((0, 5, 5), np.float32)
     nat.prox_weighted_monotonic(y, np.zeros((0, 2)))          # empty batch is a no-op
