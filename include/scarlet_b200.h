@@ -135,7 +135,7 @@ typedef struct {
      * (BASELINE config 4).  The model and the residual go through HBM, the convolution runs as overlap-save tiles of
      * 128 - 2*ker_half pixels, and the constraint kernels keep their working copies in an HBM scratch.  Chosen
      * automatically when the shape or a component count needs it; scene_mode = 1 forces it (tests).  Needs
-     * ker_half when any ker_idx >= 0; only approximate_L fits (blend.py:189-202) and no low-resolution planes yet. */
+     * ker_half when any ker_idx >= 0; no low-resolution planes yet. */
     int32_t ker_half;               /* half-width (k/2) of the truncated difference kernels; 0 = not given */
     int32_t scene_mode;             /* 0 = automatic, 1 = force scene mode */
 } scl_batch_desc;

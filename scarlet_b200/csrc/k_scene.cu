@@ -172,3 +172,177 @@ extern "C" __global__ void scl_k_scene_lipschitz(const float* __restrict__ A, co
     lips[2 * b] = (float)(LA * n_obs);
     lips[2 * b + 1] = (float)(LS * n_obs);
 }
+
+// ---------------------------------------------------------------- exact Lipschitz constants for any K
+// Blend._set_lipschitz (blend.py:203-217): L_sed = lambda_max(S S^T), L_morph = lambda_max(A^T A).
+// Gram matrix: gram[b][i][j] = sum_p S[k0+i][p] S[k0+j][p], Kp x Kp (Kp = padded component count, zero beyond K),
+// float32 products accumulated per CTA over a chunk of pixels, chunks combined with float64 atomics.
+// grid: (tiles * tiles, chunks, B), 32x32 output tile per CTA, 256 threads (2x2 outputs each).
+#define SCN_GT 32
+#define SCN_GP 64
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_scene_gram(const float* __restrict__ S, const int* __restrict__ comp_off, const int* __restrict__ active,
+                 double* __restrict__ gram, int Kp, int N, int chunk)
+{
+    __shared__ float sa[SCN_GT][SCN_GP + 1], sb[SCN_GT][SCN_GP + 1];
+    const int b = blockIdx.z;
+    if (!active[b]) return;
+    const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
+    const int nt = Kp / SCN_GT, ti = blockIdx.x / nt, tj = blockIdx.x % nt;
+    if (tj < ti || ti * SCN_GT >= K || tj * SCN_GT >= K) return;          // upper triangle, mirrored on write
+    const int p_lo = blockIdx.y * chunk, p_hi = min(N, p_lo + chunk);
+    const int r = (threadIdx.x >> 4) * 2, c = (threadIdx.x & 15) * 2;
+    float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+    for (int p0 = p_lo; p0 < p_hi; p0 += SCN_GP) {
+        for (int i = threadIdx.x; i < SCN_GT * SCN_GP; i += blockDim.x) {
+            const int row = i / SCN_GP, col = i % SCN_GP, p = p0 + col;
+            const int ka = ti * SCN_GT + row, kb = tj * SCN_GT + row;
+            sa[row][col] = (ka < K && p < p_hi) ? S[(size_t)(k0 + ka) * N + p] : 0.f;
+            sb[row][col] = (kb < K && p < p_hi) ? S[(size_t)(k0 + kb) * N + p] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (int q = 0; q < SCN_GP; q++) {
+            const float a0 = sa[r][q], a1 = sa[r + 1][q], b0 = sb[c][q], b1 = sb[c + 1][q];
+            acc[0][0] += a0 * b0; acc[0][1] += a0 * b1; acc[1][0] += a1 * b0; acc[1][1] += a1 * b1;
+        }
+        __syncthreads();
+    }
+    double* g = gram + (size_t)b * Kp * Kp;
+#pragma unroll
+    for (int u = 0; u < 2; u++)
+#pragma unroll
+        for (int v = 0; v < 2; v++) {
+            const int i = ti * SCN_GT + r + u, j = tj * SCN_GT + c + v;
+            if (i < K && j < K && (ti != tj || j >= i)) {
+                atomicAdd(g + (size_t)i * Kp + j, (double)acc[u][v]);
+                if (i != j) atomicAdd(g + (size_t)j * Kp + i, (double)acc[u][v]);
+            }
+        }
+}
+
+// f32 working copy of the Gram matrix, scaled by 1/trace.  grid: (Kp, B)
+extern "C" __global__ void scl_k_scene_eig_init(const double* __restrict__ gram, float* __restrict__ M, int Kp)
+{
+    __shared__ double red[32];
+    const double* g = gram + (size_t)blockIdx.y * Kp * Kp;
+    double tr = 0.0;
+    for (int i = threadIdx.x; i < Kp; i += blockDim.x) tr += g[(size_t)i * Kp + i];
+    tr = block_sum<double>(tr, red);
+    const double s = tr > 0.0 ? 1.0 / tr : 0.0;
+    float* m = M + ((size_t)blockIdx.y * Kp + blockIdx.x) * Kp;
+    for (int j = threadIdx.x; j < Kp; j += blockDim.x) m[j] = (float)(g[(size_t)blockIdx.x * Kp + j] * s);
+}
+
+// fro[b] = sum_ij M_ij^2 = trace(M M) for symmetric M.  grid: B
+extern "C" __global__ void __launch_bounds__(1024)
+scl_k_scene_frob(const float* __restrict__ M, double* __restrict__ fro, int Kp)
+{
+    __shared__ double red[32];
+    const float* m = M + (size_t)blockIdx.x * Kp * Kp;
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < Kp * Kp; i += blockDim.x) { const double v = m[i]; acc += v * v; }
+    acc = block_sum<double>(acc, red);
+    if (threadIdx.x == 0) fro[blockIdx.x] = acc;
+}
+
+// Normalised squaring out = in * in / trace(in * in): the top eigenvector's share of every column doubles its
+// exponent per call (K2 does the same in registers for K <= 8).  grid: (Kp/32, Kp/32, B); block (32, 8)
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const double* __restrict__ fro, int Kp)
+{
+    __shared__ float ta[32][33], tb[32][33];
+    const int b = blockIdx.z;
+    const float* A = in + (size_t)b * Kp * Kp;
+    const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32, tx = threadIdx.x, ty = threadIdx.y;
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    for (int l0 = 0; l0 < Kp; l0 += 32) {
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            ta[ty + 8 * u][tx] = A[(size_t)(i0 + ty + 8 * u) * Kp + l0 + tx];
+            tb[ty + 8 * u][tx] = A[(size_t)(l0 + ty + 8 * u) * Kp + j0 + tx];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int l = 0; l < 32; l++) {
+            const float bv = tb[l][tx];
+#pragma unroll
+            for (int u = 0; u < 4; u++) acc[u] += ta[ty + 8 * u][l] * bv;
+        }
+        __syncthreads();
+    }
+    const float s = fro[b] > 0.0 ? (float)(1.0 / fro[b]) : 0.f;
+#pragma unroll
+    for (int u = 0; u < 4; u++) out[(size_t)b * Kp * Kp + (size_t)(i0 + ty + 8 * u) * Kp + j0 + tx] = acc[u] * s;
+}
+
+// Rayleigh quotient of the heaviest column of the squared matrix against the float64 Gram matrix -> lambda_max(S S^T);
+// lambda_max(A^T A) (C x C, float64 squarings by one thread); loss sum; lips.  grid: B, block 256
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ gram, const float* __restrict__ A,
+                       const int* __restrict__ comp_off, const double* __restrict__ loss_tile,
+                       const int* __restrict__ active, double* __restrict__ logL, float* __restrict__ lips,
+                       int Kp, int C, int n_loss, int step, int logL_cap, int n_obs)
+{
+    __shared__ double red[32];
+    __shared__ int sbest;
+    __shared__ double sLS;
+    const int b = blockIdx.x;
+    if (!active[b]) return;
+    const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
+    const float* m = M + (size_t)b * Kp * Kp;
+    const double* g = gram + (size_t)b * Kp * Kp;
+    if (threadIdx.x == 0) {
+        int best = 0;
+        for (int i = 1; i < K; i++) if (m[(size_t)i * Kp + i] > m[(size_t)best * Kp + best]) best = i;
+        sbest = best;
+        // lambda_max(A^T A): C x C, normalised squarings in float64, Rayleigh quotient of the heaviest column
+        double T[SCL_MAX_BANDS][SCL_MAX_BANDS], Q[SCL_MAX_BANDS][SCL_MAX_BANDS], G0[SCL_MAX_BANDS][SCL_MAX_BANDS];
+        for (int i = 0; i < C; i++)
+            for (int j = 0; j < C; j++) {
+                double s = 0.0;
+                for (int k = 0; k < K; k++) s += (double)A[(size_t)(k0 + k) * C + i] * (double)A[(size_t)(k0 + k) * C + j];
+                G0[i][j] = T[i][j] = s;
+            }
+        for (int it = 0; it < 24; it++) {
+            double tr = 0.0;
+            for (int i = 0; i < C; i++)
+                for (int j = 0; j < C; j++) {
+                    double s = 0.0;
+                    for (int l = 0; l < C; l++) s += T[i][l] * T[l][j];
+                    Q[i][j] = s;
+                    if (i == j) tr += s;
+                }
+            const double sc = tr > 0.0 ? 1.0 / tr : 0.0;
+            for (int i = 0; i < C; i++) for (int j = 0; j < C; j++) T[i][j] = Q[i][j] * sc;
+        }
+        int bc = 0;
+        for (int i = 1; i < C; i++) if (T[i][i] > T[bc][bc]) bc = i;
+        double num = 0.0, den = 0.0;
+        for (int i = 0; i < C; i++) {
+            double w = 0.0;
+            for (int j = 0; j < C; j++) w += G0[i][j] * T[j][bc];
+            num += T[i][bc] * w; den += T[i][bc] * T[i][bc];
+        }
+        sLS = den > 0.0 ? num / den : 0.0;
+    }
+    __syncthreads();
+    const int best = sbest;
+    double num = 0.0, den = 0.0;
+    for (int i = threadIdx.x; i < K; i += blockDim.x) {
+        double w = 0.0;
+        for (int j = 0; j < K; j++) w += g[(size_t)i * Kp + j] * (double)m[(size_t)j * Kp + best];
+        const double vi = (double)m[(size_t)i * Kp + best];
+        num += vi * w; den += vi * vi;
+    }
+    num = block_sum<double>(num, red);
+    den = block_sum<double>(den, red);
+    if (threadIdx.x == 0) {
+        double total = 0.0;
+        for (int i = 0; i < n_loss; i++) total += loss_tile[(size_t)b * n_loss + i];
+        if (step < logL_cap) logL[(size_t)b * logL_cap + step] = total;
+        const double LA = den > 0.0 ? num / den : 0.0;
+        lips[2 * b] = (float)(LA * n_obs);
+        lips[2 * b + 1] = (float)(sLS * n_obs);
+    }
+}

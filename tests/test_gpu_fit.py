@@ -135,16 +135,19 @@ def test_scene_mode_equals_fused_mode(nat):
     assert_allclose(b["morph"], a["morph"], rtol=0, atol=1e-5)
 
 
+@pytest.mark.parametrize("approx", [True, False])
 @pytest.mark.parametrize("tag", ["hsc", "sim"])
-def test_scene_lockstep_npz(nat, tag):
-    """configs 1 and 2 forced through scene mode, approximate_L (blend.py:189-202), every iteration vs the oracle"""
+def test_scene_lockstep_npz(nat, tag, approx):
+    """configs 1 and 2 forced through scene mode, with approximate_L (blend.py:189-202) and with the exact constants
+    (Gram matrix by tiles, normalised squarings, Rayleigh quotient; blend.py:203-217), every iteration vs the oracle"""
     _, _, _, blend = helpers.npz_blend(tag)
-    _lockstep(nat, blend, 12, approximate_L=True, scene_mode=1)
+    _lockstep(nat, blend, 12, approximate_L=approx, scene_mode=1)
 
 
-def test_scene_lockstep_multicomponent(nat):
+@pytest.mark.parametrize("approx", [True, False])
+def test_scene_lockstep_multicomponent(nat, approx):
     _, _, _, _, blend = helpers.multi_blend()
-    _lockstep(nat, blend, 8, approximate_L=True, scene_mode=1)
+    _lockstep(nat, blend, 8, approximate_L=approx, scene_mode=1)
 
 
 def test_scene_lockstep_large_frame(nat):
@@ -152,15 +155,8 @@ def test_scene_lockstep_large_frame(nat):
     constraint kernels and beyond 8 components -- scene mode chosen automatically; every iteration vs the oracle."""
     _, _, srcs, blend = helpers.synthetic_blend(21, Ny=150, Nx=140, kmin=10, kmax=12)
     assert len(blend.components) > 8
-    _lockstep(nat, blend, 6, approximate_L=True)
-
-
-def test_scene_mode_needs_approximate_L(nat):
-    _, _, _, blend = helpers.npz_blend("sim")
-    bt = nat.Batch(scene_mode=1, **helpers.pack([blend]))
-    with pytest.raises(NotImplementedError):
-        bt.fit(2, 1e-2)
-    bt.close()
+    _lockstep(nat, blend, 4, approximate_L=True)
+    _lockstep(nat, blend, 4, approximate_L=False)
 
 
 def test_multicomponent_free_running_vs_reference(nat):
