@@ -77,9 +77,11 @@ int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, dou
                     const float* psf, int ph, int pw, int do_max_pixel, int do_centroid, void* stream);
 /* Observation.render (observation.py:203-220): out = convolve(model, diff kernel) per band.
  * model/out float32 [n][C][Ny][Nx]; spec complex64 [n_ker][128][65] (rfft2 of the truncated difference kernel
- * with its centre tap at index 0); ker_idx int32 [n*C] (-1 = identity).  adjoint != 0 applies the transpose. */
+ * with its centre tap at index 0); ker_idx int32 [n*C] (-1 = identity).  adjoint != 0 applies the transpose.
+ * ker_half: reach (k/2) of the kernels; frames with Ny + ker_half > 128 run as overlap-save tiles (0 = not given:
+ * single-tile frames only). */
 int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int Nx, const float* spec, int n_ker,
-                     const int32_t* ker_idx, int adjoint, void* stream);
+                     const int32_t* ker_idx, int adjoint, int ker_half, void* stream);
 /* LowResObservation._render (observation.py:524-558) as its matrix: out[i][c][q] = sum_p op[c][q][p] model[i][c][p].
  * model float32 [n][C][N] (the observation's bands of the model, N = Ny*Nx); op float32 [C][n_lr][N], the
  * resample-and-convolve operator of one geometry (built once by LowResObservation.match); out float32 [n][C][n_lr]. */

@@ -271,8 +271,9 @@ def measure(x, centers, psf=None, do_max=True, do_centroid=True):
     return c, s
 
 
-def convolve(model, spec, ker_idx, adjoint=False):
-    """model float32 [n, C, Ny, Nx]; spec complex64 [n_ker,128,65]; ker_idx int32 [n*C]."""
+def convolve(model, spec, ker_idx, adjoint=False, ker_half=0):
+    """model float32 [n, C, Ny, Nx]; spec complex64 [n_ker,128,65]; ker_idx int32 [n*C]; ker_half: reach of the
+    kernels (kernel_half), needed for frames beyond one convolution tile."""
     require_device()
     model = np.ascontiguousarray(model, dtype=np.float32)
     n, C, Ny, Nx = model.shape
@@ -281,7 +282,8 @@ def convolve(model, spec, ker_idx, adjoint=False):
     n_ker = 0 if spec is None else len(spec)
     if spec is not None:
         spec = np.ascontiguousarray(spec, dtype=np.complex64)
-    _check(lib().scl_convolve_f32(_p(model), _p(out), n, C, Ny, Nx, _p(spec), n_ker, _p(ker_idx), int(adjoint), None))
+    _check(lib().scl_convolve_f32(_p(model), _p(out), n, C, Ny, Nx, _p(spec), n_ker, _p(ker_idx), int(adjoint),
+                                  int(ker_half), None))
     return out
 
 

@@ -85,8 +85,9 @@ int ensure_globals() {
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
-        CK(cudaFuncSetAttribute(scl_k_scene_conv<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
-        CK(cudaFuncSetAttribute(scl_k_scene_conv<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_scene_conv<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_scene_conv<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
+        CK(cudaFuncSetAttribute(scl_k_scene_conv<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         const int big = 200 * 1024;
         CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_source_center, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
@@ -191,12 +192,14 @@ template <typename T, bool NEAREST>
 static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T thresh, void* stream) {
     if (n == 0) return SCL_OK;
     if (!x || !centers || n < 0) return fail(SCL_E_ARG, "bad argument%s%s");
-    int rc = check_shape(Ny, Nx);
+    int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
     if ((rc = ensure_globals())) return rc;
     for (int i = 0; i < n; i++)
         if (centers[2 * i] < 0 || centers[2 * i] >= Ny || centers[2 * i + 1] < 0 || centers[2 * i + 1] >= Nx)
             return fail(SCL_E_ARG, "center outside the image%s%s");
+    const size_t msm = (size_t)Ny * Nx * sizeof(T) + (Nx + 1) * sizeof(T) + 32 + SCL_MONO_STREAM_BYTES;
+    const int in_place = msm > 200 * 1024;
     Tables t;
     if ((rc = get_tables(Ny, Nx, &t))) return rc;
     cudaStream_t s = (cudaStream_t)stream;
@@ -207,8 +210,10 @@ static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T 
     CK(dc.alloc(2 * (size_t)n));
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
-    scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, N * sizeof(T) + (Nx + 1) * sizeof(T) + 32 + SCL_MONO_STREAM_BYTES, s>>>(
-        dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan());
+    if (in_place)
+        scl_k_monotonic<T, NEAREST><<<n, SCL_THREADS, 0, s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 1);
+    else
+        scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, msm, s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 0);
     CK(cudaGetLastError());
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));
@@ -272,7 +277,7 @@ int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* center
     if (n == 0) return SCL_OK;
     if (!x || !centers || n < 0 || mode < 0 || mode > 2) return fail(SCL_E_ARG, "bad argument%s%s");
     if (mode == 0 && !shifts) return fail(SCL_E_ARG, "kspace symmetry needs shifts%s%s");
-    int rc = check_shape(Ny, Nx);
+    int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
     if ((rc = ensure_globals())) return rc;
     for (int i = 0; i < n; i++) {
@@ -282,18 +287,26 @@ int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* center
     }
     cudaStream_t s = (cudaStream_t)stream;
     size_t N = (size_t)Ny * Nx;
-    DevBuf<float> dx;
+    DevBuf<float> dx, dz;
     DevBuf<int> dc;
     DevBuf<double> ds;
-    CK(dx.alloc(n * N));
+    const bool big = !fits_smem(Ny, Nx);     // in place in HBM; the tile loops may read (never use) up to 8 rows past an image
+    CK(dx.alloc(n * N + (big ? 8 * (size_t)Nx + 16 : 0)));
     CK(dc.alloc(2 * (size_t)n));
     CK(ds.alloc(2 * (size_t)n));
-    CK(dx.up(x, s));
+    CK(cudaMemcpyAsync(dx.p, x, n * N * sizeof(float), cudaMemcpyHostToDevice, s));
+    if (big) CK(cudaMemsetAsync(dx.p + n * N, 0, (8 * (size_t)Nx + 16) * sizeof(float), s));
     CK(dc.up(centers, s));
     if (shifts) CK(ds.up(shifts, s)); else CK(cudaMemsetAsync(ds.p, 0, 2 * (size_t)n * sizeof(double), s));
-    scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl, g_nfl_even);
+    if (big) {
+        CK(dz.alloc((size_t)n * Ny * ((Nx + 3) & ~3) + 16));
+        scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem_scene(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength,
+                                                                           g_nfl, g_nfl_even, dz.p);
+    } else
+        scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl,
+                                                                     g_nfl_even, nullptr);
     CK(cudaGetLastError());
-    CK(dx.down(x, s));
+    CK(cudaMemcpyAsync(x, dx.p, n * N * sizeof(float), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
 }
@@ -303,11 +316,12 @@ int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, dou
     if (n == 0) return SCL_OK;
     if (!x || !centers || !shifts || n < 0 || (do_centroid && (!psf || ph < 1 || pw < 1)))
         return fail(SCL_E_ARG, "bad argument%s%s");
-    int rc = check_shape(Ny, Nx);
+    int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
     if ((rc = ensure_globals())) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     size_t N = (size_t)Ny * Nx;
+    const int in_place = N * sizeof(float) > 200 * 1024;
     DevBuf<float> dx, dp;
     DevBuf<int> dc;
     DevBuf<double> ds;
@@ -318,7 +332,8 @@ int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, dou
     CK(cudaMemcpyAsync(dx.p, x, n * N * sizeof(float), cudaMemcpyHostToDevice, s));
     if (psf) CK(dp.up(psf, s));
     CK(dc.up(centers, s));
-    scl_k_measure<<<n, SCL_THREADS, N * sizeof(float), s>>>(dx.p, dc.p, ds.p, Ny, Nx, dp.p, ph, pw, do_max, do_centroid);
+    scl_k_measure<<<n, SCL_THREADS, in_place ? 0 : N * sizeof(float), s>>>(dx.p, dc.p, ds.p, Ny, Nx, dp.p, ph, pw, do_max,
+                                                                            do_centroid, in_place);
     CK(cudaGetLastError());
     CK(dc.down(centers, s));
     CK(ds.down(shifts, s));
@@ -327,12 +342,17 @@ int scl_measure_f32(const float* x, int n, int Ny, int Nx, int32_t* centers, dou
 }
 
 int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int Nx, const float* spec, int n_ker,
-                     const int32_t* ker_idx, int adjoint, void* stream) {
+                     const int32_t* ker_idx, int adjoint, int ker_half, void* stream) {
     if (n == 0) return SCL_OK;
     if (!model || !out || !ker_idx || n < 0 || C < 1 || (n_ker > 0 && !spec)) return fail(SCL_E_ARG, "bad argument%s%s");
-    if (Ny > SCL_FFT || Nx > SCL_FFT) return fail(SCL_E_LIMIT, "frame larger than the 128x128 convolution tile%s%s");
+    if (C > SCL_MAX_BANDS) return fail(SCL_E_LIMIT, "1 <= C <= 8 bands supported%s%s");
     for (int i = 0; i < n * C; i++)
         if (ker_idx[i] >= n_ker) return fail(SCL_E_ARG, "ker_idx out of range%s%s");
+    // frames that do not fit one 128-point period together with the kernel: overlap-save tiles (k_scene.cu)
+    const bool tiled = ker_half > 0 && (Ny + ker_half > SCL_FFT || Nx + ker_half > SCL_FFT);
+    if (!tiled && (Ny > SCL_FFT || Nx > SCL_FFT))
+        return fail(SCL_E_LIMIT, "frame larger than the 128x128 convolution tile: pass ker_half%s%s");
+    if (tiled && 2 * ker_half >= SCL_FFT - 8) return fail(SCL_E_LIMIT, "difference kernel too wide for the 128-point tile%s%s");
     int rc = ensure_globals();
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
@@ -347,6 +367,26 @@ int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int N
     CK(cudaMemcpyAsync(dm.p, model, tot * sizeof(float), cudaMemcpyHostToDevice, s));
     if (n_ker > 0) CK(cudaMemcpyAsync(dspec.p, spec, dspec.n * sizeof(float2), cudaMemcpyHostToDevice, s));
     CK(dk.up(ker_idx, s));
+    if (tiled) {
+        const int T = SCL_FFT - 2 * ker_half, ty = (Ny + T - 1) / T, tx = (Nx + T - 1) / T;
+        SclPlanes pl;
+        pl.P = C;
+        for (int c = 0; c < SCL_MAX_BANDS; c++) pl.band[c] = c;
+        DevBuf<int> act;
+        CK(act.alloc(n));
+        std::vector<int> ones(n, 1);
+        CK(cudaMemcpyAsync(act.p, ones.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
+        if (adjoint)
+            scl_k_scene_conv<false, true><<<dim3(ty * tx, C, n), SCL_THREADS, kFwdSmem, s>>>(
+                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx);
+        else
+            scl_k_scene_conv<false, false><<<dim3(ty * tx, C, n), SCL_THREADS, kFwdSmem, s>>>(
+                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx);
+        CK(cudaGetLastError());
+        CK(dout.down(out, s));
+        CK(cudaStreamSynchronize(s));      // `ones` is a host temporary
+        return SCL_OK;
+    }
     scl_k_convolve<<<dim3(C, n), SCL_THREADS, kFwdSmem, s>>>(dm.p, dspec.p, dk.p, dout.p, C, Ny, Nx, adjoint);
     CK(cudaGetLastError());
     CK(dout.down(out, s));

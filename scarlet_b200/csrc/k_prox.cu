@@ -416,13 +416,18 @@ scl_k_compact(const int* __restrict__ active, const int* __restrict__ comp_off, 
 template <typename T, bool NEAREST>
 __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, int Nx, T thresh,
-                const float* __restrict__ wtab, const double* __restrict__ ctab, SclMonoPlan plan)
+                const float* __restrict__ wtab, const double* __restrict__ ctab, SclMonoPlan plan, int in_place)
 {
     extern __shared__ __align__(16) unsigned char smem_b[];
     const int N = Ny * Nx;
     const size_t pad = (((size_t)Nx + 1) * sizeof(T) + 15) & ~(size_t)15;
-    T* X = reinterpret_cast<T*>(smem_b + pad);
     T* g = imgs + (size_t)blockIdx.x * N;
+    if (in_place) {
+        // images beyond the shared-memory limit: the level loop works on the image where it lies (HBM / L2)
+        scl_monotonic<T, NEAREST>(g, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
+        return;
+    }
+    T* X = reinterpret_cast<T*>(smem_b + pad);
     for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
     const int cy = centers[2 * blockIdx.x], cx = centers[2 * blockIdx.x + 1];
@@ -438,9 +443,9 @@ scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, i
         scl_monotonic<T, NEAREST>(X, Ny, Nx, cy, cx, wtab, ctab, thresh);
     for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
 }
-template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*, SclMonoPlan);
-template __global__ void scl_k_monotonic<double, false>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan);
-template __global__ void scl_k_monotonic<double, true>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan);
+template __global__ void scl_k_monotonic<float, false>(float*, const int*, int, int, float, const float*, const double*, SclMonoPlan, int);
+template __global__ void scl_k_monotonic<double, false>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan, int);
+template __global__ void scl_k_monotonic<double, true>(double*, const int*, int, int, double, const float*, const double*, SclMonoPlan, int);
 
 // Plan builder (see prox_dev.cuh): one CTA per centre c = cy * Nx + cx.  With list == nullptr only the number of
 // passes is written (npass[c]); otherwise the passes themselves, at first[c].
@@ -528,37 +533,38 @@ scl_k_init_extended(const float* __restrict__ images, const int* __restrict__ co
 extern "C" __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_symmetry(float* __restrict__ imgs, const int* __restrict__ centers, const double* __restrict__ shifts,
                int Ny, int Nx, int mode, float strength, const int* __restrict__ nfl,
-               const int* __restrict__ nfl_even)
+               const int* __restrict__ nfl_even, float* __restrict__ zscratch)
 {
     extern __shared__ __align__(16) float smem_f[];
     const int N = Ny * Nx;
-    float* X = smem_f;
-    float* Z = X + ((N + 3) & ~3);
-    float* tab = Z + Ny * ((Nx + 3) & ~3);
     float* g = imgs + (size_t)blockIdx.x * N;
-    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
+    // zscratch != nullptr (images beyond the shared-memory limit): work on the image in place, Z in HBM scratch
+    float* X = zscratch ? g : smem_f;
+    float* Z = zscratch ? zscratch + (size_t)blockIdx.x * Ny * ((Nx + 3) & ~3) : X + ((N + 3) & ~3);
+    float* tab = zscratch ? smem_f : Z + Ny * ((Nx + 3) & ~3);
+    if (!zscratch) for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
     __syncthreads();
     SclWindow w;
     if (centers[2 * blockIdx.x] < 0) { w.y0 = 0; w.x0 = 0; w.ny = Ny; w.nx = Nx; w.centered = false; }   // whole array
     else w = scl_window(Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1]);
     if (mode == 0) scl_kspace_symmetry(X, Nx, w, shifts[2 * blockIdx.x], shifts[2 * blockIdx.x + 1], Z, tab, nfl, nfl_even);
     else scl_flip_symmetry(X, Nx, w, mode == 2, strength);
-    for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
+    if (!zscratch) for (int p = threadIdx.x; p < N; p += blockDim.x) g[p] = X[p];
 }
 
 // max_pixel + psf_weighted_centroid for a stack of images (measurement.py)
 extern "C" __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_measure(const float* __restrict__ imgs, int* __restrict__ centers, double* __restrict__ shifts,
-              int Ny, int Nx, const float* __restrict__ psf, int ph, int pw, int do_max, int do_centroid)
+              int Ny, int Nx, const float* __restrict__ psf, int ph, int pw, int do_max, int do_centroid, int in_place)
 {
     extern __shared__ __align__(16) float smem_f[];
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
     const int N = Ny * Nx;
-    float* X = smem_f;
     const float* g = imgs + (size_t)blockIdx.x * N;
-    for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = g[p];
+    const float* X = in_place ? g : smem_f;            // in_place: images beyond the shared-memory limit
+    if (!in_place) for (int p = threadIdx.x; p < N; p += blockDim.x) smem_f[p] = g[p];
     if (threadIdx.x == 0) { sc[0] = centers[2 * blockIdx.x]; sc[1] = centers[2 * blockIdx.x + 1]; ss[0] = ss[1] = 0.0; }
     __syncthreads();
     if (do_max) { scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc); __syncthreads(); }

@@ -44,8 +44,8 @@ scl_k_scene_render(const float* __restrict__ A, const float* __restrict__ S, con
 // One overlap-save tile of one plane.  grid: (tiles_y * tiles_x, P, B); block SCL_THREADS; smem kFwdSmem.
 //   RESIDUAL: src = model M [B][C][N] (band pl.band[plane]);  dst = r = W^2 (src (*) d - I)  [B][P][N];
 //             loss_tile[b][plane][tile] = 0.5 sum (W (R - I))^2 over the tile
-//   else    : src = r [B][P][N];  dst = G = r (star) d (correlation, conj spectrum)  [B][P][N]
-template <bool RESIDUAL>
+//   else    : src = r [B][P][N];  dst = r (star) d (CONJ: correlation, conj spectrum) or r (*) d  [B][P][N]
+template <bool RESIDUAL, bool CONJ>
 __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat, const int* __restrict__ ker_idx,
                  const float* __restrict__ images, const float* __restrict__ weights, const int* __restrict__ active,
@@ -91,7 +91,7 @@ scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat,
             untangle_line(line, t, true);
         }
         __syncthreads();
-        if (RESIDUAL) column_phase<false>(buf, tw, D, F); else column_phase<true>(buf, tw, D, F);
+        column_phase<CONJ>(buf, tw, D, F);
         __syncthreads();
     }
     for (int j0 = warp * 2; j0 < F / 2; j0 += nwarp * 2) {
@@ -127,10 +127,11 @@ scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat,
         if (threadIdx.x == 0) loss_tile[((size_t)b * P + plane) * ntile + tile] = 0.5 * tot;
     }
 }
-template __global__ void scl_k_scene_conv<true>(const float*, const float2*, const int*, const float*, const float*,
-                                                const int*, float*, double*, int, SclPlanes, int, int, int, int);
-template __global__ void scl_k_scene_conv<false>(const float*, const float2*, const int*, const float*, const float*,
-                                                 const int*, float*, double*, int, SclPlanes, int, int, int, int);
+#define SCN_CONV_ARGS const float*, const float2*, const int*, const float*, const float*, const int*, float*, double*, \
+    int, SclPlanes, int, int, int, int
+template __global__ void scl_k_scene_conv<true, false>(SCN_CONV_ARGS);
+template __global__ void scl_k_scene_conv<false, true>(SCN_CONV_ARGS);
+template __global__ void scl_k_scene_conv<false, false>(SCN_CONV_ARGS);
 
 // Per-component squared norms for approximate_L (blend.py:189-202): snorm[k] = sum_p S[k][p]^2.  grid: Ktot
 extern "C" __global__ void __launch_bounds__(256)

@@ -162,5 +162,6 @@ def convolve(image1, image2, padding=3, axes=(-2, -1)):
     C, Ny, Nx = cube.shape
     spec = _native.kernel_spectrum(kers, Ny, Nx)
     idx = np.arange(C) if len(kers) == C else np.zeros(C, dtype=np.int32)
-    out = _native.convolve(cube[None].astype(np.float32), spec, idx)[0]
+    out = _native.convolve(cube[None].astype(np.float32), spec, idx,
+                           ker_half=_native.kernel_half(kers.shape[1], kers.shape[2], Ny, Nx))[0]
     return Fourier(out.reshape(img.shape).astype(img.dtype, copy=False))

@@ -118,7 +118,9 @@ class Observation():
 
     def _convolve(self, model):
         C = model.shape[0]
-        out = _native.convolve(np.asarray(model, dtype=np.float32)[None], self.kernel_spectrum(), np.arange(C))[0]
+        _, ky, kx = self._diff_kernels.image.shape
+        out = _native.convolve(np.asarray(model, dtype=np.float32)[None], self.kernel_spectrum(), np.arange(C),
+                               ker_half=_native.kernel_half(ky, kx, model.shape[1], model.shape[2]))[0]
         return out.astype(model.dtype, copy=False)
 
     def render(self, model):

@@ -148,6 +148,57 @@ def test_convolve_shapes(nat):
         assert_allclose(out[0], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
 
 
+# ---------------------------------------------------------------- images beyond the shared-memory limit
+def test_large_image_operators(nat):
+    """The array-level operators on a 300x280 image (config 4 class): the monotonic level loop, the symmetry
+    operators and the measurements work on the image in HBM; the convolution runs as overlap-save tiles."""
+    rng = np.random.default_rng(9)
+    shape, n = (300, 280), 3
+    centers = np.array([(152, 139), (40, 250), (299, 0)])      # none at the exact frame centre (operator.py:203-204)
+    for dt, th in ((np.float32, 0.0), (np.float32, 0.1), (np.float64, 0.1)):
+        x = (rng.random((n,) + shape) - .2).astype(dt)
+        y = x.copy()
+        nat.prox_weighted_monotonic(y, centers, th)
+        for i in range(n):
+            g = x[i].copy()
+            ref_prox.build_monotonic(shape, tuple(centers[i]), th)(g)
+            assert_array_equal(y[i], g)                                  # bit-exact
+    yy, xx = np.indices(shape)
+    x = np.array([np.exp(-np.hypot(yy - cy - .3, xx - cx + .2) / 6.) for cy, cx in centers[:2]]).astype(np.float32)
+    x += (.01 * rng.random(x.shape)).astype(np.float32)
+    shifts = np.array([(.3, -.2), (-.4, .1)])
+    for mode in ("soft", "sdss"):
+        y = x.copy()
+        nat.prox_symmetry(y, centers[:2], None, mode, 1.0)
+        for i in range(2):
+            g = x[i].copy()
+            ref_prox.prox_uncentered_symmetry(g, 0, tuple(centers[i]), mode, None, None, 1)
+            assert_array_equal(y[i], g)
+    y = x.copy()
+    nat.prox_symmetry(y, centers[:2], shifts, "kspace")
+    for i in range(2):
+        g = x[i].astype(np.float64)
+        ref_prox.prox_uncentered_symmetry(g, 0, tuple(centers[i]), "kspace", None, tuple(shifts[i]))
+        assert_allclose(y[i], g, rtol=0, atol=1e-5)
+    psf = np.exp(-np.hypot(*np.indices((41, 41)) - 20.) ** 2 / 2).astype(np.float32)
+    cc, ss = nat.measure(x, centers[:2] + 1, psf, True, True)
+    for i in range(2):
+        c0 = ref_prox.max_pixel(x[i], tuple(centers[i] + 1))
+        c1, s1 = ref_prox.psf_weighted_centroid(x[i], psf, c0)
+        assert_array_equal(cc[i], c1)
+        assert_allclose(ss[i], s1, rtol=0, atol=5e-6)
+    ker = rng.random((2, 41, 41))
+    model = rng.random((1, 2, 300, 280)).astype(np.float32)
+    spec = nat.kernel_spectrum(ker, 300, 280)
+    h = nat.kernel_half(41, 41, 300, 280)
+    out = nat.convolve(model, spec, [0, 1], ker_half=h)
+    adj = nat.convolve(model, spec, [0, 1], adjoint=True, ker_half=h)
+    ref = ref_fft.convolve(model[0].astype(np.float64), ker, axes=(1, 2))
+    assert_allclose(out[0], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+    ref = ref_fft.correlate(model[0].astype(np.float64), ker, axes=(1, 2))
+    assert_allclose(adj[0], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
+
+
 def test_errors(nat):
     x = np.zeros((1, 5, 5), np.float32)
     with pytest.raises(ValueError):
