@@ -79,6 +79,7 @@ def synthetic_blend(seed, C=5, Ny=64, Nx=64, kmin=2, kmax=8, psf_size=41, dtype=
     for c in centers:
         try:
             srcs.append(rb.ExtendedSource(frame, (int(round(c[0])), int(round(c[1]))), obs, bg))
+            srcs[-1].pixel_center_init = (int(round(c[0])), int(round(c[1])))
         except rb.SourceInitError:
             pass
     return frame, obs, srcs, rb.Blend(srcs, obs)

@@ -206,6 +206,30 @@ def test_two_observations_workflow(scarlet):
         assert_allclose(o.render(blend.get_model()), oo.render(gm), rtol=0, atol=3e-4 * np.abs(gm).max())
 
 
+def test_large_frame_workflow(scarlet):
+    """A 5-band 150x140 frame with 12 sources through the Python surface (config 4 class: beyond one convolution tile
+    and beyond 8 components): ExtendedSource initialisation with the large-image operators, Blend.fit in scene mode,
+    against the oracle's objects on the same data."""
+    frame_o, obs_o, srcs_o, blend_o = helpers.synthetic_blend(21, Ny=150, Nx=140, kmin=10, kmax=12)
+    frame = scarlet.Frame(frame_o.shape, psfs=frame_o.psfs)
+    obs = scarlet.Observation(obs_o.images, psfs=obs_o.frame.psfs, weights=obs_o.weights).match(frame)
+    bg = np.ones(frame.C, dtype=np.float32)
+    srcs = [scarlet.ExtendedSource(frame, s.pixel_center_init, obs, bg) for s in srcs_o]
+    blend = scarlet.Blend(srcs, obs)
+    assert len(blend.components) == len(blend_o.components) > 8
+    assert_array_equal([s.pixel_center for s in srcs], [s.pixel_center for s in srcs_o])
+    assert_allclose(np.array([c.morph for c in blend.components]), np.array([c.morph for c in blend_o.components]),
+                    rtol=0, atol=3e-6)
+    blend.fit(8, e_rel=0)
+    for _ in range(8):
+        blend_o.step(0.0)
+    assert_allclose(blend.mse, blend_o.mse, rtol=2e-4)
+    gm = blend_o.get_model()
+    assert_allclose(blend.get_model(), gm, rtol=0, atol=2e-4 * np.abs(gm).max())
+    ren = obs.render(blend.get_model())                    # tiled device convolution
+    assert_allclose(ren, obs_o.render(gm), rtol=0, atol=3e-4 * np.abs(gm).max())
+
+
 def test_multiresolution_workflow(scarlet):
     """Frame(wcs) + Observation + LowResObservation + CombinedExtendedSource + Blend.fit, as in the reference's
     multi-resolution use, against the reference's own run of the same scene (tests/golden/make_golden_lowres.py)."""
