@@ -9,6 +9,12 @@
 #define SCL_RS 65                // complex row stride of the smem spectrum tile (odd: conflict-free columns)
 #define SCL_THREADS 256
 #define SCL_PROX_THREADS 128     // constraint kernel: one CTA of 4 warps per component
+#ifndef SCL_PROX_WIDE
+#define SCL_PROX_WIDE 512        // the same kernel in scene mode (working set in HBM)
+#endif
+#ifndef SCL_WIDE_MIN
+#define SCL_WIDE_MIN 2           // resident CTAs per SM the wide variant is compiled for
+#endif
 
 // component flags (host mirror: scarlet_b200/_native.py)
 #define SCL_F_SYMMETRIC 1u       // run the symmetry prox (source.py:427-432)

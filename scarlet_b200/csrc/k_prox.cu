@@ -137,8 +137,8 @@ __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, 
     }
 }
 
-extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
-scl_k_prox(SclProxArgs a)
+template <int THREADS>
+__device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
 {
     extern __shared__ __align__(16) float smem_f[];
     const int k = a.comp_list[blockIdx.x];
@@ -160,7 +160,7 @@ scl_k_prox(SclProxArgs a)
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
     // gradient steps of this component
-    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
+    __shared__ double sdA[THREADS / 32][SCL_MAX_BANDS];
     __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
     scl_component_step(a, k, b, fl, X, sdA, sAnew, sAold);
     if (threadIdx.x == 0) {
@@ -295,6 +295,12 @@ scl_k_prox(SclProxArgs a)
 #undef SCL_PHASE
 }
 
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
+scl_k_prox(SclProxArgs a) { scl_prox_body<SCL_PROX_THREADS>(a); }
+// scene mode (working set in HBM, hundreds of thousands of pixels per component): wider CTAs
+extern "C" __global__ void __launch_bounds__(SCL_PROX_WIDE, SCL_WIDE_MIN)
+scl_k_prox_wide(SclProxArgs a) { scl_prox_body<SCL_PROX_WIDE>(a); }
+
 // K2b: MultiComponentSource.update, first half (source.py:605-627).  One CTA per multi-component source:
 //   _morph = sum_k morph_k * sum(sed_k)  over the source's components, AFTER this iteration's gradient steps
 //   pixel_center = max_pixel(_morph, pixel_center);  every 5th iteration (symmetric sources):
@@ -303,8 +309,8 @@ scl_k_prox(SclProxArgs a)
 // The stepped morphologies/SEDs are recomputed here with K3's own routine (same thread partition, same
 // reduction order, hence the same bits), since K3 keeps them in shared memory only.
 // dynamic smem: as scl_k_prox (M [N] in the X slot, the stepped component in the Z slot)
-extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
-scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
+template <int THREADS>
+__device__ __forceinline__ void scl_source_center_body(const SclProxArgs& a, const int* __restrict__ msrc)
 {
     extern __shared__ __align__(16) float smem_s[];
     const int k0 = msrc[2 * blockIdx.x], n = msrc[2 * blockIdx.x + 1];
@@ -317,7 +323,7 @@ scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
-    __shared__ double sdA[SCL_PROX_THREADS / 32][SCL_MAX_BANDS];
+    __shared__ double sdA[THREADS / 32][SCL_MAX_BANDS];
     __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;
     const unsigned fl0 = a.cflags[k0];
@@ -353,6 +359,11 @@ scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc)
         a.shift[2 * k] = ss[0]; a.shift[2 * k + 1] = ss[1];
     }
 }
+
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
+scl_k_source_center(SclProxArgs a, const int* __restrict__ msrc) { scl_source_center_body<SCL_PROX_THREADS>(a, msrc); }
+extern "C" __global__ void __launch_bounds__(SCL_PROX_WIDE, SCL_WIDE_MIN)
+scl_k_source_center_wide(SclProxArgs a, const int* __restrict__ msrc) { scl_source_center_body<SCL_PROX_WIDE>(a, msrc); }
 
 // K4: one thread per listed blend.  blend.py:157-176: never converged before it > 1.
 extern "C" __global__ void scl_k_converge(const int* __restrict__ comp_off, const int* __restrict__ conv,

@@ -81,6 +81,13 @@ def main():
     bt.fit(2, 0.0, approximate_L=a.approx)                       # warm-up
     info = bt.fit(a.iters, 0.0, approximate_L=a.approx, profile=True)
     out = bt.download()
+    # share of the constraint kernel's phases (clock64 sums over CTAs)
+    bt.phase_clocks(True)
+    bt.fit(3, 0.0, approximate_L=a.approx)
+    clk = bt.phase_clocks(False)
+    tot = float(sum(clk[:5])) or 1.0
+    phases = dict(zip(["gradient_step", "centre_symmetry", "level_list", "monotonic", "normalise_writeback"],
+                      [round(c / tot, 3) for c in clk[:5]]))
     bt.close()
     N = Ny * Nx
     alg = 4 * N * (2 * K + 2 * C) + 4 * C * 41 * 41 + 8 * K * C         # DESIGN.md B_iter
@@ -89,7 +96,7 @@ def main():
     print(json.dumps(dict(workload="config4-like scene", C=C, Ny=Ny, Nx=Nx, sources=ns, components=K,
                           approximate_L=a.approx, iters=info["steps"], ms_per_iter=ms,
                           kernel_ms=dict(render_conv_adjoint=km[0], lipschitz=km[1], constraints=km[2], converge=km[3]),
-                          alg_bytes_per_iter=alg, gbs=alg / ms / 1e6, launches=info["launches"],
+                          constraint_phase_share=phases, alg_bytes_per_iter=alg, gbs=alg / ms / 1e6, launches=info["launches"],
                           logL=[float(v) for v in out["logL"][0, :info["steps"]]],
                           gen_s=t_gen, tables_upload_s=t_up)))
 
