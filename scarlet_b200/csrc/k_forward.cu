@@ -301,7 +301,9 @@ scl_k_forward_adjoint(const float* __restrict__ A,        // [Ktot, C]
 
     // c: this CTA's plane; C: planes per blend (work split of the Gram rows); cm: the model band the plane sees
     const int C = pl.P, c = blockIdx.x % C, b = blend_list[blockIdx.x / C];
-    const int cm = pl.band[c];
+    int cm = 0;                      // pl.band[c] without indexing the parameter struct dynamically
+#pragma unroll
+    for (int p = 0; p < SCL_MAX_BANDS; p++) cm = (p == c) ? pl.band[p] : cm;
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const int N = Ny * Nx;

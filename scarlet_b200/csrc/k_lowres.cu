@@ -39,7 +39,9 @@ scl_k_lowres(const float* __restrict__ A,          // [Ktot, Cm]
     const int c = blockIdx.x % Plr, b = blend_list[blockIdx.x / Plr];
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
-    const int cm = pl.band[P0 + c];
+    int cm = 0;
+#pragma unroll
+    for (int p = 0; p < SCL_MAX_BANDS; p++) cm = (p == P0 + c) ? pl.band[p] : cm;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
     const float* L = lr_op + ((size_t)lr_op_idx[b] * Plr + c) * (size_t)n_lr * N;
     const float* img = lr_images + ((size_t)b * Plr + c) * n_lr;

@@ -122,8 +122,9 @@ __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, 
             if (threadIdx.x < C) {
                 // SED step (blend.py:91-93): A[k] -= (1/L_sed) dA
                 double v = 0.0;
-                for (int p = 0; p < P; p++)
-                    if (a.pl.band[p] == (int)threadIdx.x)
+#pragma unroll
+                for (int p = 0; p < SCL_MAX_BANDS; p++)
+                    if (p < P && a.pl.band[p] == (int)threadIdx.x)
                         for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][p];
                 float an = a.A[(size_t)k * C + threadIdx.x];
                 sAold[threadIdx.x] = an;
@@ -145,10 +146,12 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     const int b = a.comp_blend[k];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* xbase = a.xscratch ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_f;
+    // the narrow variant keeps everything in shared memory (a compile-time fact: X must stay an ld.shared pointer)
+    constexpr bool SCENE = THREADS != SCL_PROX_THREADS;
+    float* xbase = SCENE ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_f;
     float* X = xbase + ((Nx + 4) & ~3);         // front pad: the monotonic sweep reads X[-Nx-1 ..] unconditionally
     float* Z = X + ((N + 3) & ~3);
-    float* tab = a.xscratch ? smem_f : Z + Ny * ((Nx + 3) & ~3);
+    float* tab = SCENE ? smem_f : Z + Ny * ((Nx + 3) & ~3);
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
@@ -317,7 +320,8 @@ __device__ __forceinline__ void scl_source_center_body(const SclProxArgs& a, con
     const int b = a.comp_blend[k0];
     if (!a.active[b]) return;
     const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
-    float* xbase = a.xscratch ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_s;
+    constexpr bool SCENE = THREADS != SCL_PROX_THREADS;
+    float* xbase = SCENE ? a.xscratch + (size_t)blockIdx.x * a.xstride : smem_s;
     float* M = xbase + ((Nx + 4) & ~3);
     float* Xk = M + ((N + 3) & ~3);
     __shared__ double red[32];
