@@ -6,6 +6,7 @@ blends resident on one GPU.  Ranks own disjoint blends (weak scaling: --blends p
 step; per-blend result records are all-gathered over NCCL after the step.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--blends B] [--impl b200|reference]
+  python bench.py --workload config4 [--steps K] [--warmup W]      (one 6-band 512x512 scene, ~330 components)
 
 Prints ONE JSON line (rank 0).  `value` = blends/s with inputs resident in HBM; `e2e` = the same through the
 C ABI with host buffers (upload + fit + download per step); `roofline` = the dominant kernel against the
@@ -322,8 +323,140 @@ def run_reference(args):
                           e2e=dict(value=v, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0), gpu_launches=0)))
 
 
+# ------------------------------------------------------------------------------------------ config 4 (one big scene)
+SCENE_WORKLOAD = ("config4: one synthetic LSST-like 6-band 512x512 scene, 200 sources (70 % two-component), 41x41 PSFs, "
+                  "monotonic + symmetric constraints, Blend.fit(200, e_rel=1e-2)")
+
+
+def scene_oracle_step_seconds(batch, extra, n_steps=1):
+    """One (or a few) iterations of the CPU oracle on the same scene, single thread: seconds per iteration."""
+    from oracle import ref_blend as rb
+    C, Ny, Nx = batch["C"], batch["Ny"], batch["Nx"]
+    frame = rb.Frame((C, Ny, Nx), psfs=extra["mpsf"], dtype=np.float32)
+    obs = rb.Observation(extra["images"], psfs=extra["psfs"], weights=batch["weights"][0]).match(frame)
+    cw = rb._centroid_weight(frame)
+    srcs, k, K = [], 0, len(batch["sed"])
+    while k < K:
+        if extra["multi"][k]:
+            m = object.__new__(rb.MultiComponentSource)
+            m.frame, m.symmetric, m.monotonic, m.parent = frame, True, True, None
+            m.pixel_center, m.shift, m.centroid_weight = tuple(batch["center"][k]), (0., 0.), cw
+            m.components = [rb.Component(frame, batch["sed"][j], batch["morph"][j]) for j in (k, k + 1)]
+            srcs.append(m)
+            k += 2
+        else:
+            s_ = object.__new__(rb.ExtendedSource)
+            rb.Component.__init__(s_, frame, batch["sed"][k], batch["morph"][k])
+            s_.symmetric, s_.monotonic, s_.centroid_weight = True, True, cw
+            s_.pixel_center, s_.shift = tuple(batch["center"][k]), (0., 0.)
+            srcs.append(s_)
+            k += 1
+    blend = rb.Blend(srcs, obs)
+    t0 = time.perf_counter()
+    for _ in range(n_steps):
+        blend.step(E_REL)
+    return (time.perf_counter() - t0) / n_steps, blend.mse
+
+
+def run_scene(args):
+    """BASELINE config 4 on one GPU ("replicas only" for --gpus > 1): scenes/s of Blend.fit(200, 1e-2)."""
+    import torch
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    import __graft_entry__
+    if rank == 0:
+        __graft_entry__.build()
+    if world > 1:
+        dist.barrier()
+    from scarlet_b200 import synth, _native as nat
+    t0 = time.perf_counter()
+    batch, extra = synth.scene_arrays(args.scene_size, args.scene_sources, 6)
+    t_gen = time.perf_counter() - t0
+    K, N, Cb = len(batch["sed"]), batch["Ny"] * batch["Nx"], batch["C"]
+    bt = nat.Batch(**batch)
+    bt.snapshot()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    iters, launches = 0, 0
+    for i in range(args.warmup + args.steps):
+        if i == args.warmup:
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            ev0.record()
+            iters, launches = 0, 0
+        bt.restore()
+        info = bt.fit(MAX_ITER, E_REL, check_every=args.check_every)
+        iters += info["steps"]
+        launches += info["launches"]
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    out = bt.download()
+    # end to end: host arrays -> upload -> fit -> download of the fitted scene
+    up = {k: v for k, v in batch.items() if k not in ("C", "Ny", "Nx", "ker_half")}
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        bt.upload(**up)
+        bt.fit(MAX_ITER, E_REL, check_every=args.check_every)
+        res = bt.download()
+    e2e_s = (time.perf_counter() - t0) / args.steps
+    d2h = sum(v.nbytes for v in res.values() if isinstance(v, np.ndarray))
+    # per-kernel time of a fixed-iteration pass
+    bt.restore()
+    fx = bt.fit(args.roofline_iters, 0.0, profile=True)
+    km = [v / fx["steps"] for v in fx["kernel_ms"]]
+    alg_k3 = 4.0 * N * (2 + Cb) * K
+    alg_it = 4.0 * N * (2 * K + 2 * Cb) + 4 * Cb * PSF * PSF + 8 * K * Cb
+    roofline = dict(bound="hbm", kernel="scl_k_prox_wide", achieved=alg_k3 / (km[2] * 1e-3) / 1e9, peak=hbm_peak,
+                    unit="GB/s", frac=alg_k3 / (km[2] * 1e-3) / 1e9 / hbm_peak, traffic=None,
+                    how="CUDA events around each kernel group, %d fixed iterations (e_rel=0); latency-bound on the "
+                        "dependent levels of the monotonic sweep, see DESIGN.md scene mode" % fx["steps"],
+                    iteration=dict(ms=fx["device_ms"] / fx["steps"], alg_bytes=alg_it,
+                                   gbs=alg_it / (fx["device_ms"] / fx["steps"] * 1e-3) / 1e9),
+                    kernel_ms=dict(render_conv_adjoint=km[0], lipschitz=km[1], constraints=km[2], converge=km[3]))
+    bt.close()
+    if rank != 0:
+        return
+    line = dict(metric=METRIC, value=world * args.steps / (ms / 1e3), unit=UNIT, n_gpus=world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic",
+                config=dict(workload=SCENE_WORKLOAD, size=args.scene_size, sources=args.scene_sources, components=K,
+                            max_iter=MAX_ITER, e_rel=E_REL, iters_per_fit=iters / args.steps,
+                            l2="state per iteration (%.0f MB of morphologies) exceeds the 126 MB L2" % (4e-6 * N * K),
+                            sharding="replicas only: one scene is one unit", input_gen_s=t_gen),
+                pgm_iters_per_sec=world * iters / (ms / 1e3),
+                e2e=dict(value=world / e2e_s, unit=UNIT, h2d_bytes_per_step=int(bt.h2d_bytes), d2h_bytes_per_step=int(d2h),
+                         ms_per_step=e2e_s * 1e3),
+                gpu_launches=int(launches), roofline=roofline)
+    if not args.no_cpu:
+        t_it, _ = scene_oracle_step_seconds(batch, extra)
+        per_fit = iters / args.steps
+        line["cpu_baseline"] = dict(value=1.0 / (t_it * per_fit), unit=UNIT, cores=1, kind="port",
+                                    sample="1 iteration of the same scene with the CPU oracle (%.1f s), scaled to the "
+                                           "%.0f iterations the GPU fit took" % (t_it, per_fit),
+                                    iters_per_sec=1.0 / t_it)
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="config3", choices=["config3", "config4"])
+    ap.add_argument("--scene-size", type=int, default=512)
+    ap.add_argument("--scene-sources", type=int, default=200)
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
@@ -340,6 +473,8 @@ def main():
             args.steps = 2          # each step is a bounded CPU sample; keep the run within minutes
         args.warmup = min(args.warmup, 1)
         run_reference(args)
+    elif args.workload == "config4":
+        run_scene(args)
     else:
         run_b200(args)
 

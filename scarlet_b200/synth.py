@@ -90,3 +90,56 @@ def make_blends(indices, C=5, Ny=64, Nx=64, kmin=2, kmax=8, psf_size=41, device=
         images[s:e] = (conv.cpu().numpy() + noise).astype(np.float32)
     return dict(images=images, weights=np.ones_like(images), bg_rms=np.ones(C, np.float32),
                 model_psf=mpsf, psfs=psfs, centers=catalog)
+
+
+def scene_arrays(size=512, sources=200, bands=6, psf_size=41, seed=SEED0, multi_fraction=.7):
+    """One synthetic LSST-like scene of BASELINE config 4: `bands` x size x size, `sources` sources with
+    centres at least 10 px apart, 70 % as two-component sources (a core above half the peak + the rest, sharing one
+    centre like MultiComponentSource), 30 % single-component, monotonic + symmetric constraints on all of them.
+    Components start from the generator's own (thresholded) profiles: a timing workload for the iteration; the
+    source-initialisation path is not part of it.  Returns the arrays `_native.Batch` takes (one blend) plus
+    `multi` [K] (component belongs to a two-component source), `psfs`, `mpsf`, `diff` (difference kernels)."""
+    from . import _native as nat
+    from . import fft as sfft
+    from scipy.signal import fftconvolve
+    C, Ny, Nx = bands, size, size
+    rng = np.random.default_rng(seed)
+    mpsf, psfs = config3_psfs(C, psf_size)
+    diff = sfft.match_psfs(sfft.Fourier(psfs), sfft.Fourier(mpsf)).image.astype(np.float32)
+    centers = []
+    while len(centers) < sources:
+        c = rng.uniform(12, size - 12, 2)
+        if all(np.hypot(*(c - o)) >= 10 for o in centers):
+            centers.append(c)
+    yy, xx = np.indices((Ny, Nx), dtype=np.float32)
+    sed, morph, cflags, center, src_first, multi = [], [], [], [], [], []
+    truth = np.zeros((C, Ny, Nx), np.float32)
+    base = nat.F_CONSTRAINED | nat.F_SYMMETRIC | nat.F_MONOTONIC
+    for c in centers:
+        re, n, q, pa = rng.uniform(1.5, 5), rng.uniform(.7, 2.5), rng.uniform(.5, 1), rng.uniform(0, np.pi)
+        dy, dx = yy - c[0], xx - c[1]
+        u = dx * np.cos(pa) + dy * np.sin(pa)
+        v = (-dx * np.sin(pa) + dy * np.cos(pa)) / q
+        m = np.exp(-(np.hypot(u, v) / re) ** (1 / n)).astype(np.float32)
+        m[m < 1e-3] = 0
+        s = (rng.dirichlet(np.ones(C)) * 10 ** rng.uniform(np.log10(50), np.log10(5000))).astype(np.float32)
+        truth += s[:, None, None] * m[None]
+        pc = (int(round(c[0])), int(round(c[1])))
+        first = len(sed)
+        if rng.random() < multi_fraction:
+            core = np.where(m >= .5 * m.max(), m, 0).astype(np.float32)
+            for part, frac in ((m - .5 * core, .6), (core, .4)):
+                sed.append(s * frac); morph.append(part / part.max()); center.append(pc)
+                cflags.append(base | nat.F_SHARED_CENTER); src_first.append(first); multi.append(True)
+        else:
+            sed.append(s); morph.append(m / m.max()); center.append(pc)
+            cflags.append(base | nat.F_KSPACE); src_first.append(first); multi.append(False)
+    images = np.array([fftconvolve(truth[b], psfs[b], mode="same") for b in range(C)], dtype=np.float32)
+    images += rng.normal(0, 1, images.shape).astype(np.float32)
+    K = len(sed)
+    batch = dict(C=C, Ny=Ny, Nx=Nx, comp_off=[0, K], sed=np.array(sed), morph=np.array(morph), cflags=cflags,
+                 center=center, shift=np.zeros((K, 2)), conv=3 * np.ones(K), images=images[None],
+                 weights=np.ones((1, C, Ny, Nx), np.float32), kernel_spec=nat.kernel_spectrum(diff, Ny, Nx),
+                 ker_idx=np.arange(C), cw=mpsf, cw_idx=[0], src_first=src_first,
+                 ker_half=nat.kernel_half(psf_size, psf_size, Ny, Nx))
+    return batch, dict(multi=np.array(multi), psfs=psfs, mpsf=mpsf, diff=diff, images=images)

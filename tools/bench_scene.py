@@ -15,8 +15,7 @@ import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from scarlet_b200 import _native as nat  # noqa: E402
-from scarlet_b200 import psf as spsf  # noqa: E402
-from scarlet_b200 import fft as sfft  # noqa: E402
+from scarlet_b200 import synth  # noqa: E402
 
 
 def main():
@@ -28,55 +27,13 @@ def main():
     ap.add_argument("--approx", action="store_true")
     a = ap.parse_args()
     C, Ny, Nx, ns = a.bands, a.size, a.size, a.sources
-    rng = np.random.default_rng(20260411)
     t0 = time.time()
     nat.require_device()
-    mpsf = spsf.generate_psf_image(spsf.gaussian, (41, 41), sigma=.9).image.astype(np.float32)
-    psfs = np.array([spsf.generate_psf_image(spsf.gaussian, (41, 41), sigma=1.2 + .15 * b).image for b in range(C)],
-                    dtype=np.float32)
-    diff = sfft.match_psfs(sfft.Fourier(psfs), sfft.Fourier(mpsf[None])).image.astype(np.float32)
-    spec = nat.kernel_spectrum(diff, Ny, Nx)
-    centers = []
-    while len(centers) < ns:
-        c = rng.uniform(12, Ny - 12, 2)
-        if all(np.hypot(*(c - o)) >= 10 for o in centers):
-            centers.append(c)
-    yy, xx = np.indices((Ny, Nx), dtype=np.float32)
-    sed, morph, cflags, center, src_first = [], [], [], [], []
-    images = np.zeros((C, Ny, Nx), np.float32)
-    from scipy.signal import fftconvolve
-    truth = np.zeros((C, Ny, Nx), np.float32)
-    for i, c in enumerate(centers):
-        re, n, q, pa = rng.uniform(1.5, 5), rng.uniform(.7, 2.5), rng.uniform(.5, 1), rng.uniform(0, np.pi)
-        dy, dx = yy - c[0], xx - c[1]
-        u = dx * np.cos(pa) + dy * np.sin(pa)
-        v = (-dx * np.sin(pa) + dy * np.cos(pa)) / q
-        m = np.exp(-(np.hypot(u, v) / re) ** (1 / n)).astype(np.float32)
-        m[m < 1e-3] = 0
-        s = (rng.dirichlet(np.ones(C)) * 10 ** rng.uniform(np.log10(50), np.log10(5000))).astype(np.float32)
-        truth += s[:, None, None] * m[None]
-        pc = (int(round(c[0])), int(round(c[1])))
-        multi = rng.random() < .7
-        first = len(sed)
-        base = nat.F_CONSTRAINED | nat.F_SYMMETRIC | nat.F_MONOTONIC
-        if multi:
-            core = np.where(m >= .5 * m.max(), m, 0).astype(np.float32)
-            for part, frac in ((m - .5 * core, .6), (core, .4)):
-                sed.append(s * frac); morph.append(part / part.max()); center.append(pc)
-                cflags.append(base | nat.F_SHARED_CENTER); src_first.append(first)
-        else:
-            sed.append(s); morph.append(m / m.max()); center.append(pc)
-            cflags.append(base | nat.F_KSPACE); src_first.append(first)
-    for b in range(C):
-        images[b] = fftconvolve(truth[b], psfs[b], mode="same")
-    images += rng.normal(0, 1, images.shape).astype(np.float32)
-    K = len(sed)
+    batch, _ = synth.scene_arrays(a.size, a.sources, a.bands)
+    K = len(batch["sed"])
     t_gen = time.time() - t0
     t0 = time.time()
-    bt = nat.Batch(C, Ny, Nx, comp_off=[0, K], sed=np.array(sed), morph=np.array(morph), cflags=cflags, center=center,
-                   shift=np.zeros((K, 2)), conv=np.zeros(K), images=images[None],
-                   weights=np.ones((1, C, Ny, Nx), np.float32), kernel_spec=spec, ker_idx=np.arange(C),
-                   cw=mpsf[None], cw_idx=[0], src_first=src_first, ker_half=nat.kernel_half(41, 41, Ny, Nx))
+    bt = nat.Batch(**batch)
     t_up = time.time() - t0
     bt.fit(2, 0.0, approximate_L=a.approx)                       # warm-up
     info = bt.fit(a.iters, 0.0, approximate_L=a.approx, profile=True)
