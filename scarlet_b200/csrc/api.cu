@@ -378,10 +378,10 @@ int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int N
         CK(cudaMemcpyAsync(act.p, ones.data(), n * sizeof(int), cudaMemcpyHostToDevice, s));
         if (adjoint)
             scl_k_scene_conv<false, true><<<dim3(ty * tx, C, n), SCL_THREADS, kFwdSmem, s>>>(
-                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx);
+                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx, C, 0);
         else
             scl_k_scene_conv<false, false><<<dim3(ty * tx, C, n), SCL_THREADS, kFwdSmem, s>>>(
-                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx);
+                dm.p, dspec.p, dk.p, nullptr, nullptr, act.p, dout.p, nullptr, C, pl, Ny, Nx, ker_half, tx, C, 0);
         CK(cudaGetLastError());
         CK(dout.down(out, s));
         CK(cudaStreamSynchronize(s));      // `ones` is a host temporary

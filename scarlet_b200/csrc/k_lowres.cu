@@ -27,14 +27,13 @@ scl_k_lowres(const float* __restrict__ A,          // [Ktot, Cm]
              const int* __restrict__ active,       // [B]
              const int* __restrict__ blend_list,   // [gridDim.x / Plr]
              float* __restrict__ G,                // [B, PG, N]; this kernel fills planes P0 .. P0 + Plr - 1
-             double* __restrict__ loss_part,       // [B, PG]
-             int Cm, SclPlanes pl, int P0, int Plr, int PG, int N, int n_lr)
+             double* __restrict__ loss_out,        // [B, loss_stride]; this kernel fills entries loss_off .. + Plr - 1
+             int Cm, SclPlanes pl, int P0, int Plr, int PG, int N, int n_lr, int loss_stride, int loss_off)
 {
     extern __shared__ __align__(16) unsigned char smem_lr[];
     double* red = reinterpret_cast<double*>(smem_lr);
     float* M = reinterpret_cast<float*>(red + 32);
     float* r = M + N;
-    __shared__ float sA[SCL_MAX_COMP];
 
     const int c = blockIdx.x % Plr, b = blend_list[blockIdx.x / Plr];
     if (!active[b]) return;
@@ -48,11 +47,9 @@ scl_k_lowres(const float* __restrict__ A,          // [Ktot, Cm]
     const float* wgt = lr_weights ? lr_weights + ((size_t)b * Plr + c) * n_lr : nullptr;
     float* gout = G + ((size_t)b * PG + P0 + c) * N;
 
-    if (threadIdx.x < SCL_MAX_COMP) sA[threadIdx.x] = (threadIdx.x < K) ? A[(size_t)(k0 + threadIdx.x) * Cm + cm] : 0.f;
-    __syncthreads();
-    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {          // any number of components
         float m = 0.f;
-        for (int k = 0; k < K; k++) m += sA[k] * S[(size_t)(k0 + k) * N + p];
+        for (int k = 0; k < K; k++) m += A[(size_t)(k0 + k) * Cm + cm] * S[(size_t)(k0 + k) * N + p];
         M[p] = m;
     }
     __syncthreads();
@@ -77,7 +74,7 @@ scl_k_lowres(const float* __restrict__ A,          // [Ktot, Cm]
         gout[p] = g;
     }
     const double tot = block_sum<double>(loss, red);
-    if (threadIdx.x == 0) loss_part[b * PG + P0 + c] = 0.5 * tot;
+    if (threadIdx.x == 0) loss_out[(size_t)b * loss_stride + loss_off + c] = 0.5 * tot;
 }
 
 // Array-level operator: out[n][c][q] = sum_p op[c][q][p] model[n][c][p]  (LowResObservation._render for display /

@@ -50,7 +50,7 @@ __global__ void __launch_bounds__(SCL_THREADS)
 scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat, const int* __restrict__ ker_idx,
                  const float* __restrict__ images, const float* __restrict__ weights, const int* __restrict__ active,
                  float* __restrict__ dst, double* __restrict__ loss_tile,
-                 int Cm, SclPlanes pl, int Ny, int Nx, int h, int tiles_x)
+                 int Cm, SclPlanes pl, int Ny, int Nx, int h, int tiles_x, int dst_planes, int loss_stride)
 {
     extern __shared__ __align__(16) unsigned char smem_sc[];
     float2* buf = reinterpret_cast<float2*>(smem_sc);
@@ -67,7 +67,7 @@ scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat,
     const float inv = 1.0f / (float)(F * F);
     const int kid = ker_idx[b * P + plane];
     const float* in = RESIDUAL ? src + ((size_t)b * Cm + pl.band[plane]) * N : src + ((size_t)b * P + plane) * N;
-    float* out = dst + ((size_t)b * P + plane) * N;
+    float* out = dst + ((size_t)b * dst_planes + plane) * N;      // dst_planes >= P (G also holds low-resolution planes)
     const float* img = RESIDUAL ? images + ((size_t)b * P + plane) * N : nullptr;
     const float* wgt = (RESIDUAL && weights) ? weights + ((size_t)b * P + plane) * N : nullptr;
     const float2* D = Dhat + (size_t)(kid < 0 ? 0 : kid) * F * RS;
@@ -124,11 +124,11 @@ scl_k_scene_conv(const float* __restrict__ src, const float2* __restrict__ Dhat,
     }
     if (RESIDUAL) {
         const double tot = block_sum<double>(loss, red);
-        if (threadIdx.x == 0) loss_tile[((size_t)b * P + plane) * ntile + tile] = 0.5 * tot;
+        if (threadIdx.x == 0) loss_tile[(size_t)b * loss_stride + plane * ntile + tile] = 0.5 * tot;
     }
 }
 #define SCN_CONV_ARGS const float*, const float2*, const int*, const float*, const float*, const int*, float*, double*, \
-    int, SclPlanes, int, int, int, int
+    int, SclPlanes, int, int, int, int, int, int
 template __global__ void scl_k_scene_conv<true, false>(SCN_CONV_ARGS);
 template __global__ void scl_k_scene_conv<false, true>(SCN_CONV_ARGS);
 template __global__ void scl_k_scene_conv<false, false>(SCN_CONV_ARGS);

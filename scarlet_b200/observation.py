@@ -259,7 +259,8 @@ class LowResObservation(Observation):
         kx = self._shift_kernels(self.other_shifts[1], Fx)                       # [n_x, Fx]
         cols = (np.arange(Fx)[:, None] - (np.arange(Nx)[None, :] + px)) % Fx
         KX = kx[::-1][:, cols]                                                   # [n_x (flipped), Fx, Nx]
-        op = np.einsum("cjyv,ivx->cjiyx", resconv[:, :, py:py + Ny, :], KX)
+        # [c, j, y, v] . [i, v, x] over v -> [c, j, y, i, x] (one BLAS call) -> [c, j, i, y, x]
+        op = np.tensordot(resconv[:, :, py:py + Ny, :], KX, axes=([3], [1])).transpose(0, 1, 3, 2, 4)
         C_lr, n_y, n_x = op.shape[:3]
         assert (n_y, n_x) == self.lr_shape
         self._lr_op = np.ascontiguousarray(op.reshape(C_lr, n_y * n_x, Ny * Nx), dtype=np.float32)

@@ -100,6 +100,17 @@ def test_lockstep_low_resolution_observation(nat):
     _lockstep(nat, blend, 10, e_rel=1e-9)
 
 
+@pytest.mark.parametrize("approx", [True, False])
+def test_scene_lockstep_low_resolution(nat, approx):
+    """The multi-resolution scene forced through scene mode (tiled full-resolution planes + scl_k_lowres planes,
+    losses and adjoint images combined), every iteration vs the oracle."""
+    import os
+    gold = np.load(os.path.join(helpers.GOLD, "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "A_")
+    srcs, blend = helpers.lowres_blend(gold, frame, ohr, olr)
+    _lockstep(nat, blend, 6, e_rel=1e-9, approximate_L=approx, scene_mode=1)
+
+
 def test_low_resolution_free_running_vs_reference(nat):
     """The same scene free-running against the reference's own 12 iterations (make_golden_lowres.py)."""
     import os
