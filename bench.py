@@ -452,9 +452,106 @@ def run_scene(args):
     print(json.dumps(line))
 
 
+# ------------------------------------------------------------------------------------------ config 5 (multi-resolution)
+MULTIRES_WORKLOAD = ("config5: joint fit of a 3-band 128x128 observation (41x41 PSFs) and a 5-band 34x34 LowResObservation "
+                     "(pixel scale 4, 15x15 PSFs, sub-pixel offset, unrotated), %d CombinedExtendedSources, "
+                     "Blend.fit(200, e_rel=1e-2) through the Python surface")
+
+
+def run_multires(args):
+    """BASELINE config 5 on one GPU, built and fitted through the drop-in Python API (scarlet.Frame / Observation /
+    LowResObservation / CombinedExtendedSource / Blend).  One step = Blend.fit(200, 1e-2) from the initial sources."""
+    import copy
+    import torch
+    torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    if int(os.environ.get("RANK", 0)) != 0:
+        return
+    import __graft_entry__
+    __graft_entry__.build()
+    sys.path.insert(0, os.path.join(ROOT, "tests", "golden"))
+    from wcs_stub import make_pair            # affine WCS stand-in (astropy is not in this image)
+    import scarlet_b200 as scarlet
+    from scarlet_b200 import psf as spsf
+    rng = np.random.default_rng(20260411 + 5)
+    HY = HX = 128
+    LY = LX = 34
+    ns = args.multires_sources
+    chan = ["h0", "h1", "h2", "l0", "l1", "l2", "l3", "l4"]
+    whr, wlr = make_pair((HY, HX), (LY, LX), scale=4.0, lr_offset=(.3, -.2))
+    mpsf = spsf.generate_psf_image(spsf.gaussian, (41, 41), sigma=.9).image.astype(np.float32)
+    hr_psfs = np.array([spsf.generate_psf_image(spsf.gaussian, (41, 41), sigma=1.2 + .15 * b).image for b in range(3)],
+                       dtype=np.float32)
+    lr_psfs = np.array([spsf.generate_psf_image(spsf.gaussian, (15, 15), sigma=.8 + .05 * b).image for b in range(5)],
+                       dtype=np.float32)
+    t0 = time.perf_counter()
+    frame = scarlet.Frame((8, HY, HX), wcs=whr, psfs=mpsf[None], channels=chan)
+    centers = []
+    while len(centers) < ns:
+        c = rng.uniform(24, HY - 24, 2)
+        if all(np.hypot(*(c - o)) >= 14 for o in centers):
+            centers.append(c)
+    yy, xx = np.indices((HY, HX))
+    truth = np.zeros((8, HY, HX), np.float32)
+    for c in centers:
+        re, q, pa = rng.uniform(2, 4), rng.uniform(.6, 1), rng.uniform(0, np.pi)
+        u = (xx - c[1]) * np.cos(pa) + (yy - c[0]) * np.sin(pa)
+        v = (-(xx - c[1]) * np.sin(pa) + (yy - c[0]) * np.cos(pa)) / q
+        sed = rng.dirichlet(np.ones(8)) * 10 ** rng.uniform(3, 4)
+        truth += (sed[:, None, None] * np.exp(-np.hypot(u, v) / re)[None]).astype(np.float32)
+    # images: this package's own forward models of the true scene + noise
+    ohr = scarlet.Observation(np.zeros((3, HY, HX), np.float32), psfs=hr_psfs, wcs=whr, channels=chan[:3]).match(frame)
+    olr = scarlet.LowResObservation(np.zeros((5, LY, LX), np.float32), wcs=wlr, psfs=lr_psfs, channels=chan[3:]).match(frame)
+    hr_img = (ohr.render(truth) + rng.normal(0, 1, (3, HY, HX))).astype(np.float32)
+    lr_img = rng.normal(0, 1, (5, LY, LX)).astype(np.float32)
+    ys, xs = olr._window()
+    lr_img[:, ys, xs] += olr._render(truth)
+    ohr = scarlet.Observation(hr_img, psfs=hr_psfs, wcs=whr, channels=chan[:3]).match(frame)
+    t1 = time.perf_counter()
+    olr = scarlet.LowResObservation(lr_img, wcs=wlr, psfs=lr_psfs, channels=chan[3:]).match(frame)
+    t_match = time.perf_counter() - t1
+    bg = [np.ones(3, np.float32), np.ones(5, np.float32)]
+    srcs0 = [scarlet.CombinedExtendedSource(frame, (round(c[0]) - HY / 2, round(c[1]) - HX / 2), [ohr, olr], bg, obs_idx=0)
+             for c in centers]
+    t_setup = time.perf_counter() - t0
+    from scarlet_b200.blend import pack_blends
+    ms_list, its, launches = [], [], 0
+    e2e_list = []
+    for i in range(args.warmup + args.steps):
+        srcs = [copy.copy(s) for s in srcs0]
+        for s, s0 in zip(srcs, srcs0):
+            s._sed, s._morph = s0._sed.copy(), s0._morph.copy()
+        blend = scarlet.Blend(srcs, [ohr, olr])
+        t0 = time.perf_counter()
+        infos = scarlet.fit_many([blend], MAX_ITER, E_REL)
+        dt = time.perf_counter() - t0
+        if i >= args.warmup:
+            ms_list.append(infos[0]["device_ms"]); its.append(blend.it); launches += infos[0]["launches"]
+            e2e_list.append(dt)
+    packed = pack_blends([blend])
+    h2d = sum(v.nbytes for v in packed.values() if isinstance(v, np.ndarray)) + sum(
+        v.nbytes for v in (packed["lr"] or {}).values() if isinstance(v, np.ndarray))
+    ms = float(np.mean(ms_list))
+    K = len(srcs0)
+    print(json.dumps(dict(
+        metric=METRIC, value=1e3 / ms, unit=UNIT, n_gpus=1, steps=args.steps, warmup=args.warmup, ms_per_step=ms,
+        higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
+        config=dict(workload=MULTIRES_WORKLOAD % K, components=K, max_iter=MAX_ITER, e_rel=E_REL,
+                    iters_per_fit=float(np.mean(its)), lr_operator_bytes=int(olr._lr_op.nbytes),
+                    lowres_match_s=t_match, setup_s=t_setup,
+                    note="scene mode (128x128 frame + 41x41 PSF exceeds one convolution tile); the low-resolution "
+                         "operator (335 MB) is streamed twice per plane and iteration"),
+        pgm_iters_per_sec=float(np.mean(its)) / (ms / 1e3),
+        e2e=dict(value=1.0 / float(np.mean(e2e_list)), unit=UNIT, h2d_bytes_per_step=int(h2d),
+                 d2h_bytes_per_step=int(4 * K * (HY * HX + 8)), ms_per_step=1e3 * float(np.mean(e2e_list))),
+        gpu_launches=int(launches), logL_first_last=[float(blend.mse[0]), float(blend.mse[-1])],
+        cpu_baseline=None, cpu_baseline_note="the oracle's adjoint of the low-resolution render needs its dense matrix "
+        "(16384 renders at this size); parity at fixture size is tests/test_gpu_fit.py::test_low_resolution_*")))
+
+
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--workload", default="config3", choices=["config3", "config4"])
+    ap.add_argument("--multires-sources", type=int, default=6)
+    ap.add_argument("--workload", default="config3", choices=["config3", "config4", "config5"])
     ap.add_argument("--scene-size", type=int, default=512)
     ap.add_argument("--scene-sources", type=int, default=200)
     ap.add_argument("--gpus", type=int, default=1)
@@ -475,6 +572,8 @@ def main():
         run_reference(args)
     elif args.workload == "config4":
         run_scene(args)
+    elif args.workload == "config5":
+        run_multires(args)
     else:
         run_b200(args)
 
