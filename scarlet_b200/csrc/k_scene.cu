@@ -178,52 +178,80 @@ extern "C" __global__ void scl_k_scene_lipschitz(const float* __restrict__ A, co
 // Blend._set_lipschitz (blend.py:203-217): L_sed = lambda_max(S S^T), L_morph = lambda_max(A^T A).
 // Gram matrix: gram[b][i][j] = sum_p S[k0+i][p] S[k0+j][p], Kp x Kp (Kp = padded component count, zero beyond K),
 // float32 products accumulated per CTA over a chunk of pixels, chunks combined with float64 atomics.
-// grid: (tiles * tiles, chunks, B), 32x32 output tile per CTA, 256 threads (2x2 outputs each).
-#define SCN_GT 32
-#define SCN_GP 64
+// grid: (tiles * tiles, chunks, B), 64x64 output tile per CTA, 256 threads (4x4 outputs each).
+#define SCN_GT 64
+#define SCN_GP 32
 extern "C" __global__ void __launch_bounds__(256)
 scl_k_scene_gram(const float* __restrict__ S, const int* __restrict__ comp_off, const int* __restrict__ active,
-                 double* __restrict__ gram, int Kp, int N, int chunk)
+                 float* __restrict__ part, int Kp, int N, int chunk)      // part [B][chunks][Kp][Kp]
 {
-    __shared__ float sa[SCN_GT][SCN_GP + 1], sb[SCN_GT][SCN_GP + 1];
+    // pixel-major tiles [pixel][component] (+1 pad: conflict-free transposed stores); a thread owns the 4x4 outputs
+    // (r0 + 16u, c0 + 16v): per pixel 4 + 4 conflict-free shared loads feed 16 FMAs
+    __shared__ float sa[SCN_GP][SCN_GT + 1], sb[SCN_GP][SCN_GT + 1];
     const int b = blockIdx.z;
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
-    const int nt = Kp / SCN_GT, ti = blockIdx.x / nt, tj = blockIdx.x % nt;
+    const int nt = (Kp + SCN_GT - 1) / SCN_GT, ti = blockIdx.x / nt, tj = blockIdx.x % nt;
     if (tj < ti || ti * SCN_GT >= K || tj * SCN_GT >= K) return;          // upper triangle, mirrored on write
     const int p_lo = blockIdx.y * chunk, p_hi = min(N, p_lo + chunk);
-    const int r = (threadIdx.x >> 4) * 2, c = (threadIdx.x & 15) * 2;
-    float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+    const int r0 = threadIdx.x >> 4, c0 = threadIdx.x & 15;
+    float acc[4][4];
+#pragma unroll
+    for (int u = 0; u < 4; u++)
+#pragma unroll
+        for (int v = 0; v < 4; v++) acc[u][v] = 0.f;
     for (int p0 = p_lo; p0 < p_hi; p0 += SCN_GP) {
         for (int i = threadIdx.x; i < SCN_GT * SCN_GP; i += blockDim.x) {
             const int row = i / SCN_GP, col = i % SCN_GP, p = p0 + col;
             const int ka = ti * SCN_GT + row, kb = tj * SCN_GT + row;
-            sa[row][col] = (ka < K && p < p_hi) ? S[(size_t)(k0 + ka) * N + p] : 0.f;
-            sb[row][col] = (kb < K && p < p_hi) ? S[(size_t)(k0 + kb) * N + p] : 0.f;
+            sa[col][row] = (ka < K && p < p_hi) ? S[(size_t)(k0 + ka) * N + p] : 0.f;
+            sb[col][row] = (kb < K && p < p_hi) ? S[(size_t)(k0 + kb) * N + p] : 0.f;
         }
         __syncthreads();
 #pragma unroll 8
         for (int q = 0; q < SCN_GP; q++) {
-            const float a0 = sa[r][q], a1 = sa[r + 1][q], b0 = sb[c][q], b1 = sb[c + 1][q];
-            acc[0][0] += a0 * b0; acc[0][1] += a0 * b1; acc[1][0] += a1 * b0; acc[1][1] += a1 * b1;
+            float a[4], bb[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) { a[u] = sa[q][r0 + 16 * u]; bb[u] = sb[q][c0 + 16 * u]; }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+#pragma unroll
+                for (int v = 0; v < 4; v++) acc[u][v] += a[u] * bb[v];
         }
         __syncthreads();
     }
-    double* g = gram + (size_t)b * Kp * Kp;
+    // per-chunk partial sums, combined in chunk order by scl_k_scene_gram_reduce (5 M float64 atomics cost more than
+    // the products themselves)
+    float* g = part + ((size_t)b * gridDim.y + blockIdx.y) * Kp * Kp;
 #pragma unroll
-    for (int u = 0; u < 2; u++)
+    for (int u = 0; u < 4; u++)
 #pragma unroll
-        for (int v = 0; v < 2; v++) {
-            const int i = ti * SCN_GT + r + u, j = tj * SCN_GT + c + v;
-            if (i < K && j < K && (ti != tj || j >= i)) {
-                atomicAdd(g + (size_t)i * Kp + j, (double)acc[u][v]);
-                if (i != j) atomicAdd(g + (size_t)j * Kp + i, (double)acc[u][v]);
-            }
+        for (int v = 0; v < 4; v++) {
+            const int i = ti * SCN_GT + r0 + 16 * u, j = tj * SCN_GT + c0 + 16 * v;
+            if (i < K && j < K) g[(size_t)i * Kp + j] = acc[u][v];
         }
 }
 
+// gram[b][i][j] = gram[b][j][i] = sum over chunks of part[b][chunk][i][j], j >= i.  grid: (K rows, B)
+extern "C" __global__ void __launch_bounds__(128)
+scl_k_scene_gram_reduce(const float* __restrict__ part, const int* __restrict__ comp_off,
+                        const int* __restrict__ active, double* __restrict__ gram, int Kp, int chunks)
+{
+    const int b = blockIdx.y, i = blockIdx.x;
+    if (!active[b]) return;
+    const int K = comp_off[b + 1] - comp_off[b];
+    if (i >= K) return;
+    for (int j = i + threadIdx.x; j < K; j += blockDim.x) {
+        double v = 0.0;
+        for (int c = 0; c < chunks; c++) v += (double)part[(((size_t)b * chunks + c) * Kp + i) * Kp + j];
+        gram[((size_t)b * Kp + i) * Kp + j] = v;
+        gram[((size_t)b * Kp + j) * Kp + i] = v;
+    }
+}
+
 // f32 working copy of the Gram matrix, scaled by 1/trace.  grid: (Kp, B)
-extern "C" __global__ void scl_k_scene_eig_init(const double* __restrict__ gram, float* __restrict__ M, int Kp)
+extern "C" __global__ void scl_k_scene_eig_init(const double* __restrict__ gram, float* __restrict__ M,
+                                                double* __restrict__ fro, int Kp)
 {
     __shared__ double red[32];
     const double* g = gram + (size_t)blockIdx.y * Kp * Kp;
@@ -232,7 +260,14 @@ extern "C" __global__ void scl_k_scene_eig_init(const double* __restrict__ gram,
     tr = block_sum<double>(tr, red);
     const double s = tr > 0.0 ? 1.0 / tr : 0.0;
     float* m = M + ((size_t)blockIdx.y * Kp + blockIdx.x) * Kp;
-    for (int j = threadIdx.x; j < Kp; j += blockDim.x) m[j] = (float)(g[(size_t)blockIdx.x * Kp + j] * s);
+    double f2 = 0.0;
+    for (int j = threadIdx.x; j < Kp; j += blockDim.x) {
+        const float v = (float)(g[(size_t)blockIdx.x * Kp + j] * s);
+        m[j] = v;
+        f2 += (double)v * (double)v;
+    }
+    f2 = block_sum<double>(f2, red);
+    if (threadIdx.x == 0 && f2 != 0.0) atomicAdd(fro + blockIdx.y, f2);      // trace(M M) of the first squaring
 }
 
 // fro[b] = sum_ij M_ij^2 = trace(M M) for symmetric M.  grid: B
@@ -250,9 +285,11 @@ scl_k_scene_frob(const float* __restrict__ M, double* __restrict__ fro, int Kp)
 // Normalised squaring out = in * in / trace(in * in): the top eigenvector's share of every column doubles its
 // exponent per call (K2 does the same in registers for K <= 8).  grid: (Kp/32, Kp/32, B); block (32, 8)
 extern "C" __global__ void __launch_bounds__(256)
-scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const double* __restrict__ fro, int Kp)
+scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const double* __restrict__ fro,
+                   double* __restrict__ fro_next, int Kp)
 {
     __shared__ float ta[32][33], tb[32][33];
+    __shared__ double red[32];
     const int b = blockIdx.z;
     const float* A = in + (size_t)b * Kp * Kp;
     const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32, tx = threadIdx.x, ty = threadIdx.y;
@@ -274,7 +311,22 @@ scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const 
     }
     const float s = fro[b] > 0.0 ? (float)(1.0 / fro[b]) : 0.f;
 #pragma unroll
-    for (int u = 0; u < 4; u++) out[(size_t)b * Kp * Kp + (size_t)(i0 + ty + 8 * u) * Kp + j0 + tx] = acc[u] * s;
+    double f2 = 0.0;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        const float v = acc[u] * s;
+        out[(size_t)b * Kp * Kp + (size_t)(i0 + ty + 8 * u) * Kp + j0 + tx] = v;
+        f2 += (double)v * (double)v;
+    }
+    // trace(out out) for the next squaring, folded in (a separate one-CTA reduction cost 59 us per squaring)
+    f2 = warp_sum<double>(f2);
+    if (tx == 0) red[ty] = f2;
+    __syncthreads();
+    if (tx == 0 && ty == 0) {
+        double t = 0.0;
+        for (int w = 0; w < 8; w++) t += red[w];
+        if (t != 0.0) atomicAdd(fro_next + b, t);
+    }
 }
 
 // Rayleigh quotient of the heaviest column of the squared matrix against the float64 Gram matrix -> lambda_max(S S^T);
@@ -293,18 +345,43 @@ scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ g
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const float* m = M + (size_t)b * Kp * Kp;
     const double* g = gram + (size_t)b * Kp * Kp;
-    if (threadIdx.x == 0) {
-        int best = 0;
-        for (int i = 1; i < K; i++) if (m[(size_t)i * Kp + i] > m[(size_t)best * Kp + best]) best = i;
-        sbest = best;
+    {
+        // heaviest column: largest diagonal entry, lowest index on ties (block-wide arg-max)
+        __shared__ float sval[256];
+        __shared__ int sidx[256];
+        float bv = -1.f; int bi = 0;
+        for (int i = threadIdx.x; i < K; i += blockDim.x) {
+            const float v = m[(size_t)i * Kp + i];
+            if (v > bv) { bv = v; bi = i; }
+        }
+        sval[threadIdx.x] = bv; sidx[threadIdx.x] = bi;
+        __syncthreads();
+        for (int o = 128; o > 0; o >>= 1) {
+            if (threadIdx.x < o) {
+                const float v = sval[threadIdx.x + o]; const int i = sidx[threadIdx.x + o];
+                if (v > sval[threadIdx.x] || (v == sval[threadIdx.x] && i < sidx[threadIdx.x])) {
+                    sval[threadIdx.x] = v; sidx[threadIdx.x] = i;
+                }
+            }
+            __syncthreads();
+        }
+        if (threadIdx.x == 0) sbest = sidx[0];
+    }
+    // A^T A: one (i, j) entry per thread of the first 64
+    __shared__ double sATA[SCL_MAX_BANDS][SCL_MAX_BANDS];
+    if (threadIdx.x < SCL_MAX_BANDS * SCL_MAX_BANDS) {
+        const int i = threadIdx.x / SCL_MAX_BANDS, j = threadIdx.x % SCL_MAX_BANDS;
+        double s = 0.0;
+        if (i < C && j < C)
+            for (int k = 0; k < K; k++) s += (double)A[(size_t)(k0 + k) * C + i] * (double)A[(size_t)(k0 + k) * C + j];
+        sATA[i][j] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x == 32) {
         // lambda_max(A^T A): C x C, normalised squarings in float64, Rayleigh quotient of the heaviest column
         double T[SCL_MAX_BANDS][SCL_MAX_BANDS], Q[SCL_MAX_BANDS][SCL_MAX_BANDS], G0[SCL_MAX_BANDS][SCL_MAX_BANDS];
         for (int i = 0; i < C; i++)
-            for (int j = 0; j < C; j++) {
-                double s = 0.0;
-                for (int k = 0; k < K; k++) s += (double)A[(size_t)(k0 + k) * C + i] * (double)A[(size_t)(k0 + k) * C + j];
-                G0[i][j] = T[i][j] = s;
-            }
+            for (int j = 0; j < C; j++) G0[i][j] = T[i][j] = sATA[i][j];
         for (int it = 0; it < 24; it++) {
             double tr = 0.0;
             for (int i = 0; i < C; i++)

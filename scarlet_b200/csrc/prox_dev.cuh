@@ -292,13 +292,27 @@ __device__ __forceinline__ double scl_add_rn(double a, double b) { return __dadd
 // T = float: the f32 overload (weights rounded to f32 first, operators_pybind11.cc:82-83);
 // T = double: the f64 overload.  NEAREST: prox_monotonic (operators_pybind11.cc:11-25) with
 // the single best-aligned closer neighbour as reference (operator.py:602-611).
+// returns the new value of pixel (y, x); the caller stores it (so that several pixels of one level can have their
+// loads in flight together)
 template <typename T, bool NEAREST>
-__device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
-                                               const float* __restrict__ wtab, const double* __restrict__ ctab,
-                                               T one_minus_thresh) {
+__device__ __forceinline__ T scl_mono_pixel_value(const T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
+                                                  const float* __restrict__ wtab, const double* __restrict__ ctab,
+                                                  T one_minus_thresh) {
     const int ti = ((Yo + Ny - 1) * (2 * Nx - 1) + (Xo + Nx - 1)) * 8;
     T w[8];
     const bool border = (y == 0) | (y == Ny - 1) | (x == 0) | (x == Nx - 1);
+    const int p = y * Nx + x;
+    // the eight neighbours are read unconditionally (taps outside the image read the pixel itself; their weight is 0),
+    // so that these loads and the weight loads below are in flight together: one memory round trip per level when X
+    // lives in HBM/L2 (scene mode)
+    T nb[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+        const int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
+        const bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
+        nb[i] = X[in ? p + oy * Nx + ox : p];
+    }
     if (sizeof(T) == 4 && !NEAREST && !border) {
         const float4 w0 = *reinterpret_cast<const float4*>(wtab + ti);
         const float4 w1 = *reinterpret_cast<const float4*>(wtab + ti + 4);
@@ -326,19 +340,23 @@ __device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int 
         }
     }
     T ref = 0;
-    const int p = y * Nx + x;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
-        int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
         if (w[i] > (T)0) {
-            if (NEAREST) ref = X[p + oy * Nx + ox];
-            else ref = scl_add_rn(ref, scl_mul_rn(X[p + oy * Nx + ox], w[i]));
+            if (NEAREST) ref = nb[i];
+            else ref = scl_add_rn(ref, scl_mul_rn(nb[i], w[i]));
         }
     }
     T r = scl_mul_rn(ref, one_minus_thresh);
     T cur = X[p];
-    X[p] = (r < cur) ? r : cur;
+    return (r < cur) ? r : cur;
+}
+
+template <typename T, bool NEAREST>
+__device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
+                                               const float* __restrict__ wtab, const double* __restrict__ ctab,
+                                               T one_minus_thresh) {
+    X[y * Nx + x] = scl_mono_pixel_value<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, one_minus_thresh);
 }
 
 // ---- fast f32 wavefront (the in-loop path) ---------------------------------
@@ -586,17 +604,32 @@ __device__ void scl_monotonic(T* X, int Ny, int Nx, int cy, int cx,
         X[cy * Nx + cx] = (r < cur) ? r : cur;
     }
     __syncthreads();
+    // The pixels of a level are independent: each thread takes up to MONO_ILP of them per round and computes all
+    // their values before storing any, so their loads overlap (with X in HBM/L2 a round is one memory round trip).
+    constexpr int MONO_ILP = 2;
     for (int v = 1; v <= vmax; v++) {
         const int amin = (v + 2) / 3, amax = v / 2;
-        for (int a = amin + slot; a <= amax; a += nslot) {
-            const int bb = v - 2 * a;
-            // drop duplicate images of the same pixel
-            if ((bb == 0 && sb) || (a == bb && sw)) continue;
-            const int pa = sa ? -a : a, pb = sb ? -bb : bb;
-            const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
-            const int y = cy + Yo, x = cx + Xo;
-            if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
-            scl_mono_pixel<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
+        for (int a0 = amin + slot; a0 <= amax; a0 += MONO_ILP * nslot) {
+            T val[MONO_ILP];
+            int pos[MONO_ILP];
+#pragma unroll
+            for (int u = 0; u < MONO_ILP; u++) {
+                const int a = a0 + u * nslot;
+                pos[u] = -1;
+                if (a > amax) continue;
+                const int bb = v - 2 * a;
+                // drop duplicate images of the same pixel
+                if ((bb == 0 && sb) || (a == bb && sw)) continue;
+                const int pa = sa ? -a : a, pb = sb ? -bb : bb;
+                const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
+                const int y = cy + Yo, x = cx + Xo;
+                if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
+                pos[u] = y * Nx + x;
+                val[u] = scl_mono_pixel_value<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
+            }
+#pragma unroll
+            for (int u = 0; u < MONO_ILP; u++)
+                if (pos[u] >= 0) X[pos[u]] = val[u];
         }
         __syncthreads();
     }
