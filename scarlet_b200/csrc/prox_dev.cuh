@@ -313,9 +313,14 @@ __device__ __forceinline__ T scl_mono_pixel_value(const T* X, int Ny, int Nx, in
         const bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
         nb[i] = X[in ? p + oy * Nx + ox : p];
     }
-    if (sizeof(T) == 4 && !NEAREST && !border) {
-        const float4 w0 = *reinterpret_cast<const float4*>(wtab + ti);
-        const float4 w1 = *reinterpret_cast<const float4*>(wtab + ti + 4);
+    if (sizeof(T) == 4 && !NEAREST && (!border || (Ny >= 2 && Nx >= 2))) {
+        // border pixels take their pre-normalised table (wt9, one per border type) like the streamed sweep: the f64
+        // renormalisation below costs ~2000 instructions, and a warp pays it whenever ONE of its lanes sits on the
+        // frame edge -- at 512x512 nearly every level touches an edge (3 us per level, 77 % of the scene-mode kernel)
+        const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
+        const float* wt = wtab + (size_t)(by * 3 + bx) * (size_t)(2 * Ny - 1) * (size_t)(2 * Nx - 1) * 8;
+        const float4 w0 = *reinterpret_cast<const float4*>(wt + ti);
+        const float4 w1 = *reinterpret_cast<const float4*>(wt + ti + 4);
         w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w;
         w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
     } else {
