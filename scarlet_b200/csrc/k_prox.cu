@@ -212,6 +212,8 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                                              a.wtab, 0.f, Z);
                 }
                 __syncthreads();
+            } else if (SCENE) {
+                scl_monotonic_hbm<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
             } else {
                 scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
             }
@@ -439,7 +441,7 @@ scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, i
     T* g = imgs + (size_t)blockIdx.x * N;
     if (in_place) {
         // images beyond the shared-memory limit: the level loop works on the image where it lies (HBM / L2)
-        scl_monotonic<T, NEAREST>(g, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
+        scl_monotonic_hbm<T, NEAREST>(g, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
         return;
     }
     T* X = reinterpret_cast<T*>(smem_b + pad);

@@ -292,35 +292,16 @@ __device__ __forceinline__ double scl_add_rn(double a, double b) { return __dadd
 // T = float: the f32 overload (weights rounded to f32 first, operators_pybind11.cc:82-83);
 // T = double: the f64 overload.  NEAREST: prox_monotonic (operators_pybind11.cc:11-25) with
 // the single best-aligned closer neighbour as reference (operator.py:602-611).
-// returns the new value of pixel (y, x); the caller stores it (so that several pixels of one level can have their
-// loads in flight together)
 template <typename T, bool NEAREST>
-__device__ __forceinline__ T scl_mono_pixel_value(const T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
-                                                  const float* __restrict__ wtab, const double* __restrict__ ctab,
-                                                  T one_minus_thresh) {
+__device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
+                                               const float* __restrict__ wtab, const double* __restrict__ ctab,
+                                               T one_minus_thresh) {
     const int ti = ((Yo + Ny - 1) * (2 * Nx - 1) + (Xo + Nx - 1)) * 8;
     T w[8];
     const bool border = (y == 0) | (y == Ny - 1) | (x == 0) | (x == Nx - 1);
-    const int p = y * Nx + x;
-    // the eight neighbours are read unconditionally (taps outside the image read the pixel itself; their weight is 0),
-    // so that these loads and the weight loads below are in flight together: one memory round trip per level when X
-    // lives in HBM/L2 (scene mode)
-    T nb[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) {
-        const int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
-        const int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
-        const bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
-        nb[i] = X[in ? p + oy * Nx + ox : p];
-    }
-    if (sizeof(T) == 4 && !NEAREST && (!border || (Ny >= 2 && Nx >= 2))) {
-        // border pixels take their pre-normalised table (wt9, one per border type) like the streamed sweep: the f64
-        // renormalisation below costs ~2000 instructions, and a warp pays it whenever ONE of its lanes sits on the
-        // frame edge -- at 512x512 nearly every level touches an edge (3 us per level, 77 % of the scene-mode kernel)
-        const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
-        const float* wt = wtab + (size_t)(by * 3 + bx) * (size_t)(2 * Ny - 1) * (size_t)(2 * Nx - 1) * 8;
-        const float4 w0 = *reinterpret_cast<const float4*>(wt + ti);
-        const float4 w1 = *reinterpret_cast<const float4*>(wt + ti + 4);
+    if (sizeof(T) == 4 && !NEAREST && !border) {
+        const float4 w0 = *reinterpret_cast<const float4*>(wtab + ti);
+        const float4 w1 = *reinterpret_cast<const float4*>(wtab + ti + 4);
         w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w;
         w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
     } else {
@@ -345,23 +326,19 @@ __device__ __forceinline__ T scl_mono_pixel_value(const T* X, int Ny, int Nx, in
         }
     }
     T ref = 0;
+    const int p = y * Nx + x;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
+        int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+        int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
         if (w[i] > (T)0) {
-            if (NEAREST) ref = nb[i];
-            else ref = scl_add_rn(ref, scl_mul_rn(nb[i], w[i]));
+            if (NEAREST) ref = X[p + oy * Nx + ox];
+            else ref = scl_add_rn(ref, scl_mul_rn(X[p + oy * Nx + ox], w[i]));
         }
     }
     T r = scl_mul_rn(ref, one_minus_thresh);
     T cur = X[p];
-    return (r < cur) ? r : cur;
-}
-
-template <typename T, bool NEAREST>
-__device__ __forceinline__ void scl_mono_pixel(T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
-                                               const float* __restrict__ wtab, const double* __restrict__ ctab,
-                                               T one_minus_thresh) {
-    X[y * Nx + x] = scl_mono_pixel_value<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, one_minus_thresh);
+    X[p] = (r < cur) ? r : cur;
 }
 
 // ---- fast f32 wavefront (the in-loop path) ---------------------------------
@@ -609,6 +586,108 @@ __device__ void scl_monotonic(T* X, int Ny, int Nx, int cy, int cx,
         X[cy * Nx + cx] = (r < cur) ? r : cur;
     }
     __syncthreads();
+    for (int v = 1; v <= vmax; v++) {
+        const int amin = (v + 2) / 3, amax = v / 2;
+        for (int a = amin + slot; a <= amax; a += nslot) {
+            const int bb = v - 2 * a;
+            // drop duplicate images of the same pixel
+            if ((bb == 0 && sb) || (a == bb && sw)) continue;
+            const int pa = sa ? -a : a, pb = sb ? -bb : bb;
+            const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
+            const int y = cy + Yo, x = cx + Xo;
+            if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
+            scl_mono_pixel<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
+        }
+        __syncthreads();
+    }
+}
+
+// ---- the same level loop for images that live in HBM / L2 (scene mode, array operators beyond the shared-memory
+// limit).  Same results bit for bit; written for memory latency instead of shared-memory latency: neighbour loads
+// unconditional, border pixels from their pre-normalised tables, a level's pixels computed before any is stored.
+// Kept apart from scl_monotonic so that the register allocation of the shared-memory kernels does not change.
+// returns the new value of pixel (y, x); the caller stores it (so that several pixels of one level can have their
+// loads in flight together)
+template <typename T, bool NEAREST>
+__device__ __forceinline__ T scl_mono_pixel_value_hbm(const T* X, int Ny, int Nx, int y, int x, int Yo, int Xo,
+                                                  const float* __restrict__ wtab, const double* __restrict__ ctab,
+                                                  T one_minus_thresh) {
+    const int ti = ((Yo + Ny - 1) * (2 * Nx - 1) + (Xo + Nx - 1)) * 8;
+    T w[8];
+    const bool border = (y == 0) | (y == Ny - 1) | (x == 0) | (x == Nx - 1);
+    const int p = y * Nx + x;
+    // the eight neighbours are read unconditionally (taps outside the image read the pixel itself; their weight is 0),
+    // so that these loads and the weight loads below are in flight together: one memory round trip per level when X
+    // lives in HBM/L2 (scene mode)
+    T nb[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+        const int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
+        const bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
+        nb[i] = X[in ? p + oy * Nx + ox : p];
+    }
+    if (sizeof(T) == 4 && !NEAREST && (!border || (Ny >= 2 && Nx >= 2))) {
+        // border pixels take their pre-normalised table (wt9, one per border type) like the streamed sweep: the f64
+        // renormalisation below costs ~2000 instructions, and a warp pays it whenever ONE of its lanes sits on the
+        // frame edge -- at 512x512 nearly every level touches an edge (3 us per level, 77 % of the scene-mode kernel)
+        const int by = (y == 0) ? 1 : ((y == Ny - 1) ? 2 : 0), bx = (x == 0) ? 1 : ((x == Nx - 1) ? 2 : 0);
+        const float* wt = wtab + (size_t)(by * 3 + bx) * (size_t)(2 * Ny - 1) * (size_t)(2 * Nx - 1) * 8;
+        const float4 w0 = *reinterpret_cast<const float4*>(wt + ti);
+        const float4 w1 = *reinterpret_cast<const float4*>(wt + ti + 4);
+        w[0] = w0.x; w[1] = w0.y; w[2] = w0.z; w[3] = w0.w;
+        w[4] = w1.x; w[5] = w1.y; w[6] = w1.z; w[7] = w1.w;
+    } else {
+        double c[8], s = 0.0;
+        int best = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            int oy = (i < 3) ? -1 : (i < 5 ? 0 : 1);
+            int ox = (i == 0 || i == 3 || i == 5) ? -1 : ((i == 1 || i == 6) ? 0 : 1);
+            bool in = (y + oy >= 0) & (y + oy < Ny) & (x + ox >= 0) & (x + ox < Nx);
+            c[i] = in ? ctab[ti + i] : 0.0;
+            s = s + c[i];
+            if (c[i] > c[best]) best = i;
+        }
+        if (NEAREST) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) w[i] = (i == best) ? (T)1 : (T)0;
+        } else {
+            if (s == 0.0) s = 1.0;
+#pragma unroll
+            for (int i = 0; i < 8; i++) w[i] = (T)(c[i] / s);
+        }
+    }
+    T ref = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        if (w[i] > (T)0) {
+            if (NEAREST) ref = nb[i];
+            else ref = scl_add_rn(ref, scl_mul_rn(nb[i], w[i]));
+        }
+    }
+    T r = scl_mul_rn(ref, one_minus_thresh);
+    T cur = X[p];
+    return (r < cur) ? r : cur;
+}
+
+
+template <typename T, bool NEAREST>
+__device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
+                              const float* __restrict__ wtab, const double* __restrict__ ctab, T thresh) {
+    const T omt = (T)1 - thresh;
+    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
+    const int vmax = 2 * max(ay, ax) + min(ay, ax);       // v = level + 1 = 2a + b
+    const int slot = threadIdx.x >> 3, oct = threadIdx.x & 7;
+    const int nslot = blockDim.x >> 3;
+    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
+    __syncthreads();
+    if (NEAREST && threadIdx.x == 0) {
+        // the peak refers to itself (operator.py:641-647): x = min(x, x (1 - thresh))
+        T cur = X[cy * Nx + cx], r = scl_mul_rn(cur, omt);
+        X[cy * Nx + cx] = (r < cur) ? r : cur;
+    }
+    __syncthreads();
     // The pixels of a level are independent: each thread takes up to MONO_ILP of them per round and computes all
     // their values before storing any, so their loads overlap (with X in HBM/L2 a round is one memory round trip).
     constexpr int MONO_ILP = 2;
@@ -630,7 +709,7 @@ __device__ void scl_monotonic(T* X, int Ny, int Nx, int cy, int cx,
                 const int y = cy + Yo, x = cx + Xo;
                 if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
                 pos[u] = y * Nx + x;
-                val[u] = scl_mono_pixel_value<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
+                val[u] = scl_mono_pixel_value_hbm<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
             }
 #pragma unroll
             for (int u = 0; u < MONO_ILP; u++)
