@@ -185,34 +185,55 @@ extern "C" __global__ void __launch_bounds__(256)
 scl_k_scene_gram(const float* __restrict__ S, const int* __restrict__ comp_off, const int* __restrict__ active,
                  float* __restrict__ part, int Kp, int N, int chunk)      // part [B][chunks][Kp][Kp]
 {
-    // pixel-major tiles [pixel][component] (+1 pad: conflict-free transposed stores); a thread owns the 4x4 outputs
-    // (r0 + 16u, c0 + 16v): per pixel 4 + 4 conflict-free shared loads feed 16 FMAs
-    __shared__ float sa[SCN_GP][SCN_GT + 1], sb[SCN_GP][SCN_GT + 1];
+    // pixel-major tiles [pixel][component]; a thread owns the 4x4 outputs (4 ty + u, 4 tx + v) and reads its four
+    // components of a pixel as ONE 16-byte shared load per operand (2 LDS.128 feed 16 FMAs).  The 4-float groups of a
+    // pixel row are XOR-swizzled with the pixel index so that the transposed stores spread over the banks.
+    __shared__ __align__(16) float sa[2][SCN_GP][SCN_GT], sb[2][SCN_GP][SCN_GT];      // double buffered (cp.async)
     const int b = blockIdx.z;
     if (!active[b]) return;
     const int k0 = comp_off[b], K = comp_off[b + 1] - k0;
     const int nt = (Kp + SCN_GT - 1) / SCN_GT, ti = blockIdx.x / nt, tj = blockIdx.x % nt;
     if (tj < ti || ti * SCN_GT >= K || tj * SCN_GT >= K) return;          // upper triangle, mirrored on write
     const int p_lo = blockIdx.y * chunk, p_hi = min(N, p_lo + chunk);
-    const int r0 = threadIdx.x >> 4, c0 = threadIdx.x & 15;
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
     float acc[4][4];
 #pragma unroll
     for (int u = 0; u < 4; u++)
 #pragma unroll
         for (int v = 0; v < 4; v++) acc[u][v] = 0.f;
-    for (int p0 = p_lo; p0 < p_hi; p0 += SCN_GP) {
+    // one pixel block (SCN_GP pixels of the 2 x 64 components) into buffer `buf`: 4-byte async copies, zero filled
+    // past K or past the chunk
+    auto stage = [&](int buf, int p0) {
         for (int i = threadIdx.x; i < SCN_GT * SCN_GP; i += blockDim.x) {
             const int row = i / SCN_GP, col = i % SCN_GP, p = p0 + col;
             const int ka = ti * SCN_GT + row, kb = tj * SCN_GT + row;
-            sa[col][row] = (ka < K && p < p_hi) ? S[(size_t)(k0 + ka) * N + p] : 0.f;
-            sb[col][row] = (kb < K && p < p_hi) ? S[(size_t)(k0 + kb) * N + p] : 0.f;
+            const int phys = (((row >> 2) ^ (col & 15)) << 2) | (row & 3);
+            const bool pin = p < p_hi;
+            const float* ga = S + (size_t)(k0 + (ka < K ? ka : 0)) * N + (pin ? p : p_lo);
+            const float* gb = S + (size_t)(k0 + (kb < K ? kb : 0)) * N + (pin ? p : p_lo);
+            const unsigned da = (unsigned)__cvta_generic_to_shared(&sa[buf][col][phys]);
+            const unsigned db = (unsigned)__cvta_generic_to_shared(&sb[buf][col][phys]);
+            const int na = (ka < K && pin) ? 4 : 0, nb = (kb < K && pin) ? 4 : 0;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" :: "r"(da), "l"(ga), "r"(na));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" :: "r"(db), "l"(gb), "r"(nb));
+        }
+        asm volatile("cp.async.commit_group;\n" ::);
+    };
+    stage(0, p_lo);
+    int buf = 0;
+    for (int p0 = p_lo; p0 < p_hi; p0 += SCN_GP, buf ^= 1) {
+        if (p0 + SCN_GP < p_hi) {
+            stage(buf ^ 1, p0 + SCN_GP);
+            asm volatile("cp.async.wait_group 1;\n" ::);
+        } else {
+            asm volatile("cp.async.wait_group 0;\n" ::);
         }
         __syncthreads();
 #pragma unroll 8
         for (int q = 0; q < SCN_GP; q++) {
-            float a[4], bb[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) { a[u] = sa[q][r0 + 16 * u]; bb[u] = sb[q][c0 + 16 * u]; }
+            const float4 a4 = *reinterpret_cast<const float4*>(&sa[buf][q][(ty ^ (q & 15)) << 2]);
+            const float4 b4 = *reinterpret_cast<const float4*>(&sb[buf][q][(tx ^ (q & 15)) << 2]);
+            const float a[4] = {a4.x, a4.y, a4.z, a4.w}, bb[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
             for (int u = 0; u < 4; u++)
 #pragma unroll
@@ -227,7 +248,7 @@ scl_k_scene_gram(const float* __restrict__ S, const int* __restrict__ comp_off, 
     for (int u = 0; u < 4; u++)
 #pragma unroll
         for (int v = 0; v < 4; v++) {
-            const int i = ti * SCN_GT + r0 + 16 * u, j = tj * SCN_GT + c0 + 16 * v;
+            const int i = ti * SCN_GT + 4 * ty + u, j = tj * SCN_GT + 4 * tx + v;
             if (i < K && j < K) g[(size_t)i * Kp + j] = acc[u][v];
         }
 }
