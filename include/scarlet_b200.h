@@ -86,6 +86,14 @@ int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int N
  * model float32 [n][C][N] (the observation's bands of the model, N = Ny*Nx); op float32 [C][n_lr][N], the
  * resample-and-convolve operator of one geometry (built once by LowResObservation.match); out float32 [n][C][n_lr]. */
 int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, int n_lr, const float* op, void* stream);
+/* fft.match_psfs (fft.py:282-301) as Observation.match calls it (observation.py:155-196), for n PSF sets at once:
+ * diff[i][c] = centred crop of fftshift(irfft2(rfft2(psf_obs[i][c]) / rfft2(psf_model[i or 0]))) at the FFT shape
+ * next_fast_len(k_obs + k_model + padding) per axis (last axis even), float64 arithmetic on the device.
+ * psf_obs float32 [n][C][ky][kx]; psf_model float32 [n_model][kym][kxm], n_model = 1 (shared) or n;
+ * diff float32 [n][C][ky][kx] or NULL; spec complex64 [n][C][128][65] or NULL: the spectrum of the truncated float32
+ * kernel placed for an Ny x Nx frame (what scl_batch_desc.kernel_spec and scl_convolve_f32 take). */
+int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const float* psf_model, int n_model,
+                       int kym, int kxm, int padding, float* diff, float* spec, int Ny, int Nx, void* stream);
 /* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
  * exported for symbol parity, returns SCL_E_LIMIT. */
 int scl_apply_filter_f32(void);

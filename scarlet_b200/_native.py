@@ -299,6 +299,26 @@ def lowres_render(model, op):
     return out
 
 
+def match_psfs(psf_obs, psf_model, padding=3, frame_shape=None, want_diff=True):
+    """fft.match_psfs for n PSF sets at once on the device (fft.py:282-301, observation.py:155-196).
+
+    psf_obs float32 [n, C, ky, kx]; psf_model float32 [1 or n, kym, kxm].  Returns (diff [n, C, ky, kx] or None,
+    spec complex64 [n, C, 128, 65] or None); the spectra are built when `frame_shape` = (Ny, Nx) is given.
+    """
+    require_device()
+    psf_obs = np.ascontiguousarray(psf_obs, dtype=np.float32)
+    psf_model = np.ascontiguousarray(psf_model, dtype=np.float32)
+    if psf_obs.ndim != 4 or psf_model.ndim != 3:
+        raise ValueError("match_psfs: psf_obs [n, C, ky, kx] and psf_model [1 or n, kym, kxm] expected")
+    n, C, ky, kx = psf_obs.shape
+    diff = np.empty((n, C, ky, kx), np.float32) if want_diff else None
+    spec = np.empty((n, C, FFT_EDGE, FFT_EDGE // 2 + 1), np.complex64) if frame_shape is not None else None
+    Ny, Nx = frame_shape if frame_shape is not None else (0, 0)
+    _check(lib().scl_match_psfs_f32(_p(psf_obs), n, C, ky, kx, _p(psf_model), psf_model.shape[0], psf_model.shape[1],
+                                    psf_model.shape[2], int(padding), _p(diff), _p(spec), int(Ny), int(Nx), None))
+    return diff, spec
+
+
 # --------------------------------------------------------------------------- batch fit
 class Batch:
     """Device-resident state of B independent blends sharing one frame shape

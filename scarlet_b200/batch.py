@@ -143,9 +143,8 @@ class BlendBatch:
         mod_psfs = fft.Fourier(np.array(model_psf, dtype=np.float32))
         obs_psfs.normalize(axes=(1, 2)) if not np.allclose(obs_psfs.sum(axis=(1, 2)), 1) else None
         mod_psfs.normalize(axes=(1, 2)) if not np.allclose(mod_psfs.sum(axis=(1, 2)), 1) else None
-        diff = fft.match_psfs(obs_psfs, mod_psfs)                       # Observation.match, observation.py:191-194
-        self.diff_kernels = diff.image
-        spec = _native.kernel_spectrum(self.diff_kernels, Ny, Nx)
+        diff, spec = _native.match_psfs(obs_psfs.image[None], mod_psfs.image[:1], frame_shape=(Ny, Nx))
+        self.diff_kernels, spec = diff[0], spec[0]                      # Observation.match, observation.py:191-194
         peak_obs = obs_psfs.max(axis=(1, 2))
         peak_mod = mod_psfs[0].max()
 

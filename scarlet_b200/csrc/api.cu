@@ -14,6 +14,7 @@
 #include "k_prox.cu"
 #include "k_lowres.cu"
 #include "k_scene.cu"
+#include "k_psf.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
@@ -412,6 +413,52 @@ int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, i
     scl_k_lowres_render<<<dim3(n_lr, C, n), 128, 0, s>>>(dm.p, dop.p, dout.p, C, N, n_lr);
     CK(cudaGetLastError());
     CK(dout.down(out, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const float* psf_model, int n_model,
+                       int kym, int kxm, int padding, float* diff, float* spec, int Ny, int Nx, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!psf_obs || !psf_model || n < 0 || C < 1 || ky < 1 || kx < 1 || kym < 1 || kxm < 1 || padding < 0 ||
+        (n_model != 1 && n_model != n) || (!diff && !spec))
+        return fail(SCL_E_ARG, "bad argument%s%s");
+    if (spec && (Ny < 1 || Nx < 1)) return fail(SCL_E_ARG, "the spectrum needs the frame shape%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    SclPsfArgs a;
+    a.C = C; a.ky = ky; a.kx = kx; a.kym = kym; a.kxm = kxm; a.n_model = n_model;
+    a.Fy = next_fast_len(ky + kym + padding);                          // fft.py:87-106
+    a.Fx = next_fast_len(kx + kxm + padding);
+    while (a.Fx % 2 != 0) a.Fx = next_fast_len(a.Fx + 1);
+    a.oy = ky; a.ox = kx;                                              // fft.py:297-300 (the stack with more bands)
+    a.offy = a.offx = 0;
+    if (spec) {                                                        // placement on the convolution grid, as
+        int Fcy = next_fast_len(Ny + ky + 3), Fcx = next_fast_len(Nx + kx + 3);     // fft.convolve pads it
+        while (Fcx % 2 != 0) Fcx = next_fast_len(Fcx + 1);
+        a.offy = scl_psf_pos(Fcy, ky);
+        a.offx = scl_psf_pos(Fcx, kx);
+        int half = -a.offy;
+        if (ky - 1 + a.offy > half) half = ky - 1 + a.offy;
+        if (-a.offx > half) half = -a.offx;
+        if (kx - 1 + a.offx > half) half = kx - 1 + a.offx;
+        if (2 * half >= SCL_FFT_EDGE - 8) return fail(SCL_E_LIMIT, "difference kernel too wide for the 128-point tile%s%s");
+    }
+    const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, 8);
+    const size_t smem = L.total * sizeof(double);
+    if (smem > 227 * 1024) return fail(SCL_E_LIMIT, "PSF stamps too large for the shared-memory transform%s%s");
+    CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<float> d1, d2, dd, ds;
+    CK(d1.alloc((size_t)n * C * ky * kx)); CK(d2.alloc((size_t)n_model * kym * kxm));
+    CK(d1.up(psf_obs, s)); CK(d2.up(psf_model, s));
+    if (diff) CK(dd.alloc((size_t)n * C * ky * kx));
+    if (spec) CK(ds.alloc((size_t)n * C * SCL_FFT_EDGE * SCL_SPEC_COLS * 2));
+    a.psf_obs = d1.p; a.psf_model = d2.p; a.diff = diff ? dd.p : nullptr; a.spec = spec ? (float2*)ds.p : nullptr;
+    scl_k_match_psfs<<<dim3(C, n), 256, smem, s>>>(a);
+    CK(cudaGetLastError());
+    if (diff) CK(dd.down(diff, s));
+    if (spec) CK(ds.down(spec, s));
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
 }

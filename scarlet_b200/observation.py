@@ -104,7 +104,15 @@ class Observation():
         self._spec = None
         if self.frame.psfs is not model_frame.psfs:
             assert self.frame.psfs is not None and model_frame.psfs is not None
-            self._diff_kernels = fft.match_psfs(self.frame.psfs, model_frame.psfs)
+            p_obs, p_mod = self.frame.psfs.image, model_frame.psfs.image
+            if p_obs.ndim == 3 and p_mod.ndim == 3 and p_mod.shape[0] == 1 and len(self.frame.shape) == 3:
+                # the usual case (one model PSF, one observed PSF per band): kernels and their spectra in one
+                # device pass (csrc/k_psf.cu)
+                diff, spec = _native.match_psfs(p_obs[None], p_mod, frame_shape=self.frame.shape[1:])
+                self._diff_kernels = fft.Fourier(diff[0].astype(p_obs.dtype, copy=False))
+                self._spec = spec[0]
+            else:
+                self._diff_kernels = fft.match_psfs(self.frame.psfs, model_frame.psfs)
         return self
 
     def kernel_spectrum(self):

@@ -199,6 +199,60 @@ def test_large_image_operators(nat):
     assert_allclose(adj[0], ref, rtol=0, atol=1e-5 * np.abs(ref).max())
 
 
+def _moffat(shape, alpha, beta, dy=0.0, dx=0.0):
+    y, x = np.indices(shape, dtype=np.float64)
+    r2 = (y - shape[0] // 2 - dy) ** 2 + (x - shape[1] // 2 - dx) ** 2
+    p = (1 + r2 / alpha ** 2) ** -beta
+    return p / p.sum()
+
+
+@pytest.mark.parametrize("tag", ["tb", "hsc", "sim"])
+def test_match_psfs_vs_reference_fixture(nat, golden, tag):
+    """Difference kernels of the reference's own runs (Observation.match in tests/test_blend.py and the two
+    notebooks' data sets, tests/golden/make_golden.py) through scl_match_psfs_f32."""
+    import os
+    from scarlet_b200 import psf as spsf
+    gdir = os.path.join(os.path.dirname(__file__), "golden")
+    if tag == "tb":
+        psfs, target = golden["tb_psfs"], golden["tb_target_psf"]
+    else:
+        fn = {"hsc": "hsc_cosmos_inputs.npz", "sim": "psf_unmatched_sim_inputs.npz"}[tag]
+        psfs = np.load(os.path.join(gdir, fn))["psfs"]
+        target = spsf.generate_psf_image(spsf.gaussian, psfs[0].shape, sigma=.9).image
+    want = golden[tag + "_diff_kernels"]
+    diff, spec = nat.match_psfs(psfs[None], target[None], frame_shape=(60, 51))
+    scale = np.abs(want).max()
+    assert_allclose(diff[0], want, rtol=0, atol=1e-5 * scale)
+    # the spectrum is that of the float32 kernel the same call returned, placed like the host helper does
+    host = nat.kernel_spectrum(diff[0], 60, 51)
+    assert_allclose(spec[0], host, rtol=0, atol=2e-6 * np.abs(host).max())
+
+
+@pytest.mark.parametrize("ky,kx,kym,kxm", [(41, 41, 41, 41), (25, 27, 15, 15), (24, 24, 41, 41), (31, 30, 11, 12)])
+def test_match_psfs_batch_vs_oracle(nat, ky, kx, kym, kxm):
+    """Many PSF sets in one launch (odd, even and mixed stamp sizes; one model PSF per set or one shared) against the
+    float64 oracle (oracle/ref_fft.match_psfs, fft.py:282-301)."""
+    rng = np.random.default_rng(ky * 100 + kxm)
+    n, C = 9, 5
+    obs = np.stack([[_moffat((ky, kx), rng.uniform(2.0, 3.5), rng.uniform(2.5, 4.0), *rng.uniform(-.3, .3, 2))
+                     for _ in range(C)] for _ in range(n)]).astype(np.float32)
+    shared = _moffat((kym, kxm), 1.3, 4.5)[None].astype(np.float32)
+    each = np.stack([_moffat((kym, kxm), rng.uniform(1.1, 1.5), 4.5) for _ in range(n)]).astype(np.float32)
+    for model in (shared, each):
+        diff, spec = nat.match_psfs(obs, model, frame_shape=(48, 64))
+        for i in range(n):
+            m = model[0 if len(model) == 1 else i]
+            want = ref_fft.match_psfs(obs[i].astype(np.float64), m[None].astype(np.float64))
+            assert_allclose(diff[i], want, rtol=0, atol=1e-5 * np.abs(want).max())
+        host = nat.kernel_spectrum(diff.reshape(n * C, ky, kx), 48, 64).reshape(spec.shape)
+        assert_allclose(spec, host, rtol=0, atol=2e-6 * np.abs(host).max())
+    only_diff, none = nat.match_psfs(obs, shared)
+    assert none is None
+    assert_array_equal(only_diff, nat.match_psfs(obs, shared, frame_shape=(48, 64))[0])
+    with pytest.raises(ValueError):
+        nat.match_psfs(obs, each[:3])
+
+
 def test_errors(nat):
     x = np.zeros((1, 5, 5), np.float32)
     with pytest.raises(ValueError):
