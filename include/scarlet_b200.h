@@ -94,6 +94,12 @@ int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, i
  * kernel placed for an Ny x Nx frame (what scl_batch_desc.kernel_spec and scl_convolve_f32 take). */
 int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const float* psf_model, int n_model,
                        int kym, int kxm, int padding, float* diff, float* spec, int Ny, int Nx, void* stream);
+/* bbox.trim (bbox.py:170-191), bbox.flux_at_edge (bbox.py:194-210) and the pixel sum of n images at once:
+ * x float32 [n][Ny][Nx]; bounds int32 [n][4] = (bottom, top, left, right) of the pixels > min_value, -1 when there
+ * is none (the reference raises ValueError there); edge int32 [n] = any border pixel > min_value; sum float64 [n].
+ * Any output may be NULL. */
+int scl_trim_f32(const float* x, int n, int Ny, int Nx, float min_value, int32_t* bounds, int32_t* edge, double* sum,
+                 void* stream);
 /* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
  * exported for symbol parity, returns SCL_E_LIMIT. */
 int scl_apply_filter_f32(void);
@@ -181,6 +187,18 @@ int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* cent
  * repeated from the same starting point without another host upload (stream-ordered device-to-device copies). */
 int scl_batch_snapshot(scl_batch* batch, void* stream);
 int scl_batch_restore(scl_batch* batch, void* stream);
+/* Post-fit products of every component, from the device state:
+ *   flux   float32 [Ktot][C]  morph.sum() * sed                       (Component.get_flux, component.py:172-175)
+ *   bounds int32   [Ktot][4]  as scl_trim_f32 on the morphology        (bbox.trim, update.py:97-102)
+ *   flags  int32   [Ktot]     BlendFlag bits (component.py:13-36): 1 SED_NOT_CONVERGED, 2 MORPH_NOT_CONVERGED as left by
+ *                             the fit, 4 EDGE_PIXELS = flux_at_edge(morph, min_value), 8 NO_VALID_PIXELS = no pixel
+ *                             above min_value.  Any output may be NULL. */
+int scl_batch_products(scl_batch* batch, float min_value, float* flux, int32_t* bounds, int32_t* flags, void* stream);
+/* Observation.render(component.get_model()) (observation.py:198-220, component.py:148-170) for the components
+ * [k0, k0 + nk): out float32 [nk][n_planes][Ny][Nx], plane p = sed[k, plane_band[p]] * morph_k convolved with the
+ * difference kernel of that plane of the component's blend.  Summed over the components of a blend this is the
+ * rendered model of the loop. */
+int scl_batch_render_components(scl_batch* batch, int k0, int nk, float* out, void* stream);
 /* Profiling aid: while enabled, the constraint kernel adds the clock64 ticks each of its phases took (summed over
  * CTAs: 0 gradient step, 1 centre + symmetry, 2 level list, 3 monotonic sweep, 4 normalise/write-back) to a device
  * counter; the call returns the sums so far in out8 (may be NULL) and clears them. */

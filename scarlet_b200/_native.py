@@ -319,6 +319,21 @@ def match_psfs(psf_obs, psf_model, padding=3, frame_shape=None, want_diff=True):
     return diff, spec
 
 
+def trim(x, min_value=0.0):
+    """bbox.trim / bbox.flux_at_edge / pixel sums of n images at once (bbox.py:170-210).
+
+    x float32 [n, Ny, Nx] -> (bounds int32 [n, 4] = bottom, top, left, right or -1, edge bool [n], sum float64 [n]).
+    """
+    require_device()
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, Ny, Nx = x.shape
+    bounds = np.empty((n, 4), np.int32)
+    edge = np.empty(n, np.int32)
+    tot = np.empty(n, np.float64)
+    _check(lib().scl_trim_f32(_p(x), n, Ny, Nx, c_float(min_value), _p(bounds), _p(edge), _p(tot), None))
+    return bounds, edge.astype(bool), tot
+
+
 # --------------------------------------------------------------------------- batch fit
 class Batch:
     """Device-resident state of B independent blends sharing one frame shape
@@ -468,6 +483,22 @@ class Batch:
                                         _p(out["conv"]), _p(out["n_iter"]), _p(out["active"]), _p(out["logL"]),
                                         _p(out["lipschitz"]), c_void_p(self.stream)))
         self.d2h_bytes = sum(v.nbytes for v in out.values() if v is not None)
+        return out
+
+    def products(self, min_value=0.0):
+        """Per component, from the device state: flux [K, C] (Component.get_flux), bounds [K, 4] (bbox.trim of the
+        morphology; -1 = nothing above min_value), flags [K] (BlendFlag bits incl. EDGE_PIXELS = 4, NO_VALID_PIXELS = 8)."""
+        flux = np.empty((self.K, self.C), np.float32)
+        bounds = np.empty((self.K, 4), np.int32)
+        flags = np.empty(self.K, np.int32)
+        _check(lib().scl_batch_products(self._h, c_float(min_value), _p(flux), _p(bounds), _p(flags), c_void_p(self.stream)))
+        return flux, bounds, flags
+
+    def render_components(self, k0=0, nk=None):
+        """Observation.render(component.get_model()) of components [k0, k0 + nk): float32 [nk, P, Ny, Nx]."""
+        nk = self.K - k0 if nk is None else int(nk)
+        out = np.empty((nk, self.P, self.Ny, self.Nx), np.float32)
+        _check(lib().scl_batch_render_components(self._h, int(k0), nk, _p(out), c_void_p(self.stream)))
         return out
 
     def close(self):

@@ -95,6 +95,19 @@ class _Chunks:
     def phase_clocks(self, enable=True):
         return [sum(v) for v in zip(*[p.phase_clocks(enable) for p in self.parts])]
 
+    def products(self, min_value=0.0):
+        parts = self._map(lambda i: self.parts[i].products(min_value))
+        return tuple(np.concatenate([p[j] for p in parts]) for j in range(3))
+
+    def render_components(self, k0=0, nk=None):
+        nk = self.K - k0 if nk is None else int(nk)
+        out = []
+        for i, part in enumerate(self.parts):           # component ranges of the chunks overlapping [k0, k0 + nk)
+            lo, hi = max(k0, self.koff[i]), min(k0 + nk, self.koff[i + 1])
+            if hi > lo:
+                out.append(part.render_components(lo - self.koff[i], hi - lo))
+        return np.concatenate(out) if out else np.empty((0, self.C, self.Ny, self.Nx), np.float32)
+
     alloc_results = _native.Batch.alloc_results
 
     def download(self, morph=True, out=None):
@@ -269,6 +282,18 @@ class BlendBatch:
         self.host["prev_loss"] = np.array([m[-1] if m else 0. for m in self.mse])
         self._pull(out)
         return info
+
+    def products(self, min_value=0.0):
+        """What a caller reads out of the fitted blends, per component and from the device state:
+        flux [K, C] (Component.get_flux, component.py:172-175), bounds [K, 4] = (bottom, top, left, right) of the
+        morphology above `min_value` (bbox.trim) or -1, flags [K] (BlendFlag bits: convergence as left by the fit,
+        EDGE_PIXELS, NO_VALID_PIXELS)."""
+        return self._dev.products(min_value)
+
+    def render_components(self, k0=0, nk=None):
+        """Observation.render(component.get_model()) for components [k0, k0 + nk), float32 [nk, C, Ny, Nx]: the
+        per-source templates in the observed frame (observation.py:198-220)."""
+        return self._dev.render_components(k0, nk)
 
     def get_model(self, b):
         """Scene model of blend b, [C, Ny, Nx] (ComponentTree.get_model, component.py:321-347)."""

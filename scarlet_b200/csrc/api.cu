@@ -15,6 +15,7 @@
 #include "k_lowres.cu"
 #include "k_scene.cu"
 #include "k_psf.cu"
+#include "k_products.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
@@ -459,6 +460,27 @@ int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const
     CK(cudaGetLastError());
     if (diff) CK(dd.down(diff, s));
     if (spec) CK(ds.down(spec, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_trim_f32(const float* x, int n, int Ny, int Nx, float min_value, int32_t* bounds, int32_t* edge, double* sum,
+                 void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || n < 0 || Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<float> dx;
+    DevBuf<int> db, de;
+    DevBuf<double> dsum;
+    CK(dx.alloc((size_t)n * Ny * Nx)); CK(db.alloc((size_t)4 * n)); CK(de.alloc(n)); CK(dsum.alloc(n));
+    CK(dx.up(x, s));
+    scl_k_trim<<<n, 256, 0, s>>>(dx.p, Ny, Nx, min_value, db.p, de.p, dsum.p);
+    CK(cudaGetLastError());
+    if (bounds) CK(db.down(bounds, s));
+    if (edge) CK(de.down(edge, s));
+    if (sum) CK(dsum.down(sum, s));
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
 }

@@ -185,3 +185,36 @@ def test_failed_sources_are_dropped_like_source_init_error():
         assert_array_equal(bb.host[k], ref.host[k])
     bb.close()
     ref.close()
+
+
+def test_products_of_a_batch():
+    """BlendBatch.products / render_components on the fitted batch: fluxes, footprint boxes and flags
+    against numpy on the downloaded state, per-component renders summing to the oracle's rendered blend model; the
+    chunked batch returns the same arrays."""
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    d = synth.make_blends(range(6), device="cpu")
+    bb = BlendBatch(d["images"], d["psfs"], d["model_psf"], d["centers"], d["bg_rms"], weights=d["weights"])
+    bb.fit(15, 0.0)
+    flux, bounds, flags = bb.products()
+    ren = bb.render_components()
+    off = bb.host["comp_off"]
+    morph = bb.host["morph"].reshape(len(flux), *bb.shape[1:])
+    assert_allclose(flux, morph.sum(axis=(1, 2))[:, None] * bb.host["sed"], rtol=2e-6)
+    for k in range(len(flux)):
+        nz = np.where(morph[k] > 0)
+        assert_array_equal(bounds[k], [nz[0].min(), nz[0].max(), nz[1].min(), nz[1].max()])
+    assert np.all((flags & 3) == (bb.host["conv"] & 3)) and not np.any(flags & 8)
+    for i in range(6):
+        obs = helpers.synthetic_blend(i)[1]
+        want = obs.render(bb.get_model(i).astype(np.float64))
+        assert_allclose(ren[off[i]:off[i + 1]].sum(axis=0), want, rtol=0, atol=2e-5 * np.abs(want).max())
+    many = BlendBatch(d["images"], d["psfs"], d["model_psf"], d["centers"], d["bg_rms"], weights=d["weights"], streams=3)
+    many.fit(15, 0.0)
+    f2, b2, g2 = many.products()
+    assert_array_equal(f2, flux)
+    assert_array_equal(b2, bounds)
+    assert_array_equal(g2, flags)
+    assert_array_equal(many.render_components(2, 9), ren[2:11])
+    many.close()
+    bb.close()

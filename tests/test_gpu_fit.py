@@ -286,3 +286,64 @@ def test_empty_and_errors(nat):
     assert out["n_iter"][0] == 0
     assert_array_equal(out["morph"], p["morph"].astype(np.float32))
     bt.close()
+
+
+# ---------------------------------------------------------------- post-fit products (k_products.cu)
+def _check_products(nat, blends, n_fit=6, **batch_kw):
+    """Device products of a fitted batch against numpy on the downloaded state and the oracle's
+    Observation.render(component.get_model()) (observation.py:198-220, component.py:148-175)."""
+    from oracle import ref_blend as rb
+    bt = nat.Batch(**helpers.pack(blends), **batch_kw)
+    bt.fit(n_fit, 0.0, approximate_L=True)
+    out = bt.download()
+    flux, bounds, flags = bt.products(0.0)
+    got = bt.render_components()
+    part = bt.render_components(1, 2)
+    bt.close()
+    K = len(out["sed"])
+    assert_array_equal(part, got[1:3])
+    k = 0
+    for bl in blends:
+        obs = [o for o in bl.observations if not hasattr(o, "dense_operator")]
+        for _ in bl.components:
+            sed, morph = out["sed"][k], out["morph"][k]
+            assert_allclose(flux[k], morph.sum() * sed, rtol=2e-6)
+            nz = np.where(morph > 0)
+            assert_array_equal(bounds[k], [nz[0].min(), nz[0].max(), nz[1].min(), nz[1].max()])
+            edge = max(morph[:, 0].max(), morph[:, -1].max(), morph[0].max(), morph[-1].max()) > 0
+            assert flags[k] == (out["conv"][k] & 3) | (4 if edge else 0)
+            model = sed[:, None, None].astype(np.float64) * morph[None].astype(np.float64)
+            want = np.concatenate([o.render(model) for o in obs])
+            assert_allclose(got[k], want, rtol=0, atol=1e-5 * max(np.abs(want).max(), 1e-30))
+            k += 1
+    assert k == K
+    return got, out
+
+
+def test_products_fused_and_scene(nat):
+    blends = [helpers.synthetic_blend(s, kmin=3, kmax=6)[3] for s in (11, 12, 13)]
+    a, _ = _check_products(nat, blends)
+    b, _ = _check_products(nat, blends, scene_mode=1)
+    assert_allclose(b, a, rtol=0, atol=2e-5 * np.abs(a).max())
+
+
+def test_products_large_frame_and_planes(nat):
+    """Tiled renders on a 150x140 frame; several observations per blend render to their own planes."""
+    _check_products(nat, [helpers.synthetic_blend(21, Ny=150, Nx=140, kmin=10, kmax=12)[3]], n_fit=3)
+    _check_products(nat, [helpers.multi_obs_blend(5)[-1]], n_fit=4)
+
+
+def test_products_flags_empty_and_edge(nat):
+    """NO_VALID_PIXELS for an all-zero morphology, EDGE_PIXELS for flux on the border (BlendFlag, component.py:13-36)."""
+    blend = helpers.synthetic_blend(3)[3]
+    p = helpers.pack([blend])
+    p["morph"] = np.array(p["morph"], dtype=np.float32)
+    Ny, Nx = p["morph"].shape[-2:]
+    p["morph"][0] = 0
+    p["morph"][1] = 0
+    p["morph"][1].reshape(Ny, Nx)[Ny - 1, 7] = 0.5
+    bt = nat.Batch(**p)
+    flux, bounds, flags = bt.products(0.0)
+    bt.close()
+    assert flags[0] & 8 and not flags[0] & 4 and list(bounds[0]) == [-1] * 4 and np.all(flux[0] == 0)
+    assert flags[1] & 4 and not flags[1] & 8 and list(bounds[1]) == [Ny - 1, Ny - 1, 7, 7]

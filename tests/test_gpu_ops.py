@@ -253,6 +253,54 @@ def test_match_psfs_batch_vs_oracle(nat, ky, kx, kym, kxm):
         nat.match_psfs(obs, each[:3])
 
 
+def test_bbox_kats():
+    """reference tests/test_bbox.py:98-151 (trim, flux_at_edge) through scl_trim_f32."""
+    from scarlet_b200 import bbox
+    x = np.arange(25).reshape(5, 5)
+    x[0] = 0
+    x[:, -2:] = 0
+    assert bbox.trim(x) == bbox.Box((1, 0), 4, 3)
+    x += 10
+    assert bbox.trim(x) == bbox.Box((0, 0), 5, 5)
+    assert bbox.trim(x, 10) == bbox.Box((1, 0), 4, 3)
+    with pytest.raises(ValueError):
+        bbox.trim(x, 100)
+
+    x = np.arange(25).reshape(5, 5)
+    assert bbox.flux_at_edge(x) is True
+    for sl, want in [((0,), True), ((-1,), True), ((slice(None), 0), True), ((slice(None), -1), False)]:
+        x[sl] = 0
+        assert bbox.flux_at_edge(x) is want
+    x = np.arange(25).reshape(5, 5)
+    assert bbox.flux_at_edge(x, 5) is True
+    for sl, want in [((0,), True), ((-1,), True), ((slice(None), 0), True), ((slice(None), -1), False)]:
+        x[sl] = 5
+        assert bbox.flux_at_edge(x, 5) is want
+
+
+def test_trim_many_vs_numpy(nat):
+    """Bounds, edge flags and pixel sums of many ragged footprints at once against numpy (bbox.py:170-210)."""
+    rng = np.random.default_rng(3)
+    n, Ny, Nx = 40, 37, 52
+    X = np.zeros((n, Ny, Nx), np.float32)
+    for i in range(n - 2):
+        y0, x0 = rng.integers(0, Ny - 3), rng.integers(0, Nx - 3)
+        y1, x1 = rng.integers(y0 + 1, Ny + 1), rng.integers(x0 + 1, Nx + 1)
+        X[i, y0:y1, x0:x1] = rng.random((y1 - y0, x1 - x0)) * (rng.random((y1 - y0, x1 - x0)) > .6)
+    X[n - 2] = -1.0                                      # nothing above the cut
+    for mv in (0.0, 0.35):
+        bounds, edge, tot = nat.trim(X, mv)
+        for i in range(n):
+            nz = np.where(X[i] > mv)
+            if len(nz[0]) == 0:
+                assert_array_equal(bounds[i], [-1] * 4)
+            else:
+                assert_array_equal(bounds[i], [nz[0].min(), nz[0].max(), nz[1].min(), nz[1].max()])
+            e = max(X[i][:, 0].max(), X[i][:, -1].max(), X[i][0].max(), X[i][-1].max()) > mv
+            assert bool(edge[i]) == bool(e)
+        assert_allclose(tot, X.astype(np.float64).sum(axis=(1, 2)), rtol=1e-12, atol=1e-9)
+
+
 def test_errors(nat):
     x = np.zeros((1, 5, 5), np.float32)
     with pytest.raises(ValueError):

@@ -92,3 +92,34 @@ def test_kernel_spectrum_layout():
     ref = ref_fft.convolve(img[None], ker[1:2], axes=(1, 2))[0]
     np.testing.assert_allclose(got, ref, atol=1e-5)
     assert [_native.next_fast_len(n) for n in range(1, 300)] == [ref_fft.next_fast_len(n) for n in range(1, 300)]
+
+
+def test_box_container():
+    """reference tests/test_bbox.py:6-95: construction, bounds, slices, empty boxes, copy, ==, &, |."""
+    from scarlet_b200.bbox import Box
+    b1 = Box((4, 1), 7, 6)
+    assert (b1.height, b1.width, b1.bottom, b1.top, b1.left, b1.right) == (7, 6, 4, 10, 1, 6)
+    assert b1.slices == (slice(4, 11), slice(1, 7)) and b1.shape == (7, 6) and b1.is_empty is False
+    b2 = Box.from_bounds(4, 10, 1, 6)
+    assert b2 == b1 and b2.slices == b1.slices and b2.shape == b1.shape
+    e = Box.from_bounds(10, 9, 5, 10)
+    assert e.is_empty is True and (e.width, e.height) == (0, 0)
+    assert e.bottom is None and e.top is None and e.left is None and e.right is None and e.yx0 is None
+    assert e.slices == (slice(0, 0), slice(0, 0))
+
+    b1 = Box((5, 10), 9, 7)
+    c = b1.copy()
+    c.yx0, c.height, c.width = (0, 2), 1, 3
+    assert (b1.bottom, b1.top, b1.left, b1.right) == (c.bottom + 5, c.top + 13, c.left + 8, c.right + 12)
+    c = b1.copy()
+    assert b1 == c and (b1 & c) == b1 and (b1 | c) == b1
+    lo = Box((3, 7), 9, 8)
+    assert b1 != lo
+    assert (b1 & lo) == Box.from_bounds(b1.bottom, lo.top, b1.left, lo.right)
+    assert (b1 | lo) == Box.from_bounds(lo.bottom, b1.top, lo.left, b1.right)
+    hi = Box((7, 12), 11, 13)
+    assert (b1 & hi) == Box.from_bounds(hi.bottom, b1.top, hi.left, b1.right)
+    assert (b1 | hi) == Box.from_bounds(b1.bottom, hi.top, b1.left, hi.right)
+    far = Box((30, 50), 10, 11)
+    assert (b1 & far) == Box((0, 0), width=0, height=0) and (b1 & far).is_empty is True
+    assert (b1 | far) == Box.from_bounds(b1.bottom, far.top, b1.left, far.right)
