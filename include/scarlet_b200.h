@@ -100,6 +100,22 @@ int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const
  * Any output may be NULL. */
 int scl_trim_f32(const float* x, int n, int Ny, int Nx, float min_value, int32_t* bounds, int32_t* edge, double* sum,
                  void* stream);
+/* update.sparse_l0 / sparse_l1 (update.py:71-82; proxmin prox_hard / prox_soft) in place on n float32 values:
+ * mode 0: x[|x| < thresh] = 0;  mode 1: x = sign(x) * max(|x| - thresh, 0).  thresh = the caller's thresh * step. */
+int scl_prox_sparse_f32(float* x, long long n, float thresh, int mode, void* stream);
+/* measurement.threshold (measurement.py:96-113) and update.threshold (update.py:85-103) for n images at once:
+ * thresh float64 [n] = 10^(left edge of the last empty bin of the log10 histogram of the positive pixels), 0 when no
+ * bin is empty; bins int32 [n] = the bin count used (50, or count/10 below 500 positive pixels).  apply != 0 also
+ * zeroes the pixels below the cut in x (float32 [n][Ny][Nx], in place) and returns the box of what is left in
+ * bounds int32 [n][4] (bottom, top, left, right; -1 = nothing). */
+int scl_threshold_f32(float* x, int n, int Ny, int Nx, int apply, double* thresh, int32_t* bins, int32_t* bounds,
+                      void* stream);
+/* interpolation.fft_resample (interpolation.py:408-448) / update.translation (update.py:159-167) for n images at once:
+ * out[i][y][x] = sum_a sum_b ky[i][a] kx[i][b] x[i][y - y0[i] - a][x - x0[i] - b], zero outside the image: the
+ * separable interpolation kernel (lanczos, bilinear, cubic / quintic splines; Ly, Lx <= 16 taps, float64) whose first
+ * tap sits at window offset (y0, x0).  x, out float32 [n][Ny][Nx]. */
+int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const double* ky, const int32_t* y0, int Ly,
+                     const double* kx, const int32_t* x0, int Lx, void* stream);
 /* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
  * exported for symbol parity, returns SCL_E_LIMIT. */
 int scl_apply_filter_f32(void);

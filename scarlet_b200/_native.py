@@ -334,6 +334,45 @@ def trim(x, min_value=0.0):
     return bounds, edge.astype(bool), tot
 
 
+def prox_sparse(x, thresh, mode):
+    """In place on a float32 array: mode 0 hard threshold (prox_hard), 1 soft threshold (prox_soft)."""
+    require_device()
+    if x.dtype != np.float32 or not x.flags.c_contiguous:
+        raise TypeError("prox_sparse: C-contiguous float32 arrays only")
+    _check(lib().scl_prox_sparse_f32(_p(x), ctypes.c_longlong(x.size), c_float(thresh), int(mode), None))
+    return x
+
+
+def threshold(x, apply=False):
+    """measurement.threshold of n images x float32 [n, Ny, Nx]: (thresh float64 [n], bins int32 [n]); with `apply`
+    also update.threshold in place: -> (thresh, bins, bounds int32 [n, 4])."""
+    require_device()
+    if x.dtype != np.float32 or not x.flags.c_contiguous or x.ndim != 3:
+        raise TypeError("threshold: C-contiguous float32 [n, Ny, Nx] arrays only")
+    n, Ny, Nx = x.shape
+    th = np.empty(n, np.float64)
+    bins = np.empty(n, np.int32)
+    bounds = np.empty((n, 4), np.int32) if apply else None
+    _check(lib().scl_threshold_f32(_p(x), n, Ny, Nx, int(bool(apply)), _p(th), _p(bins), _p(bounds), None))
+    return (th, bins, bounds) if apply else (th, bins)
+
+
+def resample(x, ky, y0, kx, x0):
+    """Separable interpolation-kernel convolution of n images (fft_resample): x float32 [n, Ny, Nx]; ky [n, Ly],
+    kx [n, Lx] taps, y0 / x0 [n] offsets of the first tap.  Returns float32 [n, Ny, Nx]."""
+    require_device()
+    x = np.ascontiguousarray(x, dtype=np.float32)
+    n, Ny, Nx = x.shape
+    ky = np.ascontiguousarray(ky, dtype=np.float64).reshape(n, -1)
+    kx = np.ascontiguousarray(kx, dtype=np.float64).reshape(n, -1)
+    y0 = np.ascontiguousarray(y0, dtype=np.int32).reshape(n)
+    x0 = np.ascontiguousarray(x0, dtype=np.int32).reshape(n)
+    out = np.empty_like(x)
+    _check(lib().scl_resample_f32(_p(x), _p(out), n, Ny, Nx, _p(ky), _p(y0), ky.shape[1], _p(kx), _p(x0), kx.shape[1],
+                                  None))
+    return out
+
+
 # --------------------------------------------------------------------------- batch fit
 class Batch:
     """Device-resident state of B independent blends sharing one frame shape

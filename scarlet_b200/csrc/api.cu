@@ -16,6 +16,7 @@
 #include "k_scene.cu"
 #include "k_psf.cu"
 #include "k_products.cu"
+#include "k_update.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
@@ -481,6 +482,67 @@ int scl_trim_f32(const float* x, int n, int Ny, int Nx, float min_value, int32_t
     if (bounds) CK(db.down(bounds, s));
     if (edge) CK(de.down(edge, s));
     if (sum) CK(dsum.down(sum, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_prox_sparse_f32(float* x, long long n, float thresh, int mode, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || n < 0 || (mode != 0 && mode != 1)) return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<float> dx;
+    CK(dx.alloc((size_t)n));
+    CK(dx.up(x, s));
+    scl_k_sparse<<<(unsigned)(((size_t)n + 255) / 256), 256, 0, s>>>(dx.p, (size_t)n, thresh, mode);
+    CK(cudaGetLastError());
+    CK(dx.down(x, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_threshold_f32(float* x, int n, int Ny, int Nx, int apply, double* thresh, int32_t* bins, int32_t* bounds,
+                      void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || n < 0 || Ny < 1 || Nx < 1) return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    DevBuf<float> dx;
+    DevBuf<double> dt;
+    DevBuf<int> db, dbo;
+    CK(dx.alloc((size_t)n * Ny * Nx)); CK(dt.alloc(n)); CK(db.alloc(n)); CK(dbo.alloc((size_t)4 * n));
+    CK(dx.up(x, s));
+    scl_k_threshold<<<n, 256, 0, s>>>(dx.p, Ny, Nx, apply, dt.p, db.p, dbo.p);
+    CK(cudaGetLastError());
+    if (apply) CK(dx.down(x, s));
+    if (thresh) CK(dt.down(thresh, s));
+    if (bins) CK(db.down(bins, s));
+    if (bounds && apply) CK(dbo.down(bounds, s));
+    CK(cudaStreamSynchronize(s));
+    return SCL_OK;
+}
+
+int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const double* ky, const int32_t* y0, int Ly,
+                     const double* kx, const int32_t* x0, int Lx, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x || !out || !ky || !kx || !y0 || !x0 || n < 0 || Ny < 1 || Nx < 1 || Ly < 1 || Lx < 1)
+        return fail(SCL_E_ARG, "bad argument%s%s");
+    if (Ly > SCL_RESAMPLE_MAX_TAPS || Lx > SCL_RESAMPLE_MAX_TAPS) return fail(SCL_E_LIMIT, "at most 16 taps per axis%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t N = (size_t)Ny * Nx;
+    DevBuf<float> dx, dout;
+    DevBuf<double> dky, dkx;
+    DevBuf<int> dy0, dx0;
+    CK(dx.alloc(n * N)); CK(dout.alloc(n * N)); CK(dky.alloc((size_t)n * Ly)); CK(dkx.alloc((size_t)n * Lx));
+    CK(dy0.alloc(n)); CK(dx0.alloc(n));
+    CK(dx.up(x, s)); CK(dky.up(ky, s)); CK(dkx.up(kx, s)); CK(dy0.up(y0, s)); CK(dx0.up(x0, s));
+    scl_k_resample<<<dim3((unsigned)((N + 255) / 256), n), 256, 0, s>>>(dx.p, dout.p, Ny, Nx, dky.p, dy0.p, Ly, dkx.p, dx0.p, Lx);
+    CK(cudaGetLastError());
+    CK(dout.down(out, s));
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
 }

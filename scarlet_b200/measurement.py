@@ -21,3 +21,10 @@ def psf_weighted_centroid(morph, psf, pixel_center):
     c, s = _native.measure(np.asarray(morph, dtype=np.float32)[None],
                            [(int(pixel_center[0]), int(pixel_center[1]))], psf, False, True)
     return (int(c[0, 0]), int(c[0, 1])), (float(s[0, 0]), float(s[0, 1]))
+
+
+def threshold(morph):
+    """Cut-off below which a morphology is fitting noise: 10^(left edge of the last empty bin of the log10 histogram
+    of its positive pixels), and the number of bins used (measurement.py:96-113).  On the device (csrc/k_update.cu)."""
+    th, bins = _native.threshold(np.ascontiguousarray(morph, dtype=np.float32)[None])
+    return (0 if th[0] == 0 else float(th[0])), int(bins[0])

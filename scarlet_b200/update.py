@@ -46,6 +46,51 @@ def normalized(component, type='morph_max'):
     return component
 
 
+def _on_device(morph, fn):
+    """Run `fn` on a float32 C-contiguous copy of `morph` and write the result back in morph's dtype."""
+    x = np.ascontiguousarray(morph, dtype=np.float32)
+    out = fn(x)
+    if x is not morph:
+        morph[...] = x
+    return out
+
+
+def sparse_l0(component, thresh):
+    """L0 sparsity of the morphology: pixels with |morph| < thresh * step_morph are zeroed (update.py:71-75,
+    proxmin prox_hard)."""
+    _on_device(component.morph, lambda x: _native.prox_sparse(x, thresh * component.step_morph, 0))
+    return component
+
+
+def sparse_l1(component, thresh):
+    """L1 sparsity: soft threshold of the morphology by thresh * step_morph (update.py:78-82, proxmin prox_soft)."""
+    _on_device(component.morph, lambda x: _native.prox_sparse(x, thresh * component.step_morph, 1))
+    return component
+
+
+def threshold(component):
+    """Zero the pixels below the noise cut of measurement.threshold and keep the box of the rest in
+    `component.bboxes["thresh"]` (update.py:85-103)."""
+    from .bbox import Box
+    _, _, bounds = _on_device(component.morph, lambda x: _native.threshold(x[None], apply=True))
+    b = bounds[0]
+    if b[0] < 0:
+        raise ValueError("zero-size array to reduction operation minimum which has no identity")
+    if not hasattr(component, "bboxes"):
+        component.bboxes = {}
+    component.bboxes["thresh"] = Box.from_bounds(int(b[0]), int(b[1]), int(b[2]), int(b[3]))
+    return component
+
+
+def translation(component, direction=1, kernel=None, padding=3):
+    """Shift the morphology by `direction` times the component's sub-pixel `shift` (update.py:159-167; like the
+    reference, the resampling always uses the lanczos kernel whatever `kernel` is passed)."""
+    from . import interpolation
+    dy, dx = component.shift
+    component.morph[:] = interpolation.fft_resample(component.morph, dy * direction, dx * direction)
+    return component
+
+
 def monotonic(component, pixel_center, use_nearest=False, thresh=0, exact=False, bbox=None):
     """Radial monotonicity from `pixel_center` (update.py:106-156) on the device."""
     if exact:

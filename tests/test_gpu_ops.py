@@ -301,6 +301,176 @@ def test_trim_many_vs_numpy(nat):
         assert_allclose(tot, X.astype(np.float64).sum(axis=(1, 2)), rtol=1e-12, atol=1e-9)
 
 
+class _Comp:
+    """The attributes of a Component the update functions touch."""
+    def __init__(self, sed, morph, L_morph=1.0):
+        self.sed, self.morph, self.L_morph = sed, morph, L_morph
+        self.shape = (len(sed),) + morph.shape
+
+    @property
+    def step_morph(self):
+        return 1 / self.L_morph
+
+
+def test_sparsity_kats():
+    """reference tests/test_update.py:74-97 (sparse_l0, sparse_l1) through scl_prox_sparse_f32."""
+    from scarlet_b200 import update
+    sed = np.arange(6)
+    morph = np.arange(25, dtype=float).reshape(5, 5)
+    src = _Comp(sed.copy(), morph.copy(), L_morph=1)
+    update.sparse_l0(src, thresh=4)
+    want = morph.copy()
+    want[0, :-1] = 0
+    assert_array_equal(src.sed, sed)
+    assert_array_equal(src.morph, want)
+    src = _Comp(sed.copy(), morph.astype(np.float32), L_morph=0.5)
+    update.sparse_l1(src, thresh=2)
+    want = np.zeros(25)
+    want[5:] = np.arange(20) + 1
+    assert_array_equal(src.morph, want.reshape(5, 5))
+    # both signs
+    x = np.array([[-3., -1., 0., .5, 2.]], dtype=np.float32)
+    a = _Comp(sed, x.copy())
+    update.sparse_l1(a, 1.0)
+    assert_array_equal(a.morph, [[-2., -0., 0., 0., 1.]])
+    a = _Comp(sed, x.copy())
+    update.sparse_l0(a, 1.0)
+    assert_array_equal(a.morph, [[-3., -1., 0., 0., 2.]])
+
+
+def _np_threshold(morph):
+    """measurement.py:96-113 restated with numpy (np.int -> int)."""
+    m = morph[morph > 0]
+    bins = 50
+    if m.size < 500:
+        bins = max(int(m.size / 10), 1)
+        if bins == 1:
+            return 0, bins
+    hist, edges = np.histogram(np.log10(m).reshape(-1), bins)
+    cut = np.where(hist == 0)[0]
+    if len(cut) == 0:
+        return 0, bins
+    return 10 ** edges[cut[-1]], bins
+
+
+def test_threshold_kat():
+    """reference tests/test_update.py:99-119: a 7x7 Gaussian blob on a uniform noise floor keeps only the blob."""
+    from scarlet_b200 import update, measurement, psf as spsf, bbox
+    rs = np.random.RandomState(0)
+    noise = rs.rand(21, 21) * 2
+    signal = np.zeros(noise.shape)
+    signal[7:14, 7:14] = spsf.generate_psf_image(spsf.gaussian, (21, 21), normalize=False, amplitude=10,
+                                                 sigma=3)[7:14, 7:14].image
+    morph = (signal + noise).astype(np.float32)
+    sed = np.arange(5)
+    src = _Comp(sed.copy(), morph.copy())
+    thresh, nbins = measurement.threshold(src.morph)
+    want_t, want_b = _np_threshold(morph)
+    assert nbins == want_b == 44
+    assert_allclose(thresh, want_t, rtol=1e-5)
+    want = np.zeros(morph.shape)
+    want[7:14, 7:14] = morph[7:14, 7:14]
+    update.threshold(src)
+    assert_array_equal(src.sed, sed)
+    assert_array_equal(src.morph, want)
+    assert src.bboxes["thresh"] == bbox.Box((7, 7), 7, 7)
+
+
+def test_threshold_many_vs_numpy(nat):
+    """Cuts, bin counts, zeroed images and boxes of a stack of morphologies against numpy.histogram: bright cores on
+    faint noise floors (a gap in the histogram), plain noise (no gap), tiny footprints (fewer bins, or none)."""
+    rng = np.random.default_rng(8)
+    n, Ny, Nx = 24, 40, 33
+    X = np.zeros((n, Ny, Nx), np.float32)
+    y, x = np.indices((Ny, Nx))
+    for i in range(n):
+        if i % 4 == 0:
+            X[i] = rng.random((Ny, Nx))                                  # no structure
+        elif i % 4 == 1:
+            X[i, 5:8, 4:4 + 1 + i // 4] = rng.random((3, 1 + i // 4)) + .1      # 3 .. 18 pixels
+        else:
+            core = 50 * np.exp(-((y - 17 - i % 5) ** 2 + (x - 15) ** 2) / 8.0)
+            core[core < 5] = 0
+            X[i] = core + 1e-3 * rng.random((Ny, Nx)) * (rng.random((Ny, Nx)) > .3)
+    th, bins = nat.threshold(X.copy())
+    Y = X.copy()
+    th2, bins2, bounds = nat.threshold(Y, apply=True)
+    assert_array_equal(th2, th)
+    assert_array_equal(bins2, bins)
+    gaps = 0
+    for i in range(n):
+        wt, wb = _np_threshold(X[i])
+        assert bins[i] == wb
+        assert_allclose(th[i], wt, rtol=1e-5, atol=0)
+        gaps += wt > 0
+        keep = X[i].astype(np.float64) >= th[i]
+        assert_array_equal(Y[i], np.where(keep, X[i], 0))
+        nz = np.where(Y[i] > 0)
+        assert_array_equal(bounds[i], [nz[0].min(), nz[0].max(), nz[1].min(), nz[1].max()])
+    assert gaps >= n // 2
+
+
+@pytest.fixture(scope="module")
+def gold_resample():
+    import os
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_golden_resample.npz"))
+
+
+@pytest.mark.parametrize("name", ["lanczos", "bilinear", "catmull_rom", "mitchel_netravali", "cubic_spline",
+                                  "quintic_spline"])
+def test_fft_resample_vs_reference_fixture(gold_resample, name):
+    """interpolation.fft_resample of the reference itself (tests/golden/make_golden_resample.py), every kernel of
+    interpolation.py:139-270, six sub-pixel shifts; taps equal to 1e-14, images to float32 rounding."""
+    from scarlet_b200 import interpolation
+    g = gold_resample
+    fn = getattr(interpolation, name)
+    for taps, d in zip(g["taps_" + name], (.217, -.691, .5, 0.)):
+        y, w = fn(d)
+        assert_allclose(np.concatenate([y, w]), taps, rtol=0, atol=1e-14)
+    img = g["img"]
+    for (dy, dx), want in zip(g["shifts"], g["resample_" + name]):
+        got = interpolation.fft_resample(img, dy, dx, kernel=fn)
+        assert got.shape == img.shape and got.dtype == img.dtype
+        assert_allclose(got, want, rtol=0, atol=3e-7 * np.abs(want).max())
+    with pytest.raises(ValueError):
+        interpolation.lanczos(1.5)
+
+
+def test_fft_resample_kat():
+    """reference tests/test_interpolation.py:365-391 (bilinear shifts of a 6x6 ramp)."""
+    from scarlet_b200 import interpolation
+    small = np.arange(36).reshape(6, 6)
+    img = np.zeros((11, 11))
+    img[2:8, 2:8] = small
+    for (dy, dx), (oy, ox) in [((.217, -.026), (3, 1)), ((-.691, .321), (1, 3))]:
+        Dy, Dx = abs(dy), abs(dx)
+        truth = np.zeros(img.shape)
+        truth[2:8, 2:8] += small * (1 - Dx) * (1 - Dy)
+        truth[2:8, ox:ox + 6] += small * Dx * (1 - Dy)
+        truth[oy:oy + 6, 2:8] += small * (1 - Dx) * Dy
+        truth[oy:oy + 6, ox:ox + 6] += small * Dx * Dy
+        assert_allclose(interpolation.fft_resample(img, dy, dx, kernel=interpolation.bilinear), truth, rtol=0, atol=1e-5)
+
+
+def test_translation_and_threshold_vs_reference_fixture(gold_resample):
+    """update.translation (both directions) and update.threshold / measurement.threshold as run by the reference."""
+    from scarlet_b200 import update, measurement
+    g = gold_resample
+    for direction, want in zip((1, -1), g["translation"]):
+        c = _Comp(np.arange(3), g["img"].astype(np.float32))
+        c.shift = (.31, -.44)
+        update.translation(c, direction)
+        assert_allclose(c.morph, want, rtol=0, atol=3e-7 * np.abs(want).max())
+    c = _Comp(np.arange(3), g["thresh_in"].copy())
+    t, b = measurement.threshold(c.morph)
+    assert b == int(g["thresh_bins"])
+    assert_allclose(t, float(g["thresh_value"]), rtol=1e-5)
+    update.threshold(c)
+    assert_array_equal(c.morph, g["thresh_out"])
+    bb = c.bboxes["thresh"]
+    assert_array_equal([bb.bottom, bb.top, bb.left, bb.right], g["thresh_box"])
+
+
 def test_errors(nat):
     x = np.zeros((1, 5, 5), np.float32)
     with pytest.raises(ValueError):
