@@ -5,7 +5,7 @@ import re
 import ctypes
 import numpy as np
 import pytest
-from numpy.testing import assert_array_equal
+from numpy.testing import assert_array_equal, assert_allclose
 
 from oracle import ref_prox, ref_fft
 
@@ -123,3 +123,21 @@ def test_box_container():
     far = Box((30, 50), 10, 11)
     assert (b1 & far) == Box((0, 0), width=0, height=0) and (b1 & far).is_empty is True
     assert (b1 | far) == Box.from_bounds(b1.bottom, far.top, b1.left, far.right)
+
+
+def test_interpolation_taps_vs_reference_fixture():
+    """The 1-D interpolation kernels (host parameters of scl_resample_f32) against the reference's own taps and
+    windows (tests/golden/make_golden_resample.py; interpolation.py:139-270)."""
+    from scarlet_b200 import interpolation
+    g = np.load(os.path.join(ROOT, "tests", "golden", "ref_golden_resample.npz"))
+    for name in ("lanczos", "bilinear", "catmull_rom", "mitchel_netravali", "cubic_spline", "quintic_spline"):
+        fn = getattr(interpolation, name)
+        for taps, d in zip(g["taps_" + name], (.217, -.691, .5, 0.)):
+            y, w = fn(d)
+            assert_allclose(np.concatenate([y, w]), taps, rtol=0, atol=1e-14)
+            assert abs(y.sum() - 1) < 1e-2 or name == "lanczos"
+    k, yw, xw = interpolation.get_separable_kernel(.3, -.2, kernel=interpolation.bilinear)
+    assert_allclose(k, np.outer([.7, .3], [.2, .8]))
+    assert list(yw) == [0, 1] and list(xw) == [-1, 0]
+    with pytest.raises(ValueError):
+        interpolation.bilinear(-1.01)
