@@ -170,6 +170,13 @@ typedef struct {
      * ker_half when any ker_idx >= 0; no low-resolution planes yet. */
     int32_t ker_half;               /* half-width (k/2) of the truncated difference kernels; 0 = not given */
     int32_t scene_mode;             /* 0 = automatic, 1 = force scene mode */
+    /* PSFs instead of spectra (Observation.match inside the batch, observation.py:155-196): when psf_obs is not NULL
+     * kernel_spec is ignored and the n_ker = psf_sets * P spectra are built on the device (as scl_match_psfs_f32 does)
+     * and stay there: spectrum s * P + p is psf_obs[s][p] matched to psf_model[s] (or [0] when psf_model_sets == 1).
+     * ker_half is derived from the stamp size when it is 0. */
+    const float* psf_obs;           /* [psf_sets][P][psf_ky][psf_kx] or NULL */
+    const float* psf_model;         /* [psf_model_sets][psf_kym][psf_kxm] */
+    int32_t psf_sets, psf_model_sets, psf_ky, psf_kx, psf_kym, psf_kxm;
 } scl_batch_desc;
 
 /* Allocate device state for `desc`'s sizes and upload it. */

@@ -37,6 +37,9 @@ class BatchDesc(ctypes.Structure):
         ("n_lr_planes", ctypes.c_int32), ("lr_n", ctypes.c_int32), ("lr_images", c_void_p), ("lr_weights", c_void_p),
         ("n_lr_op", ctypes.c_int32), ("lr_op", c_void_p), ("lr_op_idx", c_void_p),
         ("ker_half", ctypes.c_int32), ("scene_mode", ctypes.c_int32),
+        ("psf_obs", c_void_p), ("psf_model", c_void_p),
+        ("psf_sets", ctypes.c_int32), ("psf_model_sets", ctypes.c_int32), ("psf_ky", ctypes.c_int32),
+        ("psf_kx", ctypes.c_int32), ("psf_kym", ctypes.c_int32), ("psf_kxm", ctypes.c_int32),
     ]
 
 
@@ -380,8 +383,10 @@ class Batch:
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
                  kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None,
-                 plane_band=None, n_obs=1, lr=None, ker_half=0, scene_mode=0):
-        """plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
+                 plane_band=None, n_obs=1, lr=None, ker_half=0, scene_mode=0, psfs=None):
+        """psfs: dict(obs [S, P, ky, kx], model [1 or S, kym, kxm]) instead of kernel_spec (pass None there): the S * P
+        difference kernels are matched on the device and their spectra stay there; ker_idx then indexes s * P + p.
+        plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
         all observations stacked as P planes, plane p seeing model band plane_band[p] (include/scarlet_b200.h)."""
         require_device()
         monotonic_tables(Ny, Nx)
@@ -390,6 +395,7 @@ class Batch:
         # lr: dict(images [B, Plr, n_lr], weights or None, op [n_op, Plr, n_lr, N], op_idx [B]) -- the planes of
         # low-resolution observations; plane_band then lists the full-resolution planes first, these after
         self.lr = lr
+        self.psfs = psfs
         self.Plr = 0 if lr is None else int(np.shape(lr["images"])[1])
         self.P = self.C if plane_band is None else len(self.plane_band) - self.Plr
         self.n_obs = int(n_obs)
@@ -449,6 +455,17 @@ class Batch:
             d.lr_images, d.lr_weights, d.lr_op, d.lr_op_idx = (_p(lr["images"]), _p(lr["weights"]), _p(lr["op"]),
                                                                _p(lr["op_idx"]))
         d.n_ker = 0 if a["kernel_spec"] is None else len(a["kernel_spec"])
+        if self.psfs is not None:
+            if a["kernel_spec"] is not None:
+                raise ValueError("give kernel_spec or psfs, not both")
+            po, pm = ca(self.psfs["obs"], dtype=np.float32), ca(self.psfs["model"], dtype=np.float32)
+            if po.ndim != 4 or pm.ndim != 3 or po.shape[1] != self.P:
+                raise ValueError("psfs: obs [S, P, ky, kx] and model [1 or S, kym, kxm] expected")
+            a.update(psf_obs=po, psf_model=pm)
+            d.psf_obs, d.psf_model = _p(po), _p(pm)
+            d.psf_sets, d.psf_model_sets = po.shape[0], pm.shape[0]
+            d.psf_ky, d.psf_kx, d.psf_kym, d.psf_kxm = po.shape[2], po.shape[3], pm.shape[1], pm.shape[2]
+            d.n_ker = po.shape[0] * self.P
         if a["cw"] is None:
             d.n_cw, d.ph, d.pw = 0, 0, 0
         else:
@@ -457,7 +474,9 @@ class Batch:
         return d
 
     def upload(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-               cw, cw_idx, it0=None, prev_loss=None, src_first=None):
+               cw, cw_idx, it0=None, prev_loss=None, src_first=None, psfs=None):
+        if psfs is not None:
+            self.psfs = psfs
         desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
                           cw, cw_idx, it0, prev_loss, src_first)
         _check(lib().scl_batch_upload(self._h, ctypes.byref(desc), c_void_p(self.stream)))

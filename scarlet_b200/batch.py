@@ -54,6 +54,10 @@ class _Chunks:
                 out[key] = (np.asarray(v[b0:b1 + 1]) - k0).astype(np.int32)
             elif key == "ker_idx":
                 out[key] = v[b0 * self.C:b1 * self.C]
+                if a.get("psfs") is not None:                  # per-blend PSF sets: re-based to the chunk's own sets
+                    out[key] = out[key] - b0 * self.C
+            elif key == "psfs":
+                out[key] = dict(obs=v["obs"][b0:b1], model=v["model"])
             elif key == "src_first":
                 out[key] = (np.asarray(v[k0:k1]) - k0).astype(np.int32)
             elif key in _PER_COMP:
@@ -152,13 +156,25 @@ class BlendBatch:
         B, C, Ny, Nx = images.shape
         self.shape = (C, Ny, Nx)
         bg_rms = np.asarray(bg_rms, dtype=np.float32)
-        obs_psfs = fft.Fourier(np.array(psfs, dtype=np.float32))
+        psf_arr = np.array(psfs, dtype=np.float32)
+        per_blend = psf_arr.ndim == 4                   # [B, C, ky, kx]: every blend has its own observed PSFs
         mod_psfs = fft.Fourier(np.array(model_psf, dtype=np.float32))
-        obs_psfs.normalize(axes=(1, 2)) if not np.allclose(obs_psfs.sum(axis=(1, 2)), 1) else None
         mod_psfs.normalize(axes=(1, 2)) if not np.allclose(mod_psfs.sum(axis=(1, 2)), 1) else None
-        diff, spec = _native.match_psfs(obs_psfs.image[None], mod_psfs.image[:1], frame_shape=(Ny, Nx))
-        self.diff_kernels, spec = diff[0], spec[0]                      # Observation.match, observation.py:191-194
-        peak_obs = obs_psfs.max(axis=(1, 2))
+        if per_blend:
+            if psf_arr.shape[:2] != (B, C):
+                raise ValueError("per-blend psfs must be [B, C, ky, kx]")
+            tot = psf_arr.sum(axis=(2, 3))
+            if not np.allclose(tot, 1):
+                psf_arr = psf_arr * (1 / tot)[:, :, None, None]          # Frame.__init__ normalises, observation.py:48-52
+            # Observation.match runs inside the batch (scl_batch_desc.psf_obs): the B * C spectra never leave HBM
+            self.diff_kernels, spec = None, None
+            peak_obs = psf_arr.max(axis=(2, 3))                          # [B, C]
+        else:
+            obs_psfs = fft.Fourier(psf_arr)
+            obs_psfs.normalize(axes=(1, 2)) if not np.allclose(obs_psfs.sum(axis=(1, 2)), 1) else None
+            diff, spec = _native.match_psfs(obs_psfs.image[None], mod_psfs.image[:1], frame_shape=(Ny, Nx))
+            self.diff_kernels, spec = diff[0], spec[0]                  # Observation.match, observation.py:191-194
+            peak_obs = obs_psfs.max(axis=(1, 2))
         peak_mod = mod_psfs[0].max()
 
         # ---- per-source SED and coadd weights (source.py:41-71,101-136): [K, C] arrays, vectorised over all
@@ -168,7 +184,7 @@ class BlendBatch:
         ctr = (np.concatenate([np.asarray(c).reshape(-1, 2) for c in centers]).astype(np.int32)
                if counts0.sum() else np.zeros((0, 2), np.int32))
         sed = images[owner, :, ctr[:, 0], ctr[:, 1]].astype(np.float32)
-        sed /= np.asarray(peak_obs, dtype=np.float32)
+        sed /= np.asarray(peak_obs[owner] if per_blend else peak_obs, dtype=np.float32)
         sed = sed * np.float32(peak_mod)
         if np.any(bg_rms <= 0):
             raise ValueError("bg_rms must be greater than zero in all channels")
@@ -203,7 +219,11 @@ class BlendBatch:
                 conv=np.full(len(keep_src), 3, np.int32),
                 images=images if len(kept) == B else images[kept],
                 weights=None if wts is None else (wts if len(kept) == B else wts[kept]),
-                kernel_spec=spec, ker_idx=np.tile(np.arange(C, dtype=np.int32), len(kept)),
+                kernel_spec=spec,
+                ker_idx=(np.arange(C * len(kept), dtype=np.int32) if per_blend
+                         else np.tile(np.arange(C, dtype=np.int32), len(kept))),
+                **(dict(psfs=dict(obs=psf_arr if len(kept) == B else psf_arr[kept],
+                                  model=np.asarray(mod_psfs.image[:1], dtype=np.float32))) if per_blend else {}),
                 cw=np.asarray(mod_psfs[0].image, dtype=np.float32)[None], cw_idx=np.zeros(len(kept), np.int32),
                 it0=np.zeros(len(kept), np.int32), prev_loss=np.zeros(len(kept), np.float64))
 

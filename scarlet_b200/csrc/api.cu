@@ -419,6 +419,35 @@ int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, i
     return SCL_OK;
 }
 
+// Shapes, placement and shared-memory size of one scl_k_match_psfs launch (fft.py:87-106 for the FFT lengths of the
+// match, fft.convolve's padding for the placement of the truncated kernel on the 128-point grid).
+int psf_prepare(SclPsfArgs& a, int C, int ky, int kx, int kym, int kxm, int n_model, int padding, bool spec, int Ny, int Nx,
+                size_t* smem, int* ker_half) {
+    a.C = C; a.ky = ky; a.kx = kx; a.kym = kym; a.kxm = kxm; a.n_model = n_model;
+    a.Fy = next_fast_len(ky + kym + padding);
+    a.Fx = next_fast_len(kx + kxm + padding);
+    while (a.Fx % 2 != 0) a.Fx = next_fast_len(a.Fx + 1);
+    a.oy = ky; a.ox = kx;                                              // fft.py:297-300 (the stack with more bands)
+    a.offy = a.offx = 0;
+    if (spec) {
+        int Fcy = next_fast_len(Ny + ky + 3), Fcx = next_fast_len(Nx + kx + 3);
+        while (Fcx % 2 != 0) Fcx = next_fast_len(Fcx + 1);
+        a.offy = scl_psf_pos(Fcy, ky);
+        a.offx = scl_psf_pos(Fcx, kx);
+        int half = -a.offy;
+        if (ky - 1 + a.offy > half) half = ky - 1 + a.offy;
+        if (-a.offx > half) half = -a.offx;
+        if (kx - 1 + a.offx > half) half = kx - 1 + a.offx;
+        if (2 * half >= SCL_FFT_EDGE - 8) return fail(SCL_E_LIMIT, "difference kernel too wide for the 128-point tile%s%s");
+        if (ker_half) *ker_half = half;
+    }
+    const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, 8);
+    *smem = L.total * sizeof(double);
+    if (*smem > 227 * 1024) return fail(SCL_E_LIMIT, "PSF stamps too large for the shared-memory transform%s%s");
+    CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
+    return SCL_OK;
+}
+
 int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const float* psf_model, int n_model,
                        int kym, int kxm, int padding, float* diff, float* spec, int Ny, int Nx, void* stream) {
     if (n == 0) return SCL_OK;
@@ -429,27 +458,9 @@ int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const
     int rc = ensure_globals();
     if (rc) return rc;
     SclPsfArgs a;
-    a.C = C; a.ky = ky; a.kx = kx; a.kym = kym; a.kxm = kxm; a.n_model = n_model;
-    a.Fy = next_fast_len(ky + kym + padding);                          // fft.py:87-106
-    a.Fx = next_fast_len(kx + kxm + padding);
-    while (a.Fx % 2 != 0) a.Fx = next_fast_len(a.Fx + 1);
-    a.oy = ky; a.ox = kx;                                              // fft.py:297-300 (the stack with more bands)
-    a.offy = a.offx = 0;
-    if (spec) {                                                        // placement on the convolution grid, as
-        int Fcy = next_fast_len(Ny + ky + 3), Fcx = next_fast_len(Nx + kx + 3);     // fft.convolve pads it
-        while (Fcx % 2 != 0) Fcx = next_fast_len(Fcx + 1);
-        a.offy = scl_psf_pos(Fcy, ky);
-        a.offx = scl_psf_pos(Fcx, kx);
-        int half = -a.offy;
-        if (ky - 1 + a.offy > half) half = ky - 1 + a.offy;
-        if (-a.offx > half) half = -a.offx;
-        if (kx - 1 + a.offx > half) half = kx - 1 + a.offx;
-        if (2 * half >= SCL_FFT_EDGE - 8) return fail(SCL_E_LIMIT, "difference kernel too wide for the 128-point tile%s%s");
-    }
-    const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, 8);
-    const size_t smem = L.total * sizeof(double);
-    if (smem > 227 * 1024) return fail(SCL_E_LIMIT, "PSF stamps too large for the shared-memory transform%s%s");
-    CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    size_t smem = 0;
+    rc = psf_prepare(a, C, ky, kx, kym, kxm, n_model, padding, spec != nullptr, Ny, Nx, &smem, nullptr);
+    if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     DevBuf<float> d1, d2, dd, ds;
     CK(d1.alloc((size_t)n * C * ky * kx)); CK(d2.alloc((size_t)n_model * kym * kxm));

@@ -218,3 +218,50 @@ def test_products_of_a_batch():
     assert_array_equal(many.render_components(2, 9), ren[2:11])
     many.close()
     bb.close()
+
+
+def test_per_blend_psfs_matched_inside_the_batch():
+    """Every blend with its own observed PSFs (BASELINE config 2 at scale): Observation.match runs on the device inside
+    the batch (scl_batch_desc.psf_obs) and the spectra stay in HBM.  (a) the shared PSFs tiled per blend give the
+    shared-PSF batch bit for bit, chunked or not; (b) four blends with four different PSF sets follow their oracle
+    blends (initialisation and 12 free-running iterations)."""
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    from oracle import ref_blend as rb
+    d = synth.make_blends(range(5), device="cpu")
+    B, C = d["images"].shape[:2]
+    args = (d["model_psf"], d["centers"], d["bg_rms"])
+    one = BlendBatch(d["images"], d["psfs"], *args, weights=d["weights"])
+    tiled = np.broadcast_to(np.asarray(d["psfs"], np.float32), (B,) + np.shape(d["psfs"])).copy()
+    per = BlendBatch(d["images"], tiled, *args, weights=d["weights"])
+    chunked = BlendBatch(d["images"], tiled, *args, weights=d["weights"], streams=2)
+    for bb in (one, per, chunked):
+        bb.fit(12, 0.0)
+    for k in ("sed", "morph", "center", "shift", "logL"):
+        assert_array_equal(per.last[k], one.last[k])
+        assert_array_equal(chunked.last[k], one.last[k])
+    for bb in (one, per, chunked):
+        bb.close()
+
+    ps = np.shape(d["psfs"])[-1]
+    sets = np.array([[rb.generate_psf_image(rb.gaussian, (ps, ps), sigma=1.15 + .1 * i + .15 * b) for b in range(C)]
+                     for i in range(4)], dtype=np.float32)
+    bb = BlendBatch(d["images"][:4], sets, *(d["model_psf"], d["centers"][:4], d["bg_rms"]), weights=d["weights"][:4])
+    init = {k: np.array(v) for k, v in bb.host.items() if k in ("sed", "morph", "center")}
+    bb.fit(12, 0.0)
+    off = bb.host["comp_off"]
+    mpsf = np.asarray(d["model_psf"], np.float32)
+    for i in range(4):
+        frame = rb.Frame(d["images"][i].shape, psfs=mpsf, dtype=np.float32)
+        obs = rb.Observation(d["images"][i], psfs=sets[i], weights=d["weights"][i]).match(frame)
+        srcs = [rb.ExtendedSource(frame, tuple(int(v) for v in c), obs, np.asarray(d["bg_rms"], np.float32))
+                for c in np.asarray(d["centers"][i]).reshape(-1, 2)]
+        assert off[i + 1] - off[i] == len(srcs)
+        for j, s in enumerate(srcs):
+            assert_array_equal(init["center"][off[i] + j], s.pixel_center)
+            assert_allclose(init["sed"][off[i] + j], s.sed, rtol=2e-6)
+            assert_allclose(init["morph"][off[i] + j].reshape(s.morph.shape), s.morph, rtol=0, atol=REL)
+        bl = rb.Blend(srcs, obs)
+        bl.fit(12, 0.0)
+        assert_allclose(bb.last["logL"][i], np.array(bl.mse, dtype=np.float64), rtol=20 * REL)
+    bb.close()
