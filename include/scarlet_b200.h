@@ -181,7 +181,8 @@ typedef struct {
 
 /* Allocate device state for `desc`'s sizes and upload it. */
 int scl_batch_create(const scl_batch_desc* desc, scl_batch** out, void* stream);
-/* Re-upload inputs of identical sizes into an existing batch (no allocation). */
+/* Re-upload inputs of identical sizes into an existing batch (no allocation).  kernel_spec == NULL and
+ * psf_obs == NULL (with the same n_ker) keep the kernel spectra the batch already holds. */
 int scl_batch_upload(scl_batch* batch, const scl_batch_desc* desc, void* stream);
 /* Blend.fit(max_iter, e_rel, approximate_L) (blend.py:65-102) for every blend of the batch.
  * check_every: how often (iterations) the host polls the device-side active count to stop early.

@@ -411,7 +411,7 @@ class Batch:
         _check(lib().scl_batch_create(ctypes.byref(desc), ctypes.byref(self._h), c_void_p(self.stream)))
 
     def _desc(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-              cw, cw_idx, it0, prev_loss, src_first=None):
+              cw, cw_idx, it0, prev_loss, src_first=None, keep_spectra=False):
         N = self.Ny * self.Nx
         ca = np.ascontiguousarray
         comp_off = ca(comp_off, dtype=np.int32)
@@ -458,14 +458,17 @@ class Batch:
         if self.psfs is not None:
             if a["kernel_spec"] is not None:
                 raise ValueError("give kernel_spec or psfs, not both")
-            po, pm = ca(self.psfs["obs"], dtype=np.float32), ca(self.psfs["model"], dtype=np.float32)
-            if po.ndim != 4 or pm.ndim != 3 or po.shape[1] != self.P:
+            po, pm = np.shape(self.psfs["obs"]), np.shape(self.psfs["model"])
+            if len(po) != 4 or len(pm) != 3 or po[1] != self.P:
                 raise ValueError("psfs: obs [S, P, ky, kx] and model [1 or S, kym, kxm] expected")
-            a.update(psf_obs=po, psf_model=pm)
-            d.psf_obs, d.psf_model = _p(po), _p(pm)
-            d.psf_sets, d.psf_model_sets = po.shape[0], pm.shape[0]
-            d.psf_ky, d.psf_kx, d.psf_kym, d.psf_kxm = po.shape[2], po.shape[3], pm.shape[1], pm.shape[2]
-            d.n_ker = po.shape[0] * self.P
+            d.n_ker = po[0] * self.P
+            d.ker_half = self.ker_half = self.ker_half or kernel_half(po[2], po[3], self.Ny, self.Nx)
+            if not keep_spectra:            # (re-)match on the device; otherwise the batch keeps what it holds
+                obs, mod = ca(self.psfs["obs"], dtype=np.float32), ca(self.psfs["model"], dtype=np.float32)
+                a.update(psf_obs=obs, psf_model=mod)
+                d.psf_obs, d.psf_model = _p(obs), _p(mod)
+                d.psf_sets, d.psf_model_sets = po[0], pm[0]
+                d.psf_ky, d.psf_kx, d.psf_kym, d.psf_kxm = po[2], po[3], pm[1], pm[2]
         if a["cw"] is None:
             d.n_cw, d.ph, d.pw = 0, 0, 0
         else:
@@ -475,10 +478,13 @@ class Batch:
 
     def upload(self, comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
                cw, cw_idx, it0=None, prev_loss=None, src_first=None, psfs=None):
+        """psfs: the PSF sets of the batch; the same object as at construction (or None) keeps the spectra already
+        matched on the device, a new one is matched again."""
+        keep = self.psfs is not None and (psfs is None or psfs is self.psfs)
         if psfs is not None:
             self.psfs = psfs
         desc = self._desc(comp_off, sed, morph, cflags, center, shift, conv, images, weights, kernel_spec, ker_idx,
-                          cw, cw_idx, it0, prev_loss, src_first)
+                          cw, cw_idx, it0, prev_loss, src_first, keep_spectra=keep)
         _check(lib().scl_batch_upload(self._h, ctypes.byref(desc), c_void_p(self.stream)))
 
     def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False):

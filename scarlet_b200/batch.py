@@ -35,6 +35,7 @@ class _Chunks:
         cuts = np.searchsorted(off, off[-1] * np.arange(1, n) / n)
         self.bounds = np.unique(np.concatenate([[0], cuts, [B]])).astype(int)
         self.koff = off[self.bounds].astype(int)
+        self._psf_slices = {}
         self.streams = [_native.stream_create() for _ in range(len(self.bounds) - 1)]
         self.parts = [_native.Batch(stream=s, **self._slice(host, i)) for i, s in enumerate(self.streams)]
         self.pool = ThreadPoolExecutor(len(self.parts))
@@ -56,8 +57,8 @@ class _Chunks:
                 out[key] = v[b0 * self.C:b1 * self.C]
                 if a.get("psfs") is not None:                  # per-blend PSF sets: re-based to the chunk's own sets
                     out[key] = out[key] - b0 * self.C
-            elif key == "psfs":
-                out[key] = dict(obs=v["obs"][b0:b1], model=v["model"])
+            elif key == "psfs":             # one slice object per chunk, so that a re-upload keeps the matched spectra
+                out[key] = self._psf_slices.setdefault((i, id(v)), dict(obs=v["obs"][b0:b1], model=v["model"]))
             elif key == "src_first":
                 out[key] = (np.asarray(v[k0:k1]) - k0).astype(np.int32)
             elif key in _PER_COMP:
