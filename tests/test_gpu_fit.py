@@ -194,6 +194,17 @@ def test_lockstep_synthetic(nat, seed):
     _lockstep(nat, blend, 12)
 
 
+@pytest.mark.parametrize("C,Ny,Nx,psf", [(1, 39, 41, 15), (2, 38, 38, 11), (3, 47, 40, 21), (4, 41, 52, 15), (6, 40, 40, 21),
+                                         (7, 39, 45, 11), (8, 52, 38, 21)])
+def test_lockstep_band_counts_and_ragged_frames(nat, C, Ny, Nx, psf):
+    """Every band count the kernels are instantiated for (1 .. 8), odd / non-square frames and small PSF stamps,
+    every iteration vs the oracle (exact L and approximate L)."""
+    _, _, srcs, blend = helpers.synthetic_blend(100 + C, C=C, Ny=Ny, Nx=Nx, kmin=2, kmax=3, psf_size=psf)
+    assert len(srcs) >= 1
+    _lockstep(nat, blend, 5)
+    _lockstep(nat, blend, 3, approximate_L=True)
+
+
 @pytest.mark.parametrize("tag", ["hsc", "sim"])
 def test_free_running_vs_reference(nat, golden, tag):
     """Whole fit on the GPU vs the reference's own run (tests/golden): iteration count, per-iteration
