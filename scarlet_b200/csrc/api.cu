@@ -441,7 +441,7 @@ int psf_prepare(SclPsfArgs& a, int C, int ky, int kx, int kym, int kxm, int n_mo
         if (2 * half >= SCL_FFT_EDGE - 8) return fail(SCL_E_LIMIT, "difference kernel too wide for the 128-point tile%s%s");
         if (ker_half) *ker_half = half;
     }
-    const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, 8);
+    const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, SCL_PSF_THREADS / 32);
     *smem = L.total * sizeof(double);
     if (*smem > 227 * 1024) return fail(SCL_E_LIMIT, "PSF stamps too large for the shared-memory transform%s%s");
     CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
@@ -468,7 +468,7 @@ int scl_match_psfs_f32(const float* psf_obs, int n, int C, int ky, int kx, const
     if (diff) CK(dd.alloc((size_t)n * C * ky * kx));
     if (spec) CK(ds.alloc((size_t)n * C * SCL_FFT_EDGE * SCL_SPEC_COLS * 2));
     a.psf_obs = d1.p; a.psf_model = d2.p; a.diff = diff ? dd.p : nullptr; a.spec = spec ? (float2*)ds.p : nullptr;
-    scl_k_match_psfs<<<dim3(C, n), 256, smem, s>>>(a);
+    scl_k_match_psfs<<<dim3(C, n), SCL_PSF_THREADS, smem, s>>>(a);
     CK(cudaGetLastError());
     if (diff) CK(dd.down(diff, s));
     if (spec) CK(ds.down(spec, s));

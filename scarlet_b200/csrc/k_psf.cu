@@ -16,7 +16,7 @@
 //   t_j = j + (F-k+1)//2 - F//2      (pad left (F-k+1)//2, ifftshift by F//2)
 // and the crop of the fftshift-ed inverse reads exactly the same coordinates with k = the output length.
 //
-// One CTA per (PSF set, band), 256 threads:
+// One CTA per (PSF set, band), 512 threads (one CTA per SM by shared memory; 16 warps hide the shared-load latency):
 //   1  T1[i][v] = sum_j psf_obs[i][j]   w_x^(-v t_j)     T2 likewise for the model PSF          (v = 0..Fx/2)
 //   2  one warp per column v:  P1[u] = sum_i T1[i][v] w_y^(-u t_i), P2[u];  Q[u] = P1/P2;
 //                               U[y][v] = sum_u Q[u] w_y^(+u r_y)                               (y = cropped rows)
@@ -65,7 +65,8 @@ __host__ __device__ inline SclPsfLayout scl_psf_layout(int ky, int kx, int kym, 
     return L;
 }
 
-extern "C" __global__ void __launch_bounds__(256)
+#define SCL_PSF_THREADS 512
+extern "C" __global__ void __launch_bounds__(SCL_PSF_THREADS)
 scl_k_match_psfs(SclPsfArgs a)
 {
     extern __shared__ double smem_psf[];
