@@ -1,10 +1,10 @@
-"""Component / ComponentTree: the parameter containers (mirrors scarlet/component.py).
+"""Component / ComponentTree: the parameter containers of a blend (the names and behaviour of scarlet/component.py).
 
-They hold host numpy copies of SED and morphology; `Blend.fit` packs them into device
-buffers, runs the CUDA loop and writes the results back (`_sed`/`_morph` are replaced,
-as in the reference where every step rebinds them, blend.py:92-95).
+They hold host numpy copies of SED and morphology; `Blend.fit` packs them into device buffers, runs the CUDA loop
+and writes the results back (`_sed` / `_morph` are rebound, as in the reference where every step rebinds them,
+blend.py:92-95).  Nothing here computes on pixels inside the loop.
 """
-from enum import Flag, auto
+import enum
 import logging
 
 import numpy as np
@@ -12,212 +12,180 @@ import numpy as np
 logger = logging.getLogger("scarlet.component")
 
 
-class BlendFlag(Flag):
-    """Flags that can be set by scarlet (component.py:13-36)."""
+class BlendFlag(enum.Flag):
+    """Status bits of a component (component.py:13-36); the device keeps the same bit values
+    (`scl_batch_products`, include/scarlet_b200.h)."""
     NONE = 0
-    SED_NOT_CONVERGED = auto()
-    MORPH_NOT_CONVERGED = auto()
-    EDGE_PIXELS = auto()
-    NO_VALID_PIXELS = auto()
+    SED_NOT_CONVERGED = 1
+    MORPH_NOT_CONVERGED = 2
+    EDGE_PIXELS = 4
+    NO_VALID_PIXELS = 8
 
 
 class Prior():
-    """Differentiable prior hook (component.py:39-67).  Kept for API parity; `Blend.fit`
-    rejects components with a prior (a Python callback cannot run inside the CUDA loop)."""
+    """Differentiable prior hook (component.py:39-67).  Kept for API parity; `Blend.fit` rejects components with a
+    prior (a Python callback cannot run inside the CUDA loop)."""
 
     def __init__(self, grad_func, L_func):
-        self._grad_func = grad_func
-        self._L_func = L_func
-        self.sed_grad = 0
-        self.morph_grad = 0
+        self._grad_func, self._L_func = grad_func, L_func
+        self.sed_grad = self.morph_grad = 0
 
     def compute_grad(self, component):
-        self.sed_grad, self.morph_grad = self._grad_func(component._sed, component._morph)
-        self.L_sed, self.L_morph = self._L_func(component._sed, component._morph)
+        state = (component._sed, component._morph)
+        self.sed_grad, self.morph_grad = self._grad_func(*state)
+        self.L_sed, self.L_morph = self._L_func(*state)
 
 
-class Component():
-    """A single component in a blend (component.py:70-210)."""
+class _Node:
+    """Position of a component or subtree inside its parent tree."""
+    _index = None
+    _parent = None
+
+    @property
+    def coord(self):
+        """Indices leading from the root tree to this node (None for a node outside any tree)."""
+        if self._index is None:
+            return None
+        above = self._parent.coord if self._parent._index is not None else ()
+        return tuple(above) + (self._index,)
+
+    def _attach(self, parent, index):
+        self._parent, self._index = parent, index
+
+
+def _inverse_or_none(obj, name):
+    try:
+        return 1 / getattr(obj, name)
+    except AttributeError:
+        return None
+
+
+class Component(_Node):
+    """One SED x morphology term of the scene model (component.py:70-210)."""
 
     def __init__(self, frame, sed, morph, prior=None, fix_sed=False, fix_morph=False):
         self._frame = frame
-        self._sed = np.array(sed, dtype=self._frame.dtype)
-        self._morph = np.array(morph, dtype=self._frame.dtype)
-        self.sed_grad = 0
-        self.morph_grad = 0
+        dtype = frame.dtype
+        self._sed = np.array(sed, dtype=dtype)
+        self._morph = np.array(morph, dtype=dtype)
+        self._last_sed = np.zeros_like(self._sed)
+        self._last_morph = np.zeros_like(self._morph)
         self.prior = prior
-        self.L_sed = 1
-        self.L_morph = 1
+        self.fix_sed, self.fix_morph = fix_sed, fix_morph
+        self.sed_grad = self.morph_grad = 0
+        self.L_sed = self.L_morph = 1
         self.flags = BlendFlag.SED_NOT_CONVERGED | BlendFlag.MORPH_NOT_CONVERGED
-        self._last_sed = np.zeros(self._sed.shape, dtype=self._sed.dtype)
-        self._last_morph = np.zeros(self._morph.shape, dtype=self._morph.dtype)
-        self._index = None
-        self._parent = None
-        self.fix_sed = fix_sed
-        self.fix_morph = fix_morph
 
-    @property
-    def shape(self):
-        return self._frame.shape
-
-    @property
-    def coord(self):
-        if self._index is not None:
-            if self._parent._index is not None:
-                return tuple(self._parent.coord) + (self._index,)
-            return (self._index,)
-
-    @property
-    def frame(self):
-        return self._frame
-
-    @property
-    def sed(self):
-        return self._sed
-
-    @property
-    def morph(self):
-        return self._morph
+    frame = property(lambda self: self._frame)
+    shape = property(lambda self: self._frame.shape)
+    sed = property(lambda self: self._sed)
+    morph = property(lambda self: self._morph)
+    step_sed = property(lambda self: _inverse_or_none(self, "L_sed"))
+    step_morph = property(lambda self: _inverse_or_none(self, "L_morph"))
 
     def get_model(self, sed=None, morph=None):
-        if sed is not None and morph is not None:
-            return sed[:, None, None] * morph[None, :, :]
-        elif sed is None and morph is None:
-            return self._sed[:, None, None] * self._morph[None, :, :]
-        raise ValueError("You need to supply `sed` and `morph` or neither")
+        """sed[c] * morph[y, x] as a (C, Ny, Nx) cube; both arguments or neither (component.py:148-170)."""
+        if (sed is None) != (morph is None):
+            raise ValueError("You need to supply `sed` and `morph` or neither")
+        if sed is None:
+            sed, morph = self._sed, self._morph
+        return sed[:, None, None] * morph[None, :, :]
 
     def get_flux(self):
+        """Total flux per band (component.py:172-175)."""
         return self.morph.sum() * self.sed
 
     def backward_prior(self):
-        if self.prior is not None:
-            self.prior.compute_grad(self)
-            if not self.fix_morph:
-                self.morph_grad += self.prior.morph_grad
-                self.L_morph += self.prior.L_morph
-            if not self.fix_sed:
-                self.sed_grad += self.prior.sed_grad
-                self.L_sed += self.prior.L_sed
+        """Add the prior's gradients and Lipschitz terms to the free parameters (component.py:177-190)."""
+        if self.prior is None:
+            return
+        self.prior.compute_grad(self)
+        for fixed, what in ((self.fix_morph, "morph"), (self.fix_sed, "sed")):
+            if not fixed:
+                setattr(self, what + "_grad", getattr(self, what + "_grad") + getattr(self.prior, what + "_grad"))
+                setattr(self, "L_" + what, getattr(self, "L_" + what) + getattr(self.prior, "L_" + what))
 
     def update(self):
+        """Constraint hook; sources override it (component.py:192-196)."""
         return self
 
-    @property
-    def step_morph(self):
-        try:
-            return 1 / self.L_morph
-        except AttributeError:
-            return None
 
-    @property
-    def step_sed(self):
-        try:
-            return 1 / self.L_sed
-        except AttributeError:
-            return None
-
-
-class ComponentTree():
-    """Hierarchical collection of Components (component.py:213-408)."""
+class ComponentTree(_Node):
+    """Sources and sub-trees of a scene, addressable by position (component.py:213-408)."""
 
     def __init__(self, components):
-        if not hasattr(components, "__iter__"):
-            components = (components,)
-        self._tree = tuple(components)
-        self._index = None
-        self._parent = None
-        for i, c in enumerate(self._tree):
-            if not isinstance(c, ComponentTree) and not isinstance(c, Component):
+        nodes = tuple(components) if hasattr(components, "__iter__") else (components,)
+        for node in nodes:
+            if not isinstance(node, (Component, ComponentTree)):
                 raise NotImplementedError("argument needs to be list of Components or ComponentTrees")
-            assert c.frame is self.frame, "All components need to share the same Frame"
-            c._index = i
-            c._parent = self
+        self._tree = nodes
+        for i, node in enumerate(nodes):
+            assert node.frame is self.frame, "All components need to share the same Frame"
+            node._attach(self, i)
         self._components = None
 
+    # ---- structure
     @property
     def components(self):
+        """The leaf components in tree order, each object once."""
         if self._components is None:
-            components = []
-            for c in self._tree:
-                _c = c.components if isinstance(c, ComponentTree) else [c]
-                for __c in _c:
-                    if not any(__c is o for o in components):
-                        components.append(__c)
-            self._components = tuple(components)
+            seen, flat = set(), []
+            for node in self._tree:
+                for leaf in (node.components if isinstance(node, ComponentTree) else (node,)):
+                    if id(leaf) not in seen:
+                        seen.add(id(leaf))
+                        flat.append(leaf)
+            self._components = tuple(flat)
         return self._components
 
-    @property
-    def n_components(self):
-        return len(self.components)
-
-    @property
-    def K(self):
-        return self.n_components
-
-    @property
-    def frame(self):
-        return self._tree[0].frame
-
-    @property
-    def sources(self):
-        return self._tree
-
-    @property
-    def n_sources(self):
-        return len(self._tree)
-
-    @property
-    def coord(self):
-        if self._index is not None:
-            if self._parent._index is not None:
-                return tuple(self._parent.coord) + (self._index,)
-            return (self._index,)
-
-    def get_model(self, seds=None, morphs=None):
-        model = np.zeros(self.frame.shape, dtype=self.frame.dtype)
-        for k in range(self.K):
-            if seds is not None and morphs is not None:
-                model = model + self.components[k].get_model(seds[k], morphs[k])
-            else:
-                model = model + self.components[k].get_model()
-        return model
-
-    def get_flux(self):
-        for k, component in enumerate(self.components):
-            if k == 0:
-                model = component.get_flux()
-            else:
-                model += component.get_flux()
-        return model
-
-    def update(self):
-        for node in self._tree:
-            node.update()
-
-    def __iadd__(self, c):
-        c_index = self.n_sources
-        if isinstance(c, ComponentTree):
-            self._tree = self._tree + c._tree
-        elif isinstance(c, Component):
-            self._tree = self._tree + (c,)
-        else:
-            raise NotImplementedError("argument needs to be Component or ComponentTree")
-        c._index = c_index
-        c._parent = self
-        self._components = None
-        return self
-
-    def __getitem__(self, coord):
-        if isinstance(coord, (tuple, list)):
-            if len(coord) > 1:
-                return self._tree[coord[0]].__getitem__(coord[1:])
-            return self._tree[coord[0]]
-        elif isinstance(coord, int):
-            return self._tree[coord]
-        raise NotImplementedError("coord needs to be index or list of indices")
+    n_components = property(lambda self: len(self.components))
+    K = property(lambda self: len(self.components))
+    sources = property(lambda self: self._tree)
+    n_sources = property(lambda self: len(self._tree))
+    frame = property(lambda self: self._tree[0].frame)
 
     def __iter__(self):
         return iter(self._tree)
 
     def __len__(self):
         return len(self._tree)
+
+    def __getitem__(self, coord):
+        if isinstance(coord, int):
+            return self._tree[coord]
+        if isinstance(coord, (tuple, list)):
+            node = self._tree[coord[0]]
+            return node[coord[1:]] if len(coord) > 1 else node
+        raise NotImplementedError("coord needs to be index or list of indices")
+
+    def __iadd__(self, other):
+        if isinstance(other, ComponentTree):
+            grown = self._tree + other._tree
+        elif isinstance(other, Component):
+            grown = self._tree + (other,)
+        else:
+            raise NotImplementedError("argument needs to be Component or ComponentTree")
+        other._attach(self, self.n_sources)
+        self._tree = grown
+        self._components = None
+        return self
+
+    # ---- model
+    def get_model(self, seds=None, morphs=None):
+        """Sum of the component models, optionally for given parameters (component.py:321-347)."""
+        model = np.zeros(self.frame.shape, dtype=self.frame.dtype)
+        given = seds is not None and morphs is not None
+        for k, comp in enumerate(self.components):
+            model = model + (comp.get_model(seds[k], morphs[k]) if given else comp.get_model())
+        return model
+
+    def get_flux(self):
+        """Flux per band summed over the components (component.py:349-357)."""
+        total = None
+        for comp in self.components:
+            total = comp.get_flux() if total is None else total + comp.get_flux()
+        return total
+
+    def update(self):
+        for node in self._tree:
+            node.update()
