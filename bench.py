@@ -234,15 +234,20 @@ def run_b200(args):
     value = blends_total * args.steps / (ms / 1e3)
 
     # ---- end to end through the C ABI with page-locked host buffers: upload + fit + download (+ gather)
+    # The public call (BlendBatch.fit_host) pipelines upload / loop / download chunk by chunk when the batch is split
+    # into independently driven chunks; the device-resident number above is best with one handle, so the end-to-end
+    # leg gets its own batch of the same blends with --e2e-streams chunks.
     cudart = torch.cuda.cudart()
-    res = bb._dev.alloc_results(MAX_ITER, morph=True)
-    for a in list(bb.host.values()) + list(res.values()):
+    bbe = bb
+    if args.e2e_streams != args.streams:
+        bbe = BlendBatch(data["images"], psfs, data["model_psf"], data["centers"], data["bg_rms"],
+                         weights=data["weights"], streams=args.e2e_streams)
+    res = bbe._dev.alloc_results(MAX_ITER, morph=True)
+    for a in list(bbe.host.values()) + list(res.values()):
         if isinstance(a, np.ndarray) and a.nbytes >= 4096:
             cudart.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
     def e2e_step():
-        bb.upload()
-        bb.fit_device(MAX_ITER, E_REL, check_every=args.check_every)
-        o = bb.download(morph=True, out=res)
+        _, o = bbe.fit_host(MAX_ITER, E_REL, check_every=args.check_every, out=res, morph=True)
         # per-blend result records gathered over NCCL (north_star: NCCL only for results)
         return shard.gather_records(shard.result_records(o, comp_off))
     e2e_step()
@@ -252,8 +257,11 @@ def run_b200(args):
         e2e_step()
     barrier()
     e2e_s = allmax(time.perf_counter() - t0)
-    e2e = dict(value=blends_total * args.steps / e2e_s, unit=UNIT, h2d_bytes_per_step=int(allsum(float(bb.h2d_bytes))),
-               d2h_bytes_per_step=int(allsum(float(bb.d2h_bytes))), ms_per_step=e2e_s * 1e3 / args.steps)
+    e2e = dict(value=blends_total * args.steps / e2e_s, unit=UNIT, h2d_bytes_per_step=int(allsum(float(bbe.h2d_bytes))),
+               d2h_bytes_per_step=int(allsum(float(bbe.d2h_bytes))), ms_per_step=e2e_s * 1e3 / args.steps,
+               streams_per_gpu=args.e2e_streams)
+    if bbe is not bb:
+        bbe.close()
 
     # ---- roofline of each kernel: fixed-iteration pass (e_rel = 0: every blend active in every launch)
     # (chunked batch: one chunk after another, so a "launch" below is the chunk launches of one iteration together)
@@ -565,6 +573,8 @@ def main():
     ap.add_argument("--blends", type=int, default=10000, help="blends per GPU")
     ap.add_argument("--check-every", type=int, default=8)
     ap.add_argument("--streams", type=int, default=1, help="independently driven chunks per GPU (BlendBatch streams=)")
+    ap.add_argument("--e2e-streams", type=int, default=4,
+                    help="chunks per GPU of the end-to-end leg (upload / loop / download pipelined chunk by chunk)")
     ap.add_argument("--roofline-iters", type=int, default=40)
     ap.add_argument("--ref-per-worker", type=int, default=24)
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")

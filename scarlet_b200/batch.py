@@ -8,6 +8,8 @@ and `fit` runs `Blend.fit` for all blends in one launch sequence through the C A
 """
 from concurrent.futures import ThreadPoolExecutor
 
+import threading
+
 import numpy as np
 
 from . import _native, fft
@@ -87,6 +89,30 @@ class _Chunks:
         return dict(device_ms=agg(r["device_ms"] for r in infos), steps=max(r["steps"] for r in infos),
                     kernel_ms=[sum(r["kernel_ms"][j] for r in infos) for j in range(4)],
                     launches=sum(r["launches"] for r in infos))
+
+    def run(self, host, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, out=None, morph=True):
+        """upload -> fit -> download of every chunk on its own host thread and stream, with the PCIe link handed from
+        chunk to chunk (one upload, one download at a time): a chunk iterates while the next one's inputs are still
+        arriving, and its results leave while later chunks still iterate.  Returns (info, out) like fit + download."""
+        if out is None:
+            out = self.alloc_results(max_iter, morph)
+        up, down = threading.Lock(), threading.Lock()
+
+        def one(i):
+            part = self.parts[i]
+            with up:
+                part.upload(**{k: v for k, v in self._slice(host, i).items() if k not in ("C", "Ny", "Nx")})
+            r = part.fit(max_iter, e_rel, approximate_L, check_every, False)
+            with down:
+                part.download(morph=morph, out=self._slice(out, i))
+            return r
+
+        infos = self._map(one)
+        self.max_iter = int(max_iter)
+        self.d2h_bytes = sum(p.d2h_bytes for p in self.parts)
+        return dict(device_ms=max(r["device_ms"] for r in infos), steps=max(r["steps"] for r in infos),
+                    kernel_ms=[sum(r["kernel_ms"][j] for r in infos) for j in range(4)],
+                    launches=sum(r["launches"] for r in infos)), out
 
     def constrain(self):
         self._map(lambda i: self.parts[i].constrain())
@@ -290,12 +316,20 @@ class BlendBatch:
         """Bring the snapshot back (stream-ordered device-to-device copy)."""
         self._dev.restore()
 
+    def fit_host(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, out=None, morph=True):
+        """Host state -> device, the loop, results -> host arrays (`out` as from `alloc_results`, e.g. page-locked);
+        a chunked batch (`streams > 1`) pipelines the three steps chunk by chunk (`_Chunks.run`).  Returns (info, out);
+        `self.host` is left untouched (see `fit`)."""
+        if isinstance(self._dev, _Chunks):
+            return self._dev.run(self.host, max_iter, e_rel, approximate_L, check_every, out, morph)
+        self.upload()
+        info = self.fit_device(max_iter, e_rel, approximate_L, check_every)
+        return info, self.download(morph=morph, out=out)
+
     def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8):
         """`Blend.fit` for every blend: upload host state, run, read the results back into `self.host`;
         appends the per-iteration losses to `self.mse[b]`."""
-        self.upload()
-        info = self.fit_device(max_iter, e_rel, approximate_L, check_every)
-        out = self.download()
+        info, out = self.fit_host(max_iter, e_rel, approximate_L, check_every)
         for b in range(self.B):
             n = int(out["n_iter"][b])
             self.mse[b].extend(float(v) for v in out["logL"][b, :n])
