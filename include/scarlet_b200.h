@@ -40,6 +40,10 @@ extern "C" {
 int scl_version(void);
 const char* scl_last_error(void);
 int scl_device_count(void);
+/* The CUDA device of the calling host thread (cudaGetDevice / cudaSetDevice).  The device is a per-thread setting:
+ * a host thread that drives a batch created by another thread must select that thread's device first. */
+int scl_device_get(int* device);
+int scl_device_set(int device);
 /* A CUDA stream for the `void* stream` arguments below (for callers without their own CUDA binding, e.g. ctypes).
  * Blocking flavour: ordered against the legacy default stream, so events recorded there bracket its work. */
 int scl_stream_create(void** stream);

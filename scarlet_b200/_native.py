@@ -74,6 +74,18 @@ def require_device():
         raise RuntimeError("scarlet_b200 needs a CUDA device (no CPU fallback)")
 
 
+def device_get():
+    """CUDA device of the calling host thread."""
+    d = c_int(0)
+    _check(lib().scl_device_get(ctypes.byref(d)))
+    return d.value
+
+
+def device_set(device):
+    """Select the CUDA device of the calling host thread (worker threads start on device 0)."""
+    _check(lib().scl_device_set(int(device)))
+
+
 def stream_create():
     """A CUDA stream handle (int) for the `stream=` arguments of this module."""
     s = c_void_p()

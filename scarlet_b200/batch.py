@@ -40,7 +40,8 @@ class _Chunks:
         self._psf_slices = {}
         self.streams = [_native.stream_create() for _ in range(len(self.bounds) - 1)]
         self.parts = [_native.Batch(stream=s, **self._slice(host, i)) for i, s in enumerate(self.streams)]
-        self.pool = ThreadPoolExecutor(len(self.parts))
+        # the CUDA device is a per-thread setting: the worker threads adopt the device of the thread that built the batch
+        self.pool = ThreadPoolExecutor(len(self.parts), initializer=_native.device_set, initargs=(_native.device_get(),))
         self.B, self.K = B, int(off[-1])
         self.max_iter = 0
         self.d2h_bytes = 0

@@ -235,6 +235,15 @@ int scl_device_count(void) {
     return n;
 }
 
+int scl_device_get(int* device) {
+    if (!device) return fail(SCL_E_ARG, "null device pointer%s%s");
+    CK(cudaGetDevice(device));
+    return SCL_OK;
+}
+int scl_device_set(int device) {
+    CK(cudaSetDevice(device));
+    return SCL_OK;
+}
 int scl_stream_create(void** stream) {
     if (!stream) return fail(SCL_E_ARG, "null stream pointer%s%s");
     cudaStream_t s;

@@ -265,3 +265,28 @@ def test_per_blend_psfs_matched_inside_the_batch():
         bl.fit(12, 0.0)
         assert_allclose(bb.last["logL"][i], np.array(bl.mse, dtype=np.float64), rtol=20 * REL)
     bb.close()
+
+
+def test_chunked_batch_on_second_device():
+    """The chunk worker threads adopt the device of the thread that built the batch (the CUDA device is a per-thread
+    setting; rank r of a multi-GPU job runs on cuda:r).  Needs two GPUs; runs in a fresh process because the
+    library keeps its tables on the first device it is used on (one process per GPU)."""
+    import subprocess
+    import sys
+    from scarlet_b200 import _native
+    if _native.lib().scl_device_count() < 2:
+        pytest.skip("needs two GPUs")
+    code = (
+        "import numpy as np\n"
+        "from scarlet_b200 import _native, synth\n"
+        "from scarlet_b200.batch import BlendBatch\n"
+        "_native.device_set(1)\n"
+        "d = synth.make_blends(range(9), device='cpu')\n"
+        "a = (d['images'], d['psfs'], d['model_psf'], d['centers'], d['bg_rms'])\n"
+        "one = BlendBatch(*a, weights=d['weights']); many = BlendBatch(*a, weights=d['weights'], streams=3)\n"
+        "one.fit(10, 0.0); many.fit(10, 0.0)\n"
+        "assert np.array_equal(one.last['morph'], many.last['morph']) and np.array_equal(one.last['logL'], many.last['logL'])\n"
+        "print('ok')\n")
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=600,
+                       cwd=helpers.ROOT if hasattr(helpers, "ROOT") else None)
+    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stderr[-2000:]
