@@ -120,6 +120,23 @@ int scl_threshold_f32(float* x, int n, int Ny, int Nx, int apply, double* thresh
  * tap sits at window offset (y0, x0).  x, out float32 [n][Ny][Nx]. */
 int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const double* ky, const int32_t* y0, int Ly,
                      const double* kx, const int32_t* x0, int Lx, void* stream);
+/* No counterpart in the reference: added for callers that may not allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * scl_prox_symmetry_f32 on caller-owned DEVICE arrays, stream-ordered, no host<->device copy, no synchronisation and no
+ * cudaMalloc / cudaFree / allocating library call: the working copies and the contraction scratch live in one
+ * file-scope `static __device__` array of SCL_NOALLOC_MAX_BYTES that every GPU which loads the library holds until
+ * exit.  x_dev float32 [n][Ny][Nx] in place; centers_dev int32 [n][2] ((-1,-1) = whole array); shifts_dev float64
+ * [n][2] (mode 0 only, else may be NULL); modes as scl_prox_symmetry_f32.  An image whose centre lies outside the
+ * frame is left untouched and n_bad_dev (device int32, may be NULL; the caller zeroes it) is incremented -- the host
+ * cannot validate device-resident centres without a copy.  Returns SCL_E_LIMIT when
+ *   4 * (8256 + n * (roundup4(Ny*Nx + 8*Nx + 16) + roundup4(Ny*roundup4(Nx) + 16))) > SCL_NOALLOC_MAX_BYTES
+ * (e.g. up to 479 images of 64x64, 24 of 300x280, one of 1024x1024).  The first call on a device looks up the array's
+ * device address (cudaGetSymbolAddress) and copies two small tables into it: make that call once outside any capture.
+ * Every call shares the one array, which keeps the previous call's contents (the kernel re-initialises what it
+ * reads): calls that may overlap on the GPU -- different streams, or several host threads -- race; serialise them. */
+#define SCL_NOALLOC_MAX_BYTES (16u << 20)
+int scl_prox_symmetry_noalloc_f32(float* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev,
+                                  const double* shifts_dev, int mode, float strength, int32_t* n_bad_dev, void* stream);
 /* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
  * exported for symbol parity, returns SCL_E_LIMIT. */
 int scl_apply_filter_f32(void);

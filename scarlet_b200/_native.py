@@ -270,6 +270,19 @@ def prox_symmetry(x, centers, shifts=None, mode="kspace", strength=1.0):
     return x
 
 
+def prox_symmetry_noalloc(x_ptr, n, Ny, Nx, centers_ptr, shifts_ptr=None, mode="kspace", strength=1.0, n_bad_ptr=None,
+                          stream=None):
+    """scl_prox_symmetry_noalloc_f32: prox_symmetry on caller-owned DEVICE arrays given as integer addresses (e.g.
+    torch `tensor.data_ptr()`): x float32 [n, Ny, Nx] in place, centers int32 [n, 2], shifts float64 [n, 2], n_bad
+    int32 [1] (zeroed by the caller).  Stream-ordered, no copies, no device allocation: scratch is a static device
+    array of 16 MiB (NotImplementedError beyond it).  No counterpart in the reference (include/scarlet_b200.h)."""
+    require_device()
+    m = {"kspace": 0, "soft": 1, "sdss": 2}[mode]
+    _check(lib().scl_prox_symmetry_noalloc_f32(c_void_p(x_ptr), int(n), int(Ny), int(Nx), c_void_p(centers_ptr),
+                                               c_void_p(shifts_ptr), m, c_float(strength), c_void_p(n_bad_ptr),
+                                               c_void_p(stream)))
+
+
 def measure(x, centers, psf=None, do_max=True, do_centroid=True):
     """max_pixel and/or psf_weighted_centroid for x [n, Ny, Nx] float32.
     Returns (centers int32 [n,2], shifts float64 [n,2])."""

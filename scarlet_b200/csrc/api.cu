@@ -568,3 +568,4 @@ int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const do
 }
 
 #include "api_batch.inc"
+#include "api_noalloc.inc"
