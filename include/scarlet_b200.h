@@ -137,9 +137,30 @@ int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const do
 #define SCL_NOALLOC_MAX_BYTES (16u << 20)
 int scl_prox_symmetry_noalloc_f32(float* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev,
                                   const double* shifts_dev, int mode, float strength, int32_t* n_bad_dev, void* stream);
-/* operators_pybind11.apply_filter (operators_pybind11.cc:52-70) has no caller in the reference;
- * exported for symbol parity, returns SCL_E_LIMIT. */
-int scl_apply_filter_f32(void);
+/* ---- the reference's native module, entry for entry, on the CALLER's tables -------------------------------------
+ * operators_pybind11.prox_weighted_monotonic(flat_img, step, weights, offsets, dist_idx, thresh)
+ * (operators_pybind11.cc:27-50,82-85; caller operator.py:32-37): x [N] in place; weights [n_taps][N] row-major in x's
+ * type (the pybind layer casts the caller's table to it, operators_pybind11.cc:82-85); offsets int32 [n_taps <= 8];
+ * dist_idx int32 [M], walked in the given order: x[d] = min(x[d], (1 - thresh) * sum_{i: w[i,d] > 0} x[d + off[i]] w[i,d]),
+ * accumulated in tap order in x's type.  Unlike the C++ (no bounds checks) an index that leaves the image is SCL_E_ARG. */
+int scl_pb_prox_weighted_monotonic_f32(float* x, long long N, const float* weights, const int32_t* offsets, int n_taps,
+                                       const int32_t* dist_idx, long long M, float thresh, void* stream);
+int scl_pb_prox_weighted_monotonic_f64(double* x, long long N, const double* weights, const int32_t* offsets, int n_taps,
+                                       const int32_t* dist_idx, long long M, double thresh, void* stream);
+/* operators_pybind11.prox_monotonic(X, step, ref_idx, dist_idx, thresh) (operators_pybind11.cc:11-25; caller
+ * operator.py:24-29): x[d] = min(x[d], x[ref_idx[d]] * (1 - thresh)) for d in dist_idx, float64 only. */
+int scl_pb_prox_monotonic_f64(double* x, long long N, const int32_t* ref_idx, long long n_ref, const int32_t* dist_idx,
+                              long long M, double thresh, void* stream);
+/* operators_pybind11.apply_filter(image, values, y_start, y_end, x_start, x_end, result) (operators_pybind11.cc:52-70;
+ * no caller in the reference): result = sum_n values[n] * image[y_end[n] : y_end[n] + r_n, x_end[n] : x_end[n] + c_n]
+ * added into result[y_start[n] : y_start[n] + r_n, x_start[n] : x_start[n] + c_n], r_n = rows - y_start[n] - y_end[n],
+ * c_n likewise; image / result [rows][cols] row-major. */
+int scl_apply_filter_f32(const float* image, int rows, int cols, const float* values, const int32_t* y_start,
+                         const int32_t* y_end, const int32_t* x_start, const int32_t* x_end, int n, float* result,
+                         void* stream);
+int scl_apply_filter_f64(const double* image, int rows, int cols, const double* values, const int32_t* y_start,
+                         const int32_t* y_end, const int32_t* x_start, const int32_t* x_end, int n, double* result,
+                         void* stream);
 
 /* ---- Blend.fit on a batch of independent blends ------------------------------------ */
 typedef struct scl_batch scl_batch;
@@ -198,7 +219,40 @@ typedef struct {
     const float* psf_obs;           /* [psf_sets][P][psf_ky][psf_kx] or NULL */
     const float* psf_model;         /* [psf_model_sets][psf_kym][psf_kxm] */
     int32_t psf_sets, psf_model_sets, psf_ky, psf_kx, psf_kym, psf_kxm;
+    /* Declared schedules: a component flagged SCL_SCHEDULE runs, instead of the built-in
+     * PointSource.update, the ordered list of scarlet.update / scarlet.measurement calls its source's own update()
+     * makes: sched_ops [Ktot][16] int32 op codes (SCL_OP_*, 0 ends the list), sched_args [Ktot][16] float32 (the
+     * op's parameter).  Either pointer NULL = no scheduled component.  Such batches run in scene mode. */
+    const int32_t* sched_ops;
+    const float* sched_args;
+    /* Priors (component.py:39-67,177-187) of the affine form grad_sed = a_s sed + b_s, grad_morph = a_m morph + b_m:
+     * prior_par float32 [Ktot][4] = (a_s, a_m, L_sed, L_morph), L_sed < 0 = the component has no prior;
+     * prior_b_sed float32 [Ktot][C]; prior_idx int32 [Ktot] row of prior_b_morph float32 [n_prior_morph][Ny*Nx]
+     * (-1 = b_m = 0).  prior_par == NULL = no priors.  Such batches run in scene mode. */
+    const float* prior_par;
+    const float* prior_b_sed;
+    const int32_t* prior_idx;
+    const float* prior_b_morph;
+    int32_t n_prior_morph;
 } scl_batch_desc;
+
+/* op codes of a declared schedule (reference file:line of each in csrc/k_prox.cu) */
+#define SCL_SCHEDULE 128u
+#define SCL_SCHED_OPS 16
+#define SCL_OP_POSITIVE_SED 1
+#define SCL_OP_POSITIVE_MORPH 2
+#define SCL_OP_NORM_SED 3
+#define SCL_OP_NORM_MORPH 4
+#define SCL_OP_NORM_MORPH_MAX 5
+#define SCL_OP_SPARSE_L0 6
+#define SCL_OP_SPARSE_L1 7
+#define SCL_OP_THRESHOLD 8
+#define SCL_OP_MONOTONIC 9
+#define SCL_OP_SYM_KSPACE 10
+#define SCL_OP_SYM_SOFT 11
+#define SCL_OP_SYM_SDSS 12
+#define SCL_OP_MAX_PIXEL 13
+#define SCL_OP_CENTROID 14
 
 /* Allocate device state for `desc`'s sizes and upload it. */
 int scl_batch_create(const scl_batch_desc* desc, scl_batch** out, void* stream);
@@ -248,7 +302,54 @@ int scl_batch_render_components(scl_batch* batch, int k0, int nk, float* out, vo
  * CTAs: 0 gradient step, 1 centre + symmetry, 2 level list, 3 monotonic sweep, 4 normalise/write-back) to a device
  * counter; the call returns the sums so far in out8 (may be NULL) and clears them. */
 int scl_batch_phase_clocks(scl_batch* batch, int enable, unsigned long long* out8);
+/* Test switches (no counterpart in the reference).  bit 0: the scene-mode monotonic sweep visits every level instead of
+ * stopping at the first three consecutive levels without a positive pixel (the results are bit-identical; the
+ * tests compare the two).  bit 1: scene mode forms S S^T by the dense tiled contraction instead of per pair of
+ * overlapping footprint boxes (same products; the sums differ in their last bits). */
+int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
+
+/* ---- Blend.fit in float64 (compatibility path) -----------------------------------------------------------------------
+ * The reference's own loop tests build Frame(dtype=float64) (tests/test_blend.py:59-63,79-83,100-104).  One blend per
+ * call, host arrays in and out, every step of blend.py:79-102 as a plain float64 kernel (csrc/k_f64.cu); the
+ * difference-kernel convolution is the direct real-space sum the reference's zero-padded FFT product equals
+ * (fft.py:264-317).  Same flags, planes and schedules as scl_batch_desc; no low-resolution planes. */
+typedef struct {
+    int32_t n_comp, C, Ny, Nx;
+    const double* sed;              /* [K][C] */
+    const double* morph;            /* [K][Ny*Nx] */
+    const uint32_t* cflags;         /* [K] SCL_* flags */
+    const int32_t* center;          /* [K][2] */
+    const double* shift;            /* [K][2] */
+    const int32_t* conv;            /* [K] BlendFlag bits */
+    const int32_t* src_first;       /* [K] or NULL (SCL_SHARED_CENTER components) */
+    int32_t n_planes;               /* P <= 8 image planes (bands of all observations stacked) */
+    const int32_t* plane_band;      /* [P] */
+    int32_t n_obs;
+    const double* images;           /* [P][Ny*Nx] */
+    const double* weights;          /* [P][Ny*Nx] or NULL */
+    const int32_t* ker_on;          /* [P] 0 = identical PSFs (observation.py:191-194) */
+    const double* kernels;          /* [P][ky][kx] truncated real-space difference kernels (Observation._diff_kernels) */
+    int32_t ky, kx;
+    int32_t offy, offx;             /* kernel tap (j, i) acts at displacement (j + offy, i + offx):
+                                     * off = (F - k + 1) / 2 - F / 2 with F the reference's FFT length (fft.py:60-65,87-106) */
+    const double* cw;               /* [ph][pw] centroid weights (source.py:389-397) or NULL */
+    int32_t ph, pw;
+    int32_t it0;                    /* Blend.it before this fit */
+    double prev_loss;               /* mse[-1] before this fit */
+} scl_fit64_desc;
+/* Blend.fit(max_iter, e_rel, approximate_L) (blend.py:65-102).  Outputs (any may be NULL except n_iter): final sed / morph /
+ * center / shift / conv, n_iter = iterations run, converged, logL [max_iter] (n_iter valid), lipschitz [2]. */
+int scl_fit_f64(const scl_fit64_desc* desc, int max_iter, double e_rel, int approximate_L, double* sed, double* morph,
+                int32_t* center, double* shift, int32_t* conv, int32_t* n_iter, int32_t* converged, double* logL,
+                double* lipschitz, void* stream);
+/* The constraint pass every source runs once at construction (`self.update()` with it = 0, source.py:400,492) in
+ * float64, for the components of desc (images / weights / kernels are not read and may be NULL; n_planes >= 1). */
+int scl_constrain_f64(const scl_fit64_desc* desc, double* sed, double* morph, int32_t* center, double* shift, void* stream);
+/* Observation.render (observation.py:203-220) in float64: model / out [n][C][Ny][Nx], kernels [C][ky][kx] with the
+ * placement (offy, offx) of scl_fit64_desc; adjoint != 0 applies the transpose. */
+int scl_convolve_f64(const double* model, double* out, int n, int C, int Ny, int Nx, const double* kernels, int ky, int kx,
+                     int offy, int offx, int adjoint, void* stream);
 
 #ifdef __cplusplus
 }

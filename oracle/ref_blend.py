@@ -138,6 +138,18 @@ class Component:
         return self
 
 
+class Prior:
+    """component.py:39-67: gradient and Lipschitz callbacks evaluated on the component's parameters."""
+
+    def __init__(self, grad_func, L_func):
+        self._grad_func, self._L_func = grad_func, L_func
+        self.sed_grad = self.morph_grad = 0
+
+    def compute_grad(self, component):
+        self.sed_grad, self.morph_grad = self._grad_func(component.sed, component.morph)
+        self.L_sed, self.L_morph = self._L_func(component.sed, component.morph)
+
+
 def _it(node):
     return 0 if node.parent is None else node.parent.it
 
@@ -456,10 +468,21 @@ class Blend:
         sg, mg = self.backward()
         self.L_sed, self.L_morph = self.set_lipschitz(approximate_L)
         for k, c in enumerate(self.components):
+            c.L_sed, c.L_morph = self.L_sed, self.L_morph          # blend.py:88-89
+            sgk, mgk = sg[k], mg[k]
+            prior = getattr(c, "prior", None)
+            if prior is not None:                                  # Component.backward_prior, component.py:177-187
+                prior.compute_grad(c)
+                if not c.fix_morph:
+                    mgk = mgk + prior.morph_grad
+                    c.L_morph = c.L_morph + prior.L_morph
+                if not c.fix_sed:
+                    sgk = sgk + prior.sed_grad
+                    c.L_sed = c.L_sed + prior.L_sed
             if not c.fix_sed:
-                c.sed = c.sed - (1 / self.L_sed) * sg[k]
+                c.sed = c.sed - (1 / c.L_sed) * sgk
             if not c.fix_morph:
-                c.morph = c.morph - (1 / self.L_morph) * mg[k]
+                c.morph = c.morph - (1 / c.L_morph) * mgk
         for s in self.sources:
             s.update()
         return self.check_convergence(e_rel)

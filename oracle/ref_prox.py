@@ -350,3 +350,42 @@ def normalized(sed, morph, type="morph_max"):
         morph[:] = morph / norm
     else:
         raise ValueError("Unrecognized normalization '{0}'".format(type))
+
+
+# --------------------------------------------------------------------------
+# constraints the reference exports for custom update() schedules (update.py:71-103)
+# --------------------------------------------------------------------------
+def prox_hard(X, step, thresh=0):
+    """proxmin.operators.prox_hard (third-party, absent; proxmin 0.6 operators.py: X[|X| < thresh * step] = 0),
+    pinned by the reference's tests/test_update.py:74-86; caller update.sparse_l0 (update.py:71-75)."""
+    X[np.abs(X) < thresh * step] = 0
+    return X
+
+
+def prox_soft(X, step, thresh=0):
+    """proxmin.operators.prox_soft: sign(X) * max(|X| - thresh * step, 0); pinned by tests/test_update.py:88-97;
+    caller update.sparse_l1 (update.py:78-82)."""
+    X[:] = np.sign(X) * np.maximum(np.abs(X) - thresh * step, 0)
+    return X
+
+
+def threshold(morph):
+    """measurement.threshold (measurement.py:96-113): cut at the last empty bin of the log10 histogram."""
+    _morph = morph[morph > 0]
+    _bins = 50
+    if _morph.size < 500:
+        _bins = max(int(_morph.size / 10), 1)
+        if _bins == 1:
+            return 0, _bins
+    hist, bins = np.histogram(np.log10(_morph).reshape(-1), _bins)
+    cutoff = np.where(hist == 0)[0]
+    if len(cutoff) == 0:
+        return 0, _bins
+    return 10 ** bins[cutoff[-1]], _bins
+
+
+def update_threshold(morph):
+    """update.threshold (update.py:85-103) without the bounding box: pixels below the cut are zeroed."""
+    thresh, _ = threshold(morph)
+    morph[morph < thresh] = 0
+    return morph

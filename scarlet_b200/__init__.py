@@ -6,9 +6,10 @@ All array work dispatches to hand-written sm_100a CUDA kernels through the C ABI
 libscarlet_b200.so; there is no CPU fallback.
 """
 from . import _native  # noqa: F401
-from . import fft, psf, operator, update, measurement, bbox  # noqa: F401
+from . import fft, psf, operator, update, measurement, bbox, operators_pybind11  # noqa: F401
 from .observation import Frame, Observation, LowResObservation  # noqa: F401
-from .component import Component, ComponentTree, BlendFlag, Prior  # noqa: F401
+from .component import Component, ComponentTree, BlendFlag, Prior, AffinePrior  # noqa: F401
+from . import schedule  # noqa: F401
 from .source import (PointSource, ExtendedSource, MultiComponentSource, CombinedExtendedSource,  # noqa: F401
                      RandomSource, SourceInitError, extended_sources)
 from .blend import Blend, fit_many  # noqa: F401

@@ -14,7 +14,8 @@ LIB_PATH = os.environ.get("SCL_LIB") or os.path.join(_HERE, "lib", "libscarlet_b
 FFT_EDGE = 128
 SPEC_COLS = 65
 
-F_SYMMETRIC, F_MONOTONIC, F_FIX_SED, F_FIX_MORPH, F_KSPACE, F_CONSTRAINED, F_SHARED_CENTER = 1, 2, 4, 8, 16, 32, 64
+F_SYMMETRIC, F_MONOTONIC, F_FIX_SED, F_FIX_MORPH, F_KSPACE, F_CONSTRAINED, F_SHARED_CENTER, F_SCHEDULE = 1, 2, 4, 8, 16, 32, 64, 128
+SCHED_OPS = 16      # entries of a declared schedule (include/scarlet_b200.h: SCL_SCHED_OPS)
 
 _lib = None
 _lock = threading.Lock()
@@ -40,6 +41,9 @@ class BatchDesc(ctypes.Structure):
         ("psf_obs", c_void_p), ("psf_model", c_void_p),
         ("psf_sets", ctypes.c_int32), ("psf_model_sets", ctypes.c_int32), ("psf_ky", ctypes.c_int32),
         ("psf_kx", ctypes.c_int32), ("psf_kym", ctypes.c_int32), ("psf_kxm", ctypes.c_int32),
+        ("sched_ops", c_void_p), ("sched_args", c_void_p),
+        ("prior_par", c_void_p), ("prior_b_sed", c_void_p), ("prior_idx", c_void_p), ("prior_b_morph", c_void_p),
+        ("n_prior_morph", ctypes.c_int32),
     ]
 
 
@@ -139,10 +143,11 @@ _registered = set()
 def monotonic_tables(Ny, Nx):
     """Build (once per shape) and register the monotonicity tables with the CUDA library."""
     key = (int(Ny), int(Nx))
-    if key not in _registered:
+    dkey = (device_get(),) + key            # the library keeps its tables per CUDA device
+    if dkey not in _registered:
         wtab, ctab = monotonic_tables_host(Ny, Nx)
         _check(lib().scl_set_monotonic_tables(c_int(Ny), c_int(Nx), _p(wtab), _p(ctab)))
-        _registered.add(key)
+        _registered.add(dkey)
     return _tables[key]
 
 
@@ -234,9 +239,21 @@ def _centers(centers, n):
     return c
 
 
+def _inplace_stack(x, name, dtypes):
+    """The in-place operators write through x's buffer: a sliced or transposed view would be read and written with
+    the wrong strides."""
+    if not isinstance(x, np.ndarray) or x.ndim != 3:
+        raise TypeError("%s: a [n, Ny, Nx] numpy array expected" % name)
+    if x.dtype not in dtypes:
+        raise TypeError("%s: %s arrays only" % (name, " or ".join(np.dtype(d).name for d in dtypes)))
+    if not x.flags.c_contiguous:
+        raise TypeError("%s: C-contiguous arrays only (the operator works in place)" % name)
+
+
 def prox_weighted_monotonic(x, centers, thresh=0.0):
     """In place on x [n, Ny, Nx] (float32 or float64, C-contiguous)."""
     require_device()
+    _inplace_stack(x, "prox_weighted_monotonic", (np.float32, np.float64))
     n, Ny, Nx = x.shape
     monotonic_tables(Ny, Nx)
     c = _centers(centers, n)
@@ -251,8 +268,7 @@ def prox_weighted_monotonic(x, centers, thresh=0.0):
 
 def prox_monotonic_nearest(x, centers, thresh=0.0):
     require_device()
-    if x.dtype != np.float64:
-        raise TypeError("prox_monotonic: float64 arrays only")
+    _inplace_stack(x, "prox_monotonic", (np.float64,))
     n, Ny, Nx = x.shape
     monotonic_tables(Ny, Nx)
     _check(lib().scl_prox_monotonic_f64(_p(x), n, Ny, Nx, _p(_centers(centers, n)), c_double(thresh), None))
@@ -261,8 +277,7 @@ def prox_monotonic_nearest(x, centers, thresh=0.0):
 
 def prox_symmetry(x, centers, shifts=None, mode="kspace", strength=1.0):
     require_device()
-    if x.dtype != np.float32:
-        raise TypeError("prox_symmetry: float32 arrays only")
+    _inplace_stack(x, "prox_symmetry", (np.float32,))
     n, Ny, Nx = x.shape
     m = {"kspace": 0, "soft": 1, "sdss": 2}[mode]
     sh = None if shifts is None else np.ascontiguousarray(np.asarray(shifts, dtype=np.float64).reshape(n, 2))
@@ -401,6 +416,106 @@ def resample(x, ky, y0, kx, x0):
     return out
 
 
+class Fit64Desc(ctypes.Structure):
+    _fields_ = [
+        ("n_comp", ctypes.c_int32), ("C", ctypes.c_int32), ("Ny", ctypes.c_int32), ("Nx", ctypes.c_int32),
+        ("sed", c_void_p), ("morph", c_void_p), ("cflags", c_void_p), ("center", c_void_p), ("shift", c_void_p),
+        ("conv", c_void_p), ("src_first", c_void_p),
+        ("n_planes", ctypes.c_int32), ("plane_band", c_void_p), ("n_obs", ctypes.c_int32),
+        ("images", c_void_p), ("weights", c_void_p), ("ker_on", c_void_p), ("kernels", c_void_p),
+        ("ky", ctypes.c_int32), ("kx", ctypes.c_int32), ("offy", ctypes.c_int32), ("offx", ctypes.c_int32),
+        ("cw", c_void_p), ("ph", ctypes.c_int32), ("pw", ctypes.c_int32),
+        ("it0", ctypes.c_int32), ("prev_loss", c_double),
+    ]
+
+
+def kernel_offsets(ky, kx, Ny, Nx):
+    """Displacement of tap 0 of a ky x kx difference kernel on an Ny x Nx frame, as fft.convolve places it
+    (fft.py:60-65,87-106): tap (j, i) acts at (j + offy, i + offx)."""
+    Fy, Fx = conv_fft_shape(Ny, ky, False), conv_fft_shape(Nx, kx, True)
+    return (Fy - ky + 1) // 2 - Fy // 2, (Fx - kx + 1) // 2 - Fx // 2
+
+
+def _desc64(C, Ny, Nx, sed, morph, cflags, center, shift, conv, images, weights, plane_band, n_obs, kernels, ker_on,
+            cw, it0, prev_loss, src_first):
+    ca = np.ascontiguousarray
+    N = Ny * Nx
+    sed = ca(sed, dtype=np.float64)
+    K = len(sed)
+    plane_band = ca(plane_band, dtype=np.int32)
+    P = len(plane_band)
+    a = dict(sed=sed.reshape(K, C), morph=ca(morph, dtype=np.float64).reshape(K, N), cflags=ca(cflags, dtype=np.uint32).reshape(K),
+             center=ca(center, dtype=np.int32).reshape(K, 2), shift=ca(shift, dtype=np.float64).reshape(K, 2),
+             conv=ca(conv, dtype=np.int32).reshape(K), src_first=None if src_first is None else ca(src_first, dtype=np.int32),
+             plane_band=plane_band, images=None if images is None else ca(images, dtype=np.float64).reshape(P, N),
+             weights=None if weights is None else ca(weights, dtype=np.float64).reshape(P, N),
+             ker_on=ca(ker_on, dtype=np.int32).reshape(P),
+             kernels=None if kernels is None else ca(kernels, dtype=np.float64),
+             cw=None if cw is None else ca(cw, dtype=np.float64))
+    d = Fit64Desc()
+    d.n_comp, d.C, d.Ny, d.Nx, d.n_planes, d.n_obs = K, C, Ny, Nx, P, int(n_obs)
+    for name in ("sed", "morph", "cflags", "center", "shift", "conv", "src_first", "plane_band", "images", "weights",
+                 "ker_on", "kernels", "cw"):
+        setattr(d, name, _p(a[name]))
+    if a["kernels"] is not None:
+        assert a["kernels"].shape[0] == P
+        d.ky, d.kx = a["kernels"].shape[1:]
+        d.offy, d.offx = kernel_offsets(d.ky, d.kx, Ny, Nx)
+    if a["cw"] is not None:
+        d.ph, d.pw = a["cw"].shape
+    d.it0, d.prev_loss = int(it0), float(prev_loss)
+    return d, a, K
+
+
+def constrain_f64(C, Ny, Nx, sed, morph, cflags, center, shift, cw, src_first=None):
+    """scl_constrain_f64: the construction-time update() (it = 0) of float64 components; returns dict(sed, morph,
+    center, shift)."""
+    require_device()
+    monotonic_tables(Ny, Nx)
+    K = len(sed)
+    d, a, K = _desc64(C, Ny, Nx, sed, morph, cflags, center, shift, np.zeros(K, np.int32), None, None, np.arange(C), 1,
+                      None, np.zeros(C, np.int32), cw, 0, 0.0, src_first)
+    out = dict(sed=np.empty((K, C)), morph=np.empty((K, Ny, Nx)), center=np.empty((K, 2), np.int32), shift=np.empty((K, 2)))
+    _check(lib().scl_constrain_f64(ctypes.byref(d), _p(out["sed"]), _p(out["morph"]), _p(out["center"]), _p(out["shift"]),
+                                   None))
+    return out
+
+
+def fit_f64(C, Ny, Nx, sed, morph, cflags, center, shift, conv, images, weights, plane_band, n_obs, kernels, ker_on,
+            cw, it0=0, prev_loss=0.0, src_first=None, max_iter=200, e_rel=1e-2, approximate_L=False):
+    """scl_fit_f64: Blend.fit of ONE blend in float64 (include/scarlet_b200.h).  kernels [P, ky, kx] or None."""
+    require_device()
+    monotonic_tables(Ny, Nx)
+    d, a, K = _desc64(C, Ny, Nx, sed, morph, cflags, center, shift, conv, images, weights, plane_band, n_obs, kernels,
+                      ker_on, cw, it0, prev_loss, src_first)
+    out = dict(sed=np.empty((K, C)), morph=np.empty((K, Ny, Nx)), center=np.empty((K, 2), np.int32),
+               shift=np.empty((K, 2)), conv=np.empty(K, np.int32), logL=np.zeros(max(int(max_iter), 1)),
+               lipschitz=np.zeros(2))
+    n_iter, done = ctypes.c_int32(0), ctypes.c_int32(0)
+    _check(lib().scl_fit_f64(ctypes.byref(d), int(max_iter), c_double(e_rel), int(bool(approximate_L)), _p(out["sed"]),
+                             _p(out["morph"]), _p(out["center"]), _p(out["shift"]), _p(out["conv"]), ctypes.byref(n_iter),
+                             ctypes.byref(done), _p(out["logL"]), _p(out["lipschitz"]), None))
+    out["n_iter"], out["converged"] = n_iter.value, bool(done.value)
+    if n_iter.value == 0:
+        out["sed"], out["morph"] = a["sed"].copy(), a["morph"].reshape(K, Ny, Nx).copy()
+        out["center"], out["shift"], out["conv"] = a["center"].copy(), a["shift"].copy(), a["conv"].copy()
+    out["logL"] = out["logL"][:n_iter.value]
+    return out
+
+
+def convolve_f64(model, kernels, adjoint=False):
+    """Observation.render in float64: model [n, C, Ny, Nx], real-space difference kernels [C, ky, kx]."""
+    require_device()
+    model = np.ascontiguousarray(model, dtype=np.float64)
+    kernels = np.ascontiguousarray(kernels, dtype=np.float64)
+    n, C, Ny, Nx = model.shape
+    ky, kx = kernels.shape[1:]
+    offy, offx = kernel_offsets(ky, kx, Ny, Nx)
+    out = np.empty_like(model)
+    _check(lib().scl_convolve_f64(_p(model), _p(out), n, C, Ny, Nx, _p(kernels), ky, kx, offy, offx, int(adjoint), None))
+    return out
+
+
 # --------------------------------------------------------------------------- batch fit
 class Batch:
     """Device-resident state of B independent blends sharing one frame shape
@@ -408,7 +523,7 @@ class Batch:
 
     def __init__(self, C, Ny, Nx, comp_off, sed, morph, cflags, center, shift, conv, images, weights,
                  kernel_spec, ker_idx, cw, cw_idx, it0=None, prev_loss=None, src_first=None, stream=None,
-                 plane_band=None, n_obs=1, lr=None, ker_half=0, scene_mode=0, psfs=None):
+                 plane_band=None, n_obs=1, lr=None, ker_half=0, scene_mode=0, psfs=None, sched=None, prior=None):
         """psfs: dict(obs [S, P, ky, kx], model [1 or S, kym, kxm]) instead of kernel_spec (pass None there): the S * P
         difference kernels are matched on the device and their spectra stay there; ker_idx then indexes s * P + p.
         plane_band / n_obs: several observations per blend -- images, weights and ker_idx then hold the bands of
@@ -421,6 +536,9 @@ class Batch:
         # low-resolution observations; plane_band then lists the full-resolution planes first, these after
         self.lr = lr
         self.psfs = psfs
+        # sched: dict(ops int32 [K, 16], args float32 [K, 16]) for components flagged F_SCHEDULE; prior: dict(par [K, 4]
+        # = (a_sed, a_morph, L_sed, L_morph; L_sed < 0: none), b_sed [K, C], idx [K], b_morph [n, N]) (scarlet_b200.h)
+        self.sched, self.prior = sched, prior
         self.Plr = 0 if lr is None else int(np.shape(lr["images"])[1])
         self.P = self.C if plane_band is None else len(self.plane_band) - self.Plr
         self.n_obs = int(n_obs)
@@ -494,6 +612,19 @@ class Batch:
                 d.psf_obs, d.psf_model = _p(obs), _p(mod)
                 d.psf_sets, d.psf_model_sets = po[0], pm[0]
                 d.psf_ky, d.psf_kx, d.psf_kym, d.psf_kxm = po[2], po[3], pm[1], pm[2]
+        if self.sched is not None:
+            a["sched_ops"] = ca(self.sched["ops"], dtype=np.int32).reshape(K, SCHED_OPS)
+            a["sched_args"] = ca(self.sched["args"], dtype=np.float32).reshape(K, SCHED_OPS)
+            d.sched_ops, d.sched_args = _p(a["sched_ops"]), _p(a["sched_args"])
+        if self.prior is not None:
+            a["prior_par"] = ca(self.prior["par"], dtype=np.float32).reshape(K, 4)
+            a["prior_b_sed"] = ca(self.prior["b_sed"], dtype=np.float32).reshape(K, self.C)
+            a["prior_idx"] = ca(self.prior["idx"], dtype=np.int32).reshape(K)
+            bm = self.prior.get("b_morph")
+            a["prior_b_morph"] = None if bm is None or len(bm) == 0 else ca(bm, dtype=np.float32).reshape(-1, N)
+            d.prior_par, d.prior_b_sed, d.prior_idx = _p(a["prior_par"]), _p(a["prior_b_sed"]), _p(a["prior_idx"])
+            d.prior_b_morph = _p(a["prior_b_morph"])
+            d.n_prior_morph = 0 if a["prior_b_morph"] is None else len(a["prior_b_morph"])
         if a["cw"] is None:
             d.n_cw, d.ph, d.pw = 0, 0, 0
         else:
@@ -542,6 +673,10 @@ class Batch:
         out = (ctypes.c_ulonglong * 8)()
         _check(lib().scl_batch_phase_clocks(self._h, int(bool(enable)), out))
         return [int(v) for v in out]
+
+    def debug_flags(self, flags):
+        """Test switches (include/scarlet_b200.h: scl_batch_debug_flags)."""
+        _check(lib().scl_batch_debug_flags(self._h, int(flags)))
 
     def snapshot(self):
         _check(lib().scl_batch_snapshot(self._h, c_void_p(self.stream)))

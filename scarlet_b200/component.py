@@ -23,8 +23,8 @@ class BlendFlag(enum.Flag):
 
 
 class Prior():
-    """Differentiable prior hook (component.py:39-67).  Kept for API parity; `Blend.fit` rejects components with a
-    prior (a Python callback cannot run inside the CUDA loop)."""
+    """Differentiable prior hook (component.py:39-67).  A Python callback cannot run inside the CUDA loop: `Blend.fit`
+    accepts the priors whose gradient the device can evaluate itself (`AffinePrior`) and rejects any other."""
 
     def __init__(self, grad_func, L_func):
         self._grad_func, self._L_func = grad_func, L_func
@@ -34,6 +34,28 @@ class Prior():
         state = (component._sed, component._morph)
         self.sed_grad, self.morph_grad = self._grad_func(*state)
         self.L_sed, self.L_morph = self._L_func(*state)
+
+
+class AffinePrior(Prior):
+    """A prior whose gradient is affine in the parameter it acts on,
+
+        grad_sed = a_sed * sed + b_sed            grad_morph = a_morph * morph + b_morph,
+
+    which covers the quadratic penalties lambda/2 |x - x0|^2 (a = lambda, b = -lambda x0: Gaussian priors around a
+    template SED or morphology, Tikhonov damping with x0 = 0) and linear ones (a = 0: a constant pull, e.g. an L1
+    flux penalty on non-negative parameters).  `b_sed` [C] and `b_morph` [Ny, Nx] may be scalars.  The Lipschitz
+    constants of the two gradients default to |a|.  Additive to the reference (which only has the callback form,
+    component.py:39-67); the same object is a valid reference-style Prior -- `compute_grad` evaluates the same
+    expressions on the host -- and `Blend.fit` ships (a, b, L) to the device, where Component.backward_prior
+    (component.py:177-187) runs inside the gradient step of the constraint kernel."""
+
+    def __init__(self, a_sed=0., b_sed=0., a_morph=0., b_morph=0., L_sed=None, L_morph=None):
+        self.a_sed, self.a_morph = float(a_sed), float(a_morph)
+        self.b_sed, self.b_morph = b_sed, b_morph
+        self._L = (abs(self.a_sed) if L_sed is None else float(L_sed),
+                   abs(self.a_morph) if L_morph is None else float(L_morph))
+        Prior.__init__(self, lambda sed, morph: (self.a_sed * sed + self.b_sed, self.a_morph * morph + self.b_morph),
+                       lambda sed, morph: self._L)
 
 
 class _Node:

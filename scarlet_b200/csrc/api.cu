@@ -11,16 +11,18 @@
 #include "../../include/scarlet_b200.h"
 #include "k_forward.cu"
 #include "k_grad.cu"
+#include "k_update.cu"
 #include "k_prox.cu"
 #include "k_lowres.cu"
 #include "k_scene.cu"
 #include "k_psf.cu"
 #include "k_products.cu"
-#include "k_update.cu"
+#include "k_f64.cu"
 
 static_assert(SCL_FFT == SCL_FFT_EDGE && SCL_RS == SCL_SPEC_COLS, "header / kernel constants diverged");
 static_assert(SCL_F_SYMMETRIC == SCL_SYMMETRIC && SCL_F_MONOTONIC == SCL_MONOTONIC && SCL_F_FIX_SED == SCL_FIX_SED &&
-              SCL_F_FIX_MORPH == SCL_FIX_MORPH && SCL_F_KSPACE == SCL_KSPACE && SCL_F_CONSTRAINED == SCL_CONSTRAINED,
+              SCL_F_FIX_MORPH == SCL_FIX_MORPH && SCL_F_KSPACE == SCL_KSPACE && SCL_F_CONSTRAINED == SCL_CONSTRAINED &&
+              SCL_F_SCHEDULE == SCL_SCHEDULE && SCL_SCHED_MAX == SCL_SCHED_OPS,
               "flag constants diverged");
 
 namespace {
@@ -62,16 +64,33 @@ struct Tables {
     void release() { cudaFree(wtab); cudaFree(ctab); cudaFree(plist); cudaFree(pfirst); }
 };
 constexpr size_t kPlanBudget = (size_t)768 << 20;    // bytes of sweep plans per shape
-std::mutex g_mu;
-std::map<std::pair<int, int>, Tables> g_tables;
-int* g_nfl = nullptr;        // device [kNflN]
-int* g_nfl_even = nullptr;   // device [kNflN]
 constexpr int kNflN = 4096;
-bool g_attr_done = false;
+constexpr int kMaxDev = 64;
+// Everything the library keeps on a device between calls -- operator tables, next_fast_len tables, the kernels'
+// shared-memory opt-ins -- belongs to ONE device: the state is kept per CUDA device and looked up through the
+// calling thread's current device, so a process that switches devices (scl_device_set) gets that device's own copy.
+struct DevState {
+    std::map<std::pair<int, int>, Tables> tables;
+    int* nfl = nullptr;          // device [kNflN]
+    int* nfl_even = nullptr;     // device [kNflN]
+    bool attr_done = false;
+};
+std::mutex g_mu;
+DevState g_dev[kMaxDev];
+
+DevState* dev_state() {
+    int d = 0;
+    if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= kMaxDev) return nullptr;
+    return &g_dev[d];
+}
+int* cur_nfl() { DevState* st = dev_state(); return st ? st->nfl : nullptr; }
+int* cur_nfl_even() { DevState* st = dev_state(); return st ? st->nfl_even : nullptr; }
 
 int ensure_globals() {
+    DevState* st = dev_state();
+    if (!st) return fail(SCL_E_CUDA, "no current CUDA device (or device index above 63)%s%s");
     std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_nfl) {
+    if (!st->nfl) {
         std::vector<int> a(kNflN), b(kNflN);
         for (int n = 0; n < kNflN; n++) {
             a[n] = next_fast_len(n);
@@ -79,12 +98,15 @@ int ensure_globals() {
             while (e % 2 != 0) e = next_fast_len(e + 1);      // fft.py:103-105
             b[n] = e;
         }
-        CK(cudaMalloc(&g_nfl, kNflN * sizeof(int)));
-        CK(cudaMalloc(&g_nfl_even, kNflN * sizeof(int)));
-        CK(cudaMemcpy(g_nfl, a.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
-        CK(cudaMemcpy(g_nfl_even, b.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
+        int *pa = nullptr, *pb = nullptr;
+        CK(cudaMalloc(&pa, kNflN * sizeof(int)));
+        CK(cudaMalloc(&pb, kNflN * sizeof(int)));
+        CK(cudaMemcpy(pa, a.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(pb, b.data(), kNflN * sizeof(int), cudaMemcpyHostToDevice));
+        st->nfl = pa;
+        st->nfl_even = pb;
     }
-    if (!g_attr_done) {
+    if (!st->attr_done) {
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_forward_adjoint<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
         CK(cudaFuncSetAttribute(scl_k_convolve, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem));
@@ -94,12 +116,18 @@ int ensure_globals() {
         const int big = 200 * 1024;
         CK(cudaFuncSetAttribute(scl_k_prox, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_source_center, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        // scene-mode variants: symmetry tables only, but those pass 48 KB once an image edge reaches ~1480 pixels
+        CK(cudaFuncSetAttribute(scl_k_prox_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        CK(cudaFuncSetAttribute(scl_k_source_center_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_symmetry, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_measure, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_monotonic<float, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_monotonic<double, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
         CK(cudaFuncSetAttribute(scl_k_monotonic<double, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
-        g_attr_done = true;
+        // set once to the limit psf_prepare checks against (a per-call value raced between host threads)
+        CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        CK(cudaFuncSetAttribute(scl_k_mono_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, big));
+        st->attr_done = true;
     }
     return SCL_OK;
 }
@@ -130,7 +158,6 @@ int build_plans(int Ny, int Nx, Tables* t) {
     if (rows >= (1ull << (32 - pbits)) - 1) return SCL_OK;
     const int mx = Ny > Nx ? Ny : Nx;
     const size_t smem = scl_mono_work_bytes(N, 3 * mx) + (3 * mx + 3) * sizeof(int) + 16;
-    CK(cudaFuncSetAttribute(scl_k_mono_plan, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     DevBuf<unsigned> cnt;
     CK(cnt.alloc(N));
     scl_k_mono_plan<<<N, SCL_THREADS, smem>>>(Ny, Nx, pbits, cnt.p, nullptr, nullptr);
@@ -152,10 +179,12 @@ int build_plans(int Ny, int Nx, Tables* t) {
 }
 
 int get_tables(int Ny, int Nx, Tables* t) {
+    DevState* st = dev_state();
+    if (!st) return fail(SCL_E_CUDA, "no current CUDA device%s%s");
     std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_tables.find({Ny, Nx});
-    if (it == g_tables.end())
-        return fail(SCL_E_ARG, "no monotonic tables registered for this shape (call scl_set_monotonic_tables)%s%s");
+    auto it = st->tables.find({Ny, Nx});
+    if (it == st->tables.end())
+        return fail(SCL_E_ARG, "no monotonic tables registered for this shape on the current device (call scl_set_monotonic_tables)%s%s");
     *t = it->second;
     return SCL_OK;
 }
@@ -260,6 +289,8 @@ int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ct
     int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
     if (!wtab || !ctab) return fail(SCL_E_ARG, "null table%s%s");
+    if ((rc = ensure_globals())) return rc;
+    DevState* st = dev_state();
     size_t n = (size_t)(2 * Ny - 1) * (2 * Nx - 1) * 8;
     Tables t;
     CK(cudaMalloc(&t.wtab, 9 * n * sizeof(float)));
@@ -268,9 +299,9 @@ int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ct
     CK(cudaMemcpy(t.ctab, ctab, n * sizeof(double), cudaMemcpyHostToDevice));
     if ((rc = build_plans(Ny, Nx, &t))) { t.release(); return rc; }
     std::lock_guard<std::mutex> lk(g_mu);
-    auto it = g_tables.find({Ny, Nx});
-    if (it != g_tables.end()) it->second.release();
-    g_tables[{Ny, Nx}] = t;
+    auto it = st->tables.find({Ny, Nx});
+    if (it != st->tables.end()) it->second.release();
+    st->tables[{Ny, Nx}] = t;
     return SCL_OK;
 }
 
@@ -313,10 +344,10 @@ int scl_prox_symmetry_f32(float* x, int n, int Ny, int Nx, const int32_t* center
     if (big) {
         CK(dz.alloc((size_t)n * Ny * ((Nx + 3) & ~3) + 16));
         scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem_scene(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength,
-                                                                           g_nfl, g_nfl_even, dz.p);
+                                                                           cur_nfl(), cur_nfl_even(), dz.p);
     } else
-        scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, g_nfl,
-                                                                     g_nfl_even, nullptr);
+        scl_k_symmetry<<<n, SCL_PROX_THREADS, prox_smem(Ny, Nx), s>>>(dx.p, dc.p, ds.p, Ny, Nx, mode, strength, cur_nfl(),
+                                                                     cur_nfl_even(), nullptr);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(x, dx.p, n * N * sizeof(float), cudaMemcpyDeviceToHost, s));
     CK(cudaStreamSynchronize(s));
@@ -406,10 +437,6 @@ int scl_convolve_f32(const float* model, float* out, int n, int C, int Ny, int N
     return SCL_OK;
 }
 
-int scl_apply_filter_f32(void) {
-    return fail(SCL_E_LIMIT, "apply_filter has no caller in the reference (operators_pybind11.cc:52-70); not implemented%s%s");
-}
-
 }  // extern "C"
 
 int scl_lowres_render_f32(const float* model, float* out, int n, int C, int N, int n_lr, const float* op, void* stream) {
@@ -453,7 +480,6 @@ int psf_prepare(SclPsfArgs& a, int C, int ky, int kx, int kym, int kxm, int n_mo
     const SclPsfLayout L = scl_psf_layout(ky, kx, kym, kxm, a.Fy, a.Fx, a.oy, a.ox, SCL_PSF_THREADS / 32);
     *smem = L.total * sizeof(double);
     if (*smem > 227 * 1024) return fail(SCL_E_LIMIT, "PSF stamps too large for the shared-memory transform%s%s");
-    CK(cudaFuncSetAttribute(scl_k_match_psfs, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
     return SCL_OK;
 }
 
@@ -569,3 +595,5 @@ int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const do
 
 #include "api_batch.inc"
 #include "api_noalloc.inc"
+#include "api_pybind.inc"
+#include "api_f64.inc"

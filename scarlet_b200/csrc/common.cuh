@@ -23,6 +23,7 @@
 #define SCL_F_FIX_MORPH 8u       // skip the morphology gradient step (blend.py:94)
 #define SCL_F_KSPACE    16u      // component owner has a `.shift` -> k-space symmetry; else soft, strength 1
 #define SCL_F_CONSTRAINED 32u    // run max_pixel / positive / normalized (PointSource.update); plain Components: no-op
+#define SCL_F_SCHEDULE 128u      // the component runs a declared schedule (SclProxArgs::sched_ops) instead of the built-in one
 #define SCL_F_SHARED_CENTER 64u  // component of a multi-component source: centre + shift come from the source's
                                  // flux-weighted morphology (MultiComponentSource.update, source.py:605-627)
 

@@ -40,7 +40,36 @@ struct SclProxArgs {
     // symmetry tables stay in shared memory.  nullptr: everything in shared memory.
     float* xscratch;
     size_t xstride;
+    int no_early_exit;        // tests: run the scene-mode sweep over every level (scl_monotonic_hbm, exit_level)
+    // Declared schedules (components flagged SCL_F_SCHEDULE: a custom update() built from scarlet.update /
+    // scarlet.measurement calls, traced once on the host) and priors (component.py:39-67,177-187); both only in the
+    // wide (scene-mode) kernels, which a batch that uses either is routed to.
+    const int* sched_ops;     // [Ktot][SCL_SCHED_MAX] op codes, 0 ends the list
+    const float* sched_args;  // [Ktot][SCL_SCHED_MAX]
+    const float* prior_par;   // [Ktot][4] (a_sed, a_morph, L_sed, L_morph); nullptr: no prior in the batch
+    const float* prior_b_sed; // [Ktot][C]
+    const int* prior_idx;     // [Ktot] row of prior_b_morph, -1 = none
+    const float* prior_b_morph;   // [n][N]
 };
+
+#define SCL_SCHED_MAX 16
+#ifndef SCL_OP_POSITIVE_SED
+// op codes of a declared schedule (host mirror: scarlet_b200/schedule.py)
+#define SCL_OP_POSITIVE_SED 1      // update.positive_sed            update.py:13-17
+#define SCL_OP_POSITIVE_MORPH 2    // update.positive_morph          update.py:20-24
+#define SCL_OP_NORM_SED 3          // update.normalized('sed')       update.py:52-55
+#define SCL_OP_NORM_MORPH 4        // update.normalized('morph')     update.py:56-59
+#define SCL_OP_NORM_MORPH_MAX 5    // update.normalized('morph_max') update.py:60-63
+#define SCL_OP_SPARSE_L0 6         // update.sparse_l0(thresh)       update.py:71-75   arg = thresh
+#define SCL_OP_SPARSE_L1 7         // update.sparse_l1(thresh)       update.py:78-82   arg = thresh
+#define SCL_OP_THRESHOLD 8         // update.threshold               update.py:85-103
+#define SCL_OP_MONOTONIC 9         // update.monotonic(pixel_center, thresh)   update.py:106-156   arg = thresh
+#define SCL_OP_SYM_KSPACE 10       // update.symmetric(pixel_center, "kspace") with a `.shift`   update.py:170-199
+#define SCL_OP_SYM_SOFT 11         // ... "soft" (or kspace without a shift: strength 1)         arg = strength
+#define SCL_OP_SYM_SDSS 12         // ... "sdss"
+#define SCL_OP_MAX_PIXEL 13        // pixel_center = measurement.max_pixel(morph, pixel_center)  measurement.py:3-29
+#define SCL_OP_CENTROID 14         // pixel_center, shift = measurement.psf_weighted_centroid(...) measurement.py:32-94
+#endif
 
 // dynamic smem: X[N] + Z[N] + tab[3*(2*max(Ny,Nx)-1) + 2*Nx] floats
 // block: SCL_PROX_THREADS
@@ -48,10 +77,12 @@ struct SclProxArgs {
 // loops unroll without predicates and every load address is one 64-bit add):
 //   X[p] = S[p] - step_morph * sum_c A[c] G[c][p]   (S[p] if fixm),   dAc[c] += sum_p G[c][p] S[p]
 // Four pixels per thread and round: all their loads (S and CC bands of G) are issued before any use.
-template <int CC>
+// PRIOR: the prior's morphology gradient am * S + bm[p] is added to the likelihood's (component.py:181-183)
+template <int CC, bool PRIOR = false>
 __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, const float* __restrict__ Gb, float* X, int N,
                                               const float (&ak)[SCL_MAX_BANDS], float (&dAc)[SCL_MAX_BANDS],
-                                              bool fixm, float step_morph) {
+                                              bool fixm, float step_morph, float am = 0.f,
+                                              const float* __restrict__ bm = nullptr) {
     constexpr int PX = 4;
     const int nt = blockDim.x;
     int p0 = threadIdx.x;
@@ -72,6 +103,7 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
                 d += ak[c] * gv[u][c];
                 dAc[c] += gv[u][c] * sv[u];
             }
+            if (PRIOR) d += am * sv[u] + (bm ? bm[p0 + u * nt] : 0.f);
             X[p0 + u * nt] = fixm ? sv[u] : sv[u] - step_morph * d;
         }
     }
@@ -85,6 +117,7 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
             d += ak[c] * g[c];
             dAc[c] += g[c] * s;
         }
+        if (PRIOR) d += am * s + (bm ? bm[p0] : 0.f);
         X[p0] = fixm ? s : s - step_morph * d;
     }
 }
@@ -94,21 +127,38 @@ __device__ __forceinline__ void scl_step_loop(const float* __restrict__ Sin, con
 // and both gradient steps (blend.py:91-96): X = S[k] - (1/L_morph) dS, sAnew = A[k] - (1/L_sed) dA (honouring
 // fix_morph / fix_sed); sAold = A[k] as read.  Without G (construction-time pass) X = S[k], sAnew = A[k].  All
 // threads of the CTA; the caller synchronises before reading sAnew / sAold.
+// PRIOR (wide kernels only): Component.backward_prior (component.py:177-187) for priors of the affine form
+// grad_sed = a_s sed + b_s, grad_morph = a_m morph + b_m: the prior's gradients join the likelihood's and its
+// Lipschitz constants the blend's, per component and only for parameters that are not fixed.  step_out (optional,
+// shared): the component's step_morph = 1 / L_morph, which the sparsity operators scale their threshold with.
+template <bool PRIOR = false>
 __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, int b, unsigned fl, float* X,
-                                                   double (*sdA)[SCL_MAX_BANDS], float* sAnew, float* sAold) {
+                                                   double (*sdA)[SCL_MAX_BANDS], float* sAnew, float* sAold,
+                                                   float* step_out = nullptr) {
     const int N = a.Ny * a.Nx, C = a.C, P = a.pl.P;
     {
         const float* Sin = a.S + (size_t)k * N;
         if (a.G && !(SCL_EXP & 16)) {
             const bool fixm = fl & SCL_F_FIX_MORPH;
-            const float step_morph = 1.0f / a.lips[2 * b + 1];
+            float Lm = a.lips[2 * b + 1], Ls = a.lips[2 * b], a_s = 0.f, a_m = 0.f;
+            const float* bm = nullptr;
+            const bool has_prior = PRIOR && a.prior_par && a.prior_par[4 * k + 2] >= 0.f;
+            if (has_prior) {
+                a_s = a.prior_par[4 * k]; a_m = a.prior_par[4 * k + 1];
+                if (!(fl & SCL_F_FIX_SED)) Ls = Ls + a.prior_par[4 * k + 2];
+                if (!fixm) Lm = Lm + a.prior_par[4 * k + 3];
+                if (a.prior_idx[k] >= 0) bm = a.prior_b_morph + (size_t)a.prior_idx[k] * N;
+            }
+            const float step_morph = 1.0f / Lm;
+            if (step_out && threadIdx.x == 0) *step_out = step_morph;
             const float* Gb = a.G + (size_t)b * P * N;
             // per plane: the SED entry of the band it sees; dAc[p] = sum_px G_p S, folded per band below
             float ak[SCL_MAX_BANDS], dAc[SCL_MAX_BANDS];
 #pragma unroll
             for (int c = 0; c < SCL_MAX_BANDS; c++) { ak[c] = (c < P) ? a.A[(size_t)k * C + a.pl.band[c]] : 0.f; dAc[c] = 0.f; }
             switch (P) {
-#define SCL_STEP_CASE(CC) case CC: scl_step_loop<CC>(Sin, Gb, X, N, ak, dAc, fixm, step_morph); break;
+#define SCL_STEP_CASE(CC) case CC: if (has_prior) scl_step_loop<CC, PRIOR>(Sin, Gb, X, N, ak, dAc, fixm, step_morph, a_m, bm); \
+                               else scl_step_loop<CC>(Sin, Gb, X, N, ak, dAc, fixm, step_morph); break;
                 SCL_STEP_CASE(1) SCL_STEP_CASE(2) SCL_STEP_CASE(3) SCL_STEP_CASE(4)
                 SCL_STEP_CASE(5) SCL_STEP_CASE(6) SCL_STEP_CASE(7) SCL_STEP_CASE(8)
 #undef SCL_STEP_CASE
@@ -128,13 +178,110 @@ __device__ __forceinline__ void scl_component_step(const SclProxArgs& a, int k, 
                         for (int w = 0; w < (int)(blockDim.x >> 5); w++) v += sdA[w][p];
                 float an = a.A[(size_t)k * C + threadIdx.x];
                 sAold[threadIdx.x] = an;
-                if (!(fl & SCL_F_FIX_SED)) an = an - (1.0f / a.lips[2 * b]) * (float)v;
+                float g = (float)v;
+                if (has_prior) g = g + (a_s * an + a.prior_b_sed[(size_t)k * C + threadIdx.x]);
+                if (!(fl & SCL_F_FIX_SED)) an = an - (1.0f / Ls) * g;
                 sAnew[threadIdx.x] = an;
             }
         } else {
             for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = Sin[p];
             if (threadIdx.x < C) sAnew[threadIdx.x] = sAold[threadIdx.x] = a.A[(size_t)k * C + threadIdx.x];
+            if (step_out && threadIdx.x == 0) *step_out = 1.f;
         }
+    }
+}
+
+// A declared schedule: the update() of a custom source, as the ordered list of scarlet.update / scarlet.measurement
+// calls it makes (traced once on the host, scarlet_b200/schedule.py), run on the stepped component.  All threads of
+// the CTA; X / Z: the component's working copy and symmetry scratch; sA: its stepped SED (shared); sc / ss: its
+// pixel_center and shift (shared, live: ops that move them are seen by the ops after them).
+__device__ void scl_run_schedule(const SclProxArgs& a, int k, int b, float* X, float* Z, float* tab, float* sA,
+                                 int* sc, double* ss, double* red, float step_morph)
+{
+    __shared__ float s_n;
+    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
+    const int* ops = a.sched_ops + (size_t)k * SCL_SCHED_MAX;
+    const float* args = a.sched_args + (size_t)k * SCL_SCHED_MAX;
+    __syncthreads();
+    for (int i = 0; i < SCL_SCHED_MAX; i++) {
+        const int op = ops[i];
+        if (op == 0) break;
+        const float arg = args[i];
+        switch (op) {
+        case SCL_OP_POSITIVE_SED:
+            if (threadIdx.x < C && sA[threadIdx.x] < 0.f) sA[threadIdx.x] = 0.f;
+            break;
+        case SCL_OP_POSITIVE_MORPH:
+            for (int p = threadIdx.x; p < N; p += blockDim.x) if (X[p] < 0.f) X[p] = 0.f;
+            break;
+        case SCL_OP_NORM_SED: case SCL_OP_NORM_MORPH: case SCL_OP_NORM_MORPH_MAX: {
+            float n;
+            if (op == SCL_OP_NORM_SED) {
+                if (threadIdx.x == 0) { float t = 0.f; for (int c = 0; c < C; c++) t = __fadd_rn(t, sA[c]); s_n = t; }
+                __syncthreads();
+                n = s_n;
+            } else if (op == SCL_OP_NORM_MORPH) {
+                double t = 0.0;
+                for (int p = threadIdx.x; p < N; p += blockDim.x) t += (double)X[p];
+                n = (float)block_sum<double>(t, red);
+            } else {
+                float mx = -INFINITY;
+                for (int p = threadIdx.x; p < N; p += blockDim.x) mx = fmaxf(mx, X[p]);
+                mx = warp_max(mx);
+                __syncthreads();
+                if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = (double)mx;
+                __syncthreads();
+                if (threadIdx.x == 0) {
+                    float v = -INFINITY;
+                    for (int w = 0; w < (int)(blockDim.x >> 5); w++) v = fmaxf(v, (float)red[w]);
+                    s_n = v;
+                }
+                __syncthreads();
+                n = s_n;
+            }
+            const bool sed_down = (op == SCL_OP_NORM_SED);        // 'sed': sed / n, morph * n; else the reverse
+            if (threadIdx.x < C) sA[threadIdx.x] = sed_down ? __fdiv_rn(sA[threadIdx.x], n) : __fmul_rn(sA[threadIdx.x], n);
+            for (int p = threadIdx.x; p < N; p += blockDim.x) X[p] = sed_down ? __fmul_rn(X[p], n) : __fdiv_rn(X[p], n);
+            break;
+        }
+        case SCL_OP_SPARSE_L0: case SCL_OP_SPARSE_L1: {
+            const float t = arg * step_morph;                      // proxmin: thresh * step
+            for (int p = threadIdx.x; p < N; p += blockDim.x) {
+                const float v = X[p], av = fabsf(v);
+                if (op == SCL_OP_SPARSE_L0) { if (av < t) X[p] = 0.f; }
+                else { const float m = fmaxf(av - t, 0.f); X[p] = (v > 0.f) ? m : (v < 0.f ? -m : 0.f * m); }
+            }
+            break;
+        }
+        case SCL_OP_THRESHOLD:
+            scl_threshold_body(X, Ny, Nx, 1, nullptr, nullptr, nullptr);
+            break;
+        case SCL_OP_MONOTONIC:
+            scl_monotonic_hbm<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, arg);
+            break;
+        case SCL_OP_SYM_KSPACE: case SCL_OP_SYM_SOFT: case SCL_OP_SYM_SDSS: {
+            const SclWindow w = scl_window(Ny, Nx, sc[0], sc[1]);
+            if (op == SCL_OP_SYM_KSPACE) {
+                // the centred case returns a new array that update.symmetric drops (update.py:193-198)
+                if (!w.centered) scl_kspace_symmetry(X, Nx, w, ss[0], ss[1], Z, tab, a.nfl, a.nfl_even);
+            } else {
+                scl_flip_symmetry(X, Nx, w, op == SCL_OP_SYM_SDSS, arg);
+            }
+            break;
+        }
+        case SCL_OP_MAX_PIXEL:
+            scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
+            break;
+        case SCL_OP_CENTROID: {
+            const float* psf = a.cw + (size_t)a.cw_idx[b] * a.ph * a.pw;
+            const int cy = sc[0], cx = sc[1];
+            __syncthreads();
+            scl_centroid(X, Ny, Nx, psf, a.ph, a.pw, cy, cx, sc, ss, red);
+            break;
+        }
+        default: break;
+        }
+        __syncthreads();
     }
 }
 
@@ -156,6 +303,8 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     __shared__ int sc[2];
     __shared__ double ss[2];
     __shared__ float sm;
+    __shared__ int sexit;               // last level the scene-mode sweep processed (0x7fffffff: not stopped early)
+    if (threadIdx.x == 0) sexit = 0x7fffffff;
     const unsigned fl = a.cflags[k];
     long long tprev = a.phase_clk ? clock64() : 0;
 #define SCL_PHASE(i) do { if (a.phase_clk && threadIdx.x == 0) { long long t_ = clock64(); \
@@ -165,7 +314,8 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     // gradient steps of this component
     __shared__ double sdA[THREADS / 32][SCL_MAX_BANDS];
     __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
-    scl_component_step(a, k, b, fl, X, sdA, sAnew, sAold);
+    __shared__ float sstep;
+    scl_component_step<SCENE>(a, k, b, fl, X, sdA, sAnew, sAold, SCENE ? &sstep : nullptr);
     if (threadIdx.x == 0) {
         sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
         ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
@@ -173,6 +323,12 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     __syncthreads();
     SCL_PHASE(0);      // gradient step
 
+    bool scheduled = false;
+    if (SCENE && (fl & SCL_F_SCHEDULE)) {
+        scheduled = true;
+        scl_run_schedule(a, k, b, X, Z, tab, sAnew, sc, ss, red, sstep);
+        if (threadIdx.x == 0) sm = 1.f;
+    } else
     if (fl & SCL_F_CONSTRAINED) {
         // components of a multi-component source: centre and shift were measured on the source's combined
         // morphology by scl_k_source_center just before this launch
@@ -213,7 +369,9 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                 }
                 __syncthreads();
             } else if (SCENE) {
-                scl_monotonic_hbm<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
+                scl_monotonic_hbm<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f,
+                                                a.no_early_exit ? nullptr : &sexit);
+                __syncthreads();
             } else {
                 scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);
             }
@@ -221,6 +379,42 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
         SCL_PHASE(3);  // monotonic sweep
         // positive (update.py:27-32) + morph_max (update.py:62-65)
         float mx = -INFINITY;
+        if (SCENE && (Nx & 3) == 0) {
+            // X lives in HBM / L2 here: 16-byte accesses, two per thread in flight (the scalar loop had one 4-byte load
+            // per thread outstanding and ran at a tenth of the memory bandwidth)
+            const int vx = sexit, cy = sc[0], cx = sc[1], n4 = N >> 2, nt = blockDim.x;
+            float4* X4 = reinterpret_cast<float4*>(X);
+            for (int i0 = threadIdx.x; i0 < n4; i0 += 2 * nt) {
+                float4 q[2];
+                const bool has1 = i0 + nt < n4;
+                q[0] = X4[i0];
+                q[1] = has1 ? X4[i0 + nt] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 2; u++) {
+                    if (u == 1 && !has1) break;
+                    const int p = (i0 + u * nt) << 2, y = p / Nx, x = p - y * Nx;
+                    float* e = reinterpret_cast<float*>(&q[u]);
+                    bool dirty = false;
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        // beyond the last level an early-stopped sweep processed, pixels are <= 0 without having been computed
+                        if (e[j] < 0.f || (vx != 0x7fffffff && scl_mono_level(y - cy, x + j - cx) > vx)) { e[j] = 0.f; dirty = true; }
+                        mx = fmaxf(mx, e[j]);
+                    }
+                    if (dirty) X4[i0 + u * nt] = q[u];
+                }
+            }
+        } else
+        if (SCENE && sexit != 0x7fffffff) {
+            // the sweep stopped early: pixels beyond its last level are <= 0 without having been computed
+            const int vx = sexit, cy = sc[0], cx = sc[1];
+            for (int p = threadIdx.x; p < N; p += blockDim.x) {
+                const int y = p / Nx, x = p - y * Nx;
+                float v = X[p];
+                if (v < 0.f || scl_mono_level(y - cy, x - cx) > vx) { v = 0.f; X[p] = 0.f; }
+                mx = fmaxf(mx, v);
+            }
+        } else
         for (int p = threadIdx.x; p < N; p += blockDim.x) {
             float v = X[p];
             if (v < 0.f) { v = 0.f; X[p] = 0.f; }
@@ -241,11 +435,37 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     }
     __syncthreads();
     const float norm = sm;
-    const bool constrained = fl & SCL_F_CONSTRAINED;
+    const bool constrained = (fl & SCL_F_CONSTRAINED) && !scheduled;
 
     // write back + convergence sums (blend.py:160-174)
     double d2 = 0.0, n2 = 0.0;
     float* Sout = a.S + (size_t)k * N;
+    if (SCENE && (N & 3) == 0) {
+        const int n4 = N >> 2, nt = blockDim.x;
+        const float4* X4 = reinterpret_cast<const float4*>(X);
+        float4* S4 = reinterpret_cast<float4*>(Sout);
+        for (int i0 = threadIdx.x; i0 < n4; i0 += 2 * nt) {
+            const bool has1 = i0 + nt < n4;
+            const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 o[2], v[2];
+            o[0] = S4[i0]; v[0] = X4[i0];
+            o[1] = has1 ? S4[i0 + nt] : z; v[1] = has1 ? X4[i0 + nt] : z;
+#pragma unroll
+            for (int u = 0; u < 2; u++) {
+                if (u == 1 && !has1) break;
+                float* e = reinterpret_cast<float*>(&v[u]);
+                const float* oe = reinterpret_cast<const float*>(&o[u]);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    if (constrained) e[j] = e[j] / norm;
+                    const double df = (double)oe[j] - (double)e[j];
+                    d2 += df * df;
+                    n2 += (double)e[j] * (double)e[j];
+                }
+                S4[i0 + u * nt] = v[u];
+            }
+        }
+    } else
     for (int p0 = threadIdx.x; p0 < N; p0 += 8 * blockDim.x) {
         float old[8];
 #pragma unroll
@@ -335,7 +555,7 @@ __device__ __forceinline__ void scl_source_center_body(const SclProxArgs& a, con
     const unsigned fl0 = a.cflags[k0];
     for (int j = 0; j < n; j++) {
         const int k = k0 + j;
-        scl_component_step(a, k, b, a.cflags[k], Xk, sdA, sAnew, sAold);
+        scl_component_step<SCENE>(a, k, b, a.cflags[k], Xk, sdA, sAnew, sAold);
         __syncthreads();
         float ssum = 0.f;                                    // c.sed.sum(), float32, band order
         for (int c = 0; c < C; c++) ssum = __fadd_rn(ssum, sAnew[c]);

@@ -29,9 +29,8 @@ scl_k_sparse(float* __restrict__ x, size_t n, float t, int mode)
 // 50 bins, or count/10 below 500 pixels (a single bin: no cut); the cut is 10^(left edge of the last empty bin), 0
 // when every bin is occupied.  Then update.threshold: pixels below the cut are zeroed and the box of what is left
 // is reported (bounds -1 when nothing is).
-extern "C" __global__ void __launch_bounds__(256)
-scl_k_threshold(float* __restrict__ x, int Ny, int Nx, int apply, double* __restrict__ thresh_out, int* __restrict__ bins_out,
-                int* __restrict__ bounds)
+// all threads of the CTA; X: one image; outputs (may be nullptr) written by thread 0
+__device__ void scl_threshold_body(float* X, int Ny, int Nx, int apply, double* thresh_out, int* bins_out, int* bb)
 {
     __shared__ float fred[2][32];
     __shared__ int ired[4][32];
@@ -40,7 +39,7 @@ scl_k_threshold(float* __restrict__ x, int Ny, int Nx, int apply, double* __rest
     __shared__ int s_cnt;
     __shared__ double s_thresh;
     const int N = Ny * Nx, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
-    float* X = x + (size_t)blockIdx.x * N;
+    __syncthreads();            // the shared arrays may still be read by a previous call
 
     float lo = INFINITY, hi = -INFINITY;
     int cnt = 0;
@@ -91,7 +90,7 @@ scl_k_threshold(float* __restrict__ x, int Ny, int Nx, int apply, double* __rest
         __syncthreads();
         thresh = s_thresh;
     }
-    if (threadIdx.x == 0) { thresh_out[blockIdx.x] = thresh; bins_out[blockIdx.x] = bins; }
+    if (threadIdx.x == 0) { if (thresh_out) *thresh_out = thresh; if (bins_out) *bins_out = bins; }
     if (!apply) return;
 
     int y0 = Ny, y1 = -1, x0 = Nx, x1 = -1;
@@ -116,9 +115,17 @@ scl_k_threshold(float* __restrict__ x, int Ny, int Nx, int apply, double* __rest
             y0 = min(y0, ired[0][w]); y1 = max(y1, ired[1][w]); x0 = min(x0, ired[2][w]); x1 = max(x1, ired[3][w]);
         }
         const bool any = y1 >= y0;
-        int* bb = bounds + 4 * (size_t)blockIdx.x;
-        bb[0] = any ? y0 : -1; bb[1] = any ? y1 : -1; bb[2] = any ? x0 : -1; bb[3] = any ? x1 : -1;
+        if (bb) { bb[0] = any ? y0 : -1; bb[1] = any ? y1 : -1; bb[2] = any ? x0 : -1; bb[3] = any ? x1 : -1; }
     }
+    __syncthreads();
+}
+
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_threshold(float* __restrict__ x, int Ny, int Nx, int apply, double* __restrict__ thresh_out, int* __restrict__ bins_out,
+                int* __restrict__ bounds)
+{
+    scl_threshold_body(x + (size_t)blockIdx.x * Ny * Nx, Ny, Nx, apply, thresh_out + blockIdx.x, bins_out + blockIdx.x,
+                       bounds + 4 * (size_t)blockIdx.x);
 }
 
 // interpolation.fft_resample / update.translation (interpolation.py:408-448, update.py:159-167): the image convolved

@@ -672,9 +672,17 @@ __device__ __forceinline__ T scl_mono_pixel_value_hbm(const T* X, int Ny, int Nx
 }
 
 
+// exit_level != nullptr (the in-loop caller, whose next step is prox_plus): the sweep stops once three consecutive
+// levels hold no positive pixel and *exit_level receives the last level it processed; every pixel of a higher level
+// would come out <= 0 -- its strictly closer neighbours (operator.py:569-571) lie 1, 2 or 3 levels below it, only
+// positive weights enter the sum (operators_pybind11.cc:43), so ref <= 0 and min(x, ref (1 - thresh)) <= 0 by
+// induction over the levels -- and prox_plus (update.py:27-32) turns it into 0: the caller zeroes those pixels
+// instead.  Bit-identical to the full sweep followed by prox_plus (tests/test_gpu_fit.py::test_scene_early_exit_*).
+// *exit_level = 0x7fffffff when the sweep ran to the end.  exit_level is shared memory written by thread 0.
 template <typename T, bool NEAREST>
 __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
-                              const float* __restrict__ wtab, const double* __restrict__ ctab, T thresh) {
+                              const float* __restrict__ wtab, const double* __restrict__ ctab, T thresh,
+                              int* exit_level = nullptr) {
     const T omt = (T)1 - thresh;
     const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
     const int vmax = 2 * max(ay, ax) + min(ay, ax);       // v = level + 1 = 2a + b
@@ -691,8 +699,10 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
     // The pixels of a level are independent: each thread takes up to MONO_ILP of them per round and computes all
     // their values before storing any, so their loads overlap (with X in HBM/L2 a round is one memory round trip).
     constexpr int MONO_ILP = 2;
+    int dry = 0, vlast = 0x7fffffff;    // consecutive levels without a positive pixel (block-uniform); last level done
     for (int v = 1; v <= vmax; v++) {
         const int amin = (v + 2) / 3, amax = v / 2;
+        int anypos = 0;
         for (int a0 = amin + slot; a0 <= amax; a0 += MONO_ILP * nslot) {
             T val[MONO_ILP];
             int pos[MONO_ILP];
@@ -713,8 +723,15 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
             }
 #pragma unroll
             for (int u = 0; u < MONO_ILP; u++)
-                if (pos[u] >= 0) X[pos[u]] = val[u];
+                if (pos[u] >= 0) { X[pos[u]] = val[u]; anypos |= !(val[u] <= (T)0); }
         }
-        __syncthreads();
+        if (exit_level) {
+            // the level barrier doubles as the vote (a level without pixels inside the frame counts as dry)
+            dry = __syncthreads_or(anypos) ? 0 : dry + 1;
+            if (dry >= 3 && v >= 3) { vlast = v; break; }
+        } else {
+            __syncthreads();
+        }
     }
+    if (exit_level && threadIdx.x == 0) *exit_level = vlast;
 }

@@ -105,7 +105,11 @@ class Observation():
         if self.frame.psfs is not model_frame.psfs:
             assert self.frame.psfs is not None and model_frame.psfs is not None
             p_obs, p_mod = self.frame.psfs.image, model_frame.psfs.image
-            if p_obs.ndim == 3 and p_mod.ndim == 3 and p_mod.shape[0] == 1 and len(self.frame.shape) == 3:
+            if model_frame.dtype == np.float64:
+                # float64 frames (the reference's own loop tests): the k-space division in float64 on the host,
+                # exactly fft.match_psfs (fft.py:282-301); the float64 loop convolves with the real-space kernels
+                self._diff_kernels = fft.match_psfs(self.frame.psfs, model_frame.psfs)
+            elif p_obs.ndim == 3 and p_mod.ndim == 3 and p_mod.shape[0] == 1 and len(self.frame.shape) == 3:
                 # the usual case (one model PSF, one observed PSF per band): kernels and their spectra in one
                 # device pass (csrc/k_psf.cu)
                 diff, spec = _native.match_psfs(p_obs[None], p_mod, frame_shape=self.frame.shape[1:])
@@ -127,6 +131,8 @@ class Observation():
     def _convolve(self, model):
         C = model.shape[0]
         _, ky, kx = self._diff_kernels.image.shape
+        if model.dtype == np.float64:
+            return _native.convolve_f64(model[None], np.broadcast_to(self._diff_kernels.image, (C, ky, kx)))[0]
         out = _native.convolve(np.asarray(model, dtype=np.float32)[None], self.kernel_spectrum(), np.arange(C),
                                ker_half=_native.kernel_half(ky, kx, model.shape[1], model.shape[2]))[0]
         return out.astype(model.dtype, copy=False)

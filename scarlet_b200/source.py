@@ -192,10 +192,32 @@ def constrain_sources(sources, it=0):
     frame = sources[0].frame
     C, Ny, Nx = frame.shape
     n = len(sources)
-    cw = np.asarray(_centroid_weight(frame), dtype=np.float32)
     comps = [(s, c) for s in sources for c in (s.components if isinstance(s, ComponentTree) else [s])]
     counts = [len(s.components) if isinstance(s, ComponentTree) else 1 for s in sources]
     off = np.concatenate([[0], np.cumsum(counts)])
+    if frame.dtype == np.float64:
+        # float64 frames (the reference's own loop tests): the same pass by the float64 kernels (csrc/k_f64.cu)
+        out = _native.constrain_f64(
+            C, Ny, Nx, np.array([c._sed for _, c in comps]), np.array([c._morph for _, c in comps]),
+            [component_flags(s, c) for s, c in comps], [s.pixel_center for s, _ in comps],
+            [getattr(s, "shift", (0., 0.)) for s, _ in comps], np.asarray(_centroid_weight(frame), dtype=np.float64),
+            np.repeat(off[:-1], counts))
+    else:
+        out = _constrain_f32(frame, sources, comps, counts, off)
+    for i, s in enumerate(sources):
+        for j, c in enumerate(s.components if isinstance(s, ComponentTree) else [s]):
+            c._sed = out["sed"][off[i] + j].astype(frame.dtype)
+            c._morph = out["morph"][off[i] + j].astype(frame.dtype)
+        k = off[i]
+        s.pixel_center = (int(out["center"][k, 0]), int(out["center"][k, 1]))
+        if s.symmetric:
+            s.shift = (float(out["shift"][k, 0]), float(out["shift"][k, 1]))
+
+
+def _constrain_f32(frame, sources, comps, counts, off):
+    C, Ny, Nx = frame.shape
+    n = len(sources)
+    cw = np.asarray(_centroid_weight(frame), dtype=np.float32)
     bt = _native.Batch(
         C, Ny, Nx, comp_off=off, sed=np.array([c._sed for _, c in comps]),
         morph=np.array([c._morph for _, c in comps]), cflags=[component_flags(s, c) for s, c in comps],
@@ -206,14 +228,7 @@ def constrain_sources(sources, it=0):
     bt.constrain()
     out = bt.download()
     bt.close()
-    for i, s in enumerate(sources):
-        for j, c in enumerate(s.components if isinstance(s, ComponentTree) else [s]):
-            c._sed = out["sed"][off[i] + j].astype(frame.dtype)
-            c._morph = out["morph"][off[i] + j].astype(frame.dtype)
-        k = off[i]
-        s.pixel_center = (int(out["center"][k, 0]), int(out["center"][k, 1]))
-        if s.symmetric:
-            s.shift = (float(out["shift"][k, 0]), float(out["shift"][k, 1]))
+    return out
 
 
 class RandomSource(Component):

@@ -136,6 +136,55 @@ def lowres_blend(gold, frame, ohr, olr):
     return srcs, rb.Blend(srcs, [ohr, olr])
 
 
+def scene_blend(size, sources, bands=6, psf_size=41, seed=None, multi_fraction=.7):
+    """Oracle objects for one config-4-class scene of scarlet_b200.synth.scene_arrays (70 % two-component sources
+    sharing a centre like MultiComponentSource, the rest ExtendedSource, every constraint on), started from the
+    generator's own profiles.  Returns (batch arrays as generated, extra, oracle Blend)."""
+    from scarlet_b200 import synth
+    kw = {} if seed is None else dict(seed=seed)
+    batch, extra = synth.scene_arrays(size, sources, bands, psf_size, multi_fraction=multi_fraction, **kw)
+    C, Ny, Nx = batch["C"], batch["Ny"], batch["Nx"]
+    frame = rb.Frame((C, Ny, Nx), psfs=extra["mpsf"], dtype=np.float32)
+    obs = rb.Observation(extra["images"], psfs=extra["psfs"], weights=batch["weights"][0]).match(frame)
+    cw = rb._centroid_weight(frame)
+    srcs, k, K = [], 0, len(batch["sed"])
+    while k < K:
+        if extra["multi"][k]:
+            m = object.__new__(rb.MultiComponentSource)
+            m.frame, m.symmetric, m.monotonic, m.parent = frame, True, True, None
+            m.pixel_center, m.shift, m.centroid_weight = tuple(batch["center"][k]), (0., 0.), cw
+            m.components = [rb.Component(frame, batch["sed"][j], batch["morph"][j]) for j in (k, k + 1)]
+            srcs.append(m)
+            k += 2
+        else:
+            s_ = object.__new__(rb.ExtendedSource)
+            rb.Component.__init__(s_, frame, batch["sed"][k], batch["morph"][k])
+            s_.symmetric, s_.monotonic, s_.centroid_weight = True, True, cw
+            s_.pixel_center, s_.shift = tuple(batch["center"][k]), (0., 0.)
+            srcs.append(s_)
+            k += 1
+    return batch, extra, rb.Blend(srcs, obs)
+
+
+def seed_oracle(blend, out, k0, logL):
+    """Put an oracle Blend into the state a device run left behind: components [k0, k0 + K) of a downloaded batch
+    (`out` of _native.Batch.download) and the loss history `logL` (one entry per iteration run).  The previous
+    iterate the next convergence check compares with is the state itself (blend.py:180-182)."""
+    k = k0
+    for s in blend.sources:
+        for c in s.components:
+            c.sed = out["sed"][k].astype(blend.frame.dtype).copy()
+            c.morph = out["morph"][k].astype(blend.frame.dtype).copy()
+            c.flags = int(out["conv"][k])
+            c.last_sed, c.last_morph = c.sed.copy(), c.morph.copy()
+            k += 1
+        if hasattr(s, "pixel_center"):
+            s.pixel_center = (int(out["center"][k - 1, 0]), int(out["center"][k - 1, 1]))
+            s.shift = (float(out["shift"][k - 1, 0]), float(out["shift"][k - 1, 1]))
+    blend.mse = [float(v) for v in logL]
+    return k
+
+
 def sys_path_golden():
     import sys
     if GOLD not in sys.path:

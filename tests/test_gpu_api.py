@@ -278,7 +278,8 @@ def test_multiresolution_workflow(scarlet):
 
 def test_unsupported_paths_are_loud(scarlet):
     frame, obs, srcs, blend = _scene(scarlet, "sim")
-    f64 = scarlet.Frame(obs.images.shape, psfs=frame.psfs.image.astype(np.float64), dtype=np.float64)
-    c = scarlet.Component(f64, np.ones(6), np.ones((40, 59)))
+    # float32 and float64 frames have kernels (float64: tests/test_gpu_f64.py); anything else is refused
+    f16 = scarlet.Frame(obs.images.shape, psfs=frame.psfs.image.astype(np.float16), dtype=np.float16)
+    c = scarlet.Component(f16, np.ones(6), np.ones((40, 59)))
     with pytest.raises(NotImplementedError):
         scarlet.Blend([c], obs).fit(1)

@@ -52,7 +52,7 @@ def test_fit_matches_oracle(batch6):
         ref = bl.get_model().astype(np.float64)
         got = np.einsum("kc,kyx->cyx", out["sed"][off[i]:off[i + 1]].astype(np.float64),
                         out["morph"][off[i]:off[i + 1]].astype(np.float64))
-        assert_allclose(got, ref, rtol=0, atol=1e-3 * np.abs(ref).max())
+        assert_allclose(got, ref, rtol=0, atol=2e-4 * np.abs(ref).max())    # 30 free-running fp32 iterations; single iterations: test_gpu_parity_config3.py
     # restore brings the initial state back bit for bit; the repeated fit is bit-identical
     bb.restore()
     again0 = bb.download()

@@ -170,6 +170,68 @@ def test_scene_lockstep_large_frame(nat):
     _lockstep(nat, blend, 4, approximate_L=False)
 
 
+@pytest.mark.parametrize("approx", [False, True])
+def test_scene_lockstep_config4_class_256(nat, approx):
+    """BASELINE config 4's class at a quarter of its area: a 6-band 256x256 scene with 100 sources (70 %
+    two-component => K ~ 170 > 64: several Gram tiles, the tiled squarings and the f64 Rayleigh quotient against
+    np.linalg.eigvals of blend.py:203-217, ~70 shared-centre sources, the HBM level loop), three iterations vs the
+    oracle: logL 1e-5, L 2e-6, centres / flags exact."""
+    _, _, blend = helpers.scene_blend(256, 100)
+    assert len(blend.components) > 128
+    _lockstep(nat, blend, 3, approximate_L=approx)
+
+
+def test_scene_lockstep_config4_full_512(nat):
+    """ONE lock-step iteration of the real config-4 scene (6 bands, 512x512, 200 sources, K = 329) vs the oracle
+    (~20 s of host time), exact Lipschitz constants."""
+    _, _, blend = helpers.scene_blend(512, 200)
+    assert len(blend.components) > 256
+    _lockstep(nat, blend, 1)
+
+
+@pytest.mark.parametrize("case", ["scene160", "blends64"])
+def test_scene_early_exit_is_bit_identical(nat, case):
+    """The scene-mode sweep stops at the first three consecutive levels without a positive pixel and the rest of
+    the frame is zeroed (what the full sweep + prox_plus would leave there, operator.py:569-571, update.py:27-32):
+    bit-identical state and loss history against the full sweep over several free-running iterations."""
+    if case == "scene160":
+        batch, _, _ = helpers.scene_blend(160, 24)
+        kw = dict(batch)
+    else:
+        kw = dict(helpers.pack([helpers.synthetic_blend(s, kmin=3, kmax=6)[3] for s in (11, 12, 13)]), scene_mode=1)
+    outs = []
+    for flags in (0, 1):
+        bt = nat.Batch(**kw)
+        bt.debug_flags(flags)
+        bt.fit(6, 0.0)
+        outs.append(bt.download())
+        bt.close()
+    a, b = outs
+    for key in ("sed", "morph", "center", "shift", "conv", "logL", "lipschitz"):
+        assert_array_equal(a[key], b[key])
+    if case == "scene160":
+        assert (a["morph"] == 0).mean() > 0.2       # there was something to skip
+
+
+def test_scene_gram_by_footprint_boxes_equals_dense(nat):
+    """Exact L in scene mode: S S^T over the intersections of the components' footprint boxes (scl_k_scene_bbox /
+    scl_k_scene_gram_boxes) against the dense tiled contraction over every pixel of every pair: the same products,
+    so the constants agree to float64 summation order and the iterates to a few ulp."""
+    batch, _, _ = helpers.scene_blend(160, 24)
+    outs = []
+    for flags in (0, 2):
+        bt = nat.Batch(**batch)
+        bt.debug_flags(flags)
+        bt.fit(4, 0.0)
+        outs.append(bt.download())
+        bt.close()
+    a, b = outs
+    assert_allclose(a["lipschitz"], b["lipschitz"], rtol=1e-6)
+    assert_allclose(a["logL"], b["logL"], rtol=1e-6)
+    assert_array_equal(a["center"], b["center"])
+    assert_allclose(a["morph"], b["morph"], rtol=0, atol=2e-6)
+
+
 def test_multicomponent_free_running_vs_reference(nat):
     """The same scene free-running against the reference's own run (tests/golden/make_golden_multi.py)."""
     g, _, _, srcs, blend = helpers.multi_blend()
