@@ -278,6 +278,19 @@ int scl_batch_constrain(scl_batch* batch, void* stream);
  * 0 where no pixel survives the cut (the reference raises SourceInitError, source.py:171-173). */
 int scl_batch_init_extended(scl_batch* batch, const float* cw, const float* jac, const float* cutoff,
                             int symmetric, int monotonic, int32_t* ok, void* stream);
+/* The same for a mix of source kinds, kind int32 [Ktot] per component (NULL = all 0):
+ *   0  ExtendedSource: as scl_batch_init_extended.
+ *   1  a component of a MultiComponentSource (init_multicomponent_source, source.py:242-291): the source's first
+ *      component takes the extended initialisation, the base morphology is then cut into len(percentiles) + 1 flux
+ *      layers at percentiles[i] % of its maximum (float32 [n_perc], ascending, 1 <= n_perc <= 3; the reference's
+ *      default is [25]), each layer peak-normalised, and the SEDs of the layers are the least-squares solution of
+ *      images = A^T layers (get_best_fit_seds, source.py:74-98), written over the batch's SEDs.  The components of
+ *      such a source are the SCL_SHARED_CENTER group of src_first; cw / jac / cutoff are read at its first component.
+ *   2  PointSource (source.py:355-375): the model PSF image (the blend's centroid-weight image cw) projected onto
+ *      the frame around pixel_center; the SED as uploaded.
+ * Works in scene mode too (the working copy of the coadd then lives in the HBM scratch). */
+int scl_batch_init_sources(scl_batch* batch, const int32_t* kind, const float* cw, const float* jac, const float* cutoff,
+                           int symmetric, int monotonic, const float* percentiles, int n_perc, int32_t* ok, void* stream);
 /* Copy results back.  Any pointer may be NULL.  logL: [B][max_iter of the last fit] (Blend.mse entries appended
  * by that fit; n_iter[b] of them valid); active[b] == 0 <=> blend b converged. */
 int scl_batch_download(scl_batch* batch, float* sed, float* morph, int32_t* center, double* shift, int32_t* conv,

@@ -664,6 +664,20 @@ class Batch:
                                              int(bool(monotonic)), _p(ok), c_void_p(self.stream)))
         return ok.astype(bool)
 
+    def init_sources(self, kind, cw, jac, cutoff, symmetric=True, monotonic=True, percentiles=(25,)):
+        """scl_batch_init_sources: device initialisation of extended (0), multi-component (1) and point (2) sources,
+        kind int32 [K] per component or None (all extended); returns ok [K] bool."""
+        ca = np.ascontiguousarray
+        cw = ca(cw, dtype=np.float32).reshape(self.K, self.C)
+        jac = ca(jac, dtype=np.float32).reshape(self.K)
+        cutoff = ca(cutoff, dtype=np.float32).reshape(self.K)
+        kind = None if kind is None else ca(kind, dtype=np.int32).reshape(self.K)
+        perc = ca(np.sort(np.asarray(percentiles, dtype=np.float32)))
+        ok = np.zeros(self.K, np.int32)
+        _check(lib().scl_batch_init_sources(self._h, _p(kind), _p(cw), _p(jac), _p(cutoff), int(bool(symmetric)),
+                                            int(bool(monotonic)), _p(perc), len(perc), _p(ok), c_void_p(self.stream)))
+        return ok.astype(bool)
+
     def constrain(self):
         """One `update()` pass with it = 0 on every component (what sources run at construction)."""
         _check(lib().scl_batch_constrain(self._h, c_void_p(self.stream)))

@@ -52,7 +52,7 @@ class _Chunks:
         k0, k1 = self.koff[i], self.koff[i + 1]
         out = {}
         for key, v in a.items():
-            if v is None or key in ("C", "Ny", "Nx", "kernel_spec", "cw"):
+            if v is None or key in ("C", "Ny", "Nx", "kernel_spec", "cw", "ker_half"):
                 out[key] = v
             elif key == "comp_off":
                 out[key] = (np.asarray(v[b0:b1 + 1]) - k0).astype(np.int32)
@@ -79,7 +79,7 @@ class _Chunks:
 
     def upload(self, **host):
         self._map(lambda i: self.parts[i].upload(**{k: v for k, v in self._slice(host, i).items()
-                                                    if k not in ("C", "Ny", "Nx")}))
+                                                    if k not in ("C", "Ny", "Nx", "ker_half")}))
 
     def fit(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False, serial=False):
         """`serial=True` runs the chunks one after another (isolated per-kernel timings)."""
@@ -102,7 +102,7 @@ class _Chunks:
         def one(i):
             part = self.parts[i]
             with up:
-                part.upload(**{k: v for k, v in self._slice(host, i).items() if k not in ("C", "Ny", "Nx")})
+                part.upload(**{k: v for k, v in self._slice(host, i).items() if k not in ("C", "Ny", "Nx", "ker_half")})
             r = part.fit(max_iter, e_rel, approximate_L, check_every, False)
             with down:
                 part.download(morph=morph, out=self._slice(out, i))
@@ -178,7 +178,10 @@ class BlendBatch:
     """
 
     def __init__(self, images, psfs, model_psf, centers, bg_rms, weights=None, thresh=1.0,
-                 symmetric=True, monotonic=True, stream=None, streams=1):
+                 symmetric=True, monotonic=True, stream=None, streams=1, kinds=None, flux_percentiles=(25,)):
+        """kinds: list of B integer arrays [K_b] aligned with `centers` -- 0 ExtendedSource (default), 1
+        MultiComponentSource (len(flux_percentiles) + 1 components, source.py:242-291,537-641), 2 PointSource
+        (source.py:323-440); all of them initialised on the device (scl_batch_init_sources)."""
         _native.require_device()
         images = np.ascontiguousarray(images, dtype=np.float32)
         B, C, Ny, Nx = images.shape
@@ -211,9 +214,21 @@ class BlendBatch:
         owner = np.repeat(np.arange(B), counts0)
         ctr = (np.concatenate([np.asarray(c).reshape(-1, 2) for c in centers]).astype(np.int32)
                if counts0.sum() else np.zeros((0, 2), np.int32))
+        kind_src = (np.concatenate([np.asarray(k, dtype=np.int32).reshape(-1) for k in kinds]) if kinds is not None
+                    else np.zeros(len(ctr), np.int32))
+        if len(kind_src) != len(ctr) or np.any((kind_src < 0) | (kind_src > 2)):
+            raise ValueError("kinds: one entry of 0 (extended), 1 (multi-component) or 2 (point) per catalogue row")
+        perc = np.sort(np.asarray(flux_percentiles, dtype=np.float32))
+        n_layers = len(perc) + 1
+        # catalogue rows -> components: a multi-component source owns n_layers consecutive components
+        reps = np.where(kind_src == 1, n_layers, 1)
+        first = np.concatenate([[0], np.cumsum(reps)])[:-1]
+        owner, ctr, kind = np.repeat(owner, reps), np.repeat(ctr, reps, axis=0), np.repeat(kind_src, reps)
+        src_first = np.repeat(first, reps).astype(np.int32)
         sed = images[owner, :, ctr[:, 0], ctr[:, 1]].astype(np.float32)
         sed /= np.asarray(peak_obs[owner] if per_blend else peak_obs, dtype=np.float32)
-        sed = sed * np.float32(peak_mod)
+        # get_psf_sed scales with the model PSF's peak (source.py:64-69); PointSource.__init__ does not (source.py:377-381)
+        sed = np.where((kind == 2)[:, None], sed, sed * np.float32(peak_mod)).astype(np.float32)
         if np.any(bg_rms <= 0):
             raise ValueError("bg_rms must be greater than zero in all channels")
         pos = sed > 0
@@ -231,18 +246,24 @@ class BlendBatch:
         # ---- morphologies on the device (source.py:139-180): coadd, sdss symmetry, monotonic(thresh=.1), noise cut,
         # peak normalisation -- one CTA per candidate source on the batch's own images (scl_batch_init_extended)
         Kc = len(sed)
-        flags = _FLAGS_EXTENDED
+        flags = np.where(kind == 1, _native.F_CONSTRAINED | _native.F_SHARED_CENTER | _native.F_SYMMETRIC | _native.F_MONOTONIC,
+                         _FLAGS_EXTENDED).astype(np.uint32)
         if not symmetric:
-            flags &= ~_native.F_SYMMETRIC
+            flags &= ~np.uint32(_native.F_SYMMETRIC)
         if not monotonic:
-            flags &= ~_native.F_MONOTONIC
+            flags &= ~np.uint32(_native.F_MONOTONIC)
+        self.kind = kind
         wts = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
 
-        def host_dict(keep_src, kept, morph):
+        def host_dict(keep_src, kept, morph, sed=sed):
             cnt = np.bincount(owner[keep_src], minlength=B)[kept]
+            # first component of each kept component's source, renumbered after dropping
+            newpos = -np.ones(Kc + 1, np.int64)
+            newpos[keep_src] = np.arange(len(keep_src))
             return dict(
                 C=C, Ny=Ny, Nx=Nx, comp_off=np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32),
-                sed=sed[keep_src], morph=morph, cflags=np.full(len(keep_src), flags, np.uint32),
+                sed=sed[keep_src], morph=morph, cflags=flags[keep_src],
+                **(dict(src_first=newpos[src_first[keep_src]].astype(np.int32)) if np.any(kind == 1) else {}),
                 center=ctr[keep_src], shift=np.zeros((len(keep_src), 2), np.float64),
                 conv=np.full(len(keep_src), 3, np.int32),
                 images=images if len(kept) == B else images[kept],
@@ -252,13 +273,16 @@ class BlendBatch:
                          else np.tile(np.arange(C, dtype=np.int32), len(kept))),
                 **(dict(psfs=dict(obs=psf_arr if len(kept) == B else psf_arr[kept],
                                   model=np.asarray(mod_psfs.image[:1], dtype=np.float32))) if per_blend else {}),
+                # reach of the difference kernels: frames beyond one convolution tile run in scene mode
+                ker_half=_native.kernel_half(psf_arr.shape[-2], psf_arr.shape[-1], Ny, Nx),
                 cw=np.asarray(mod_psfs[0].image, dtype=np.float32)[None], cw_idx=np.zeros(len(kept), np.int32),
                 it0=np.zeros(len(kept), np.int32), prev_loss=np.zeros(len(kept), np.float64))
 
         has = np.nonzero(counts0 > 0)[0]
         cand = host_dict(np.arange(Kc), has, None)
         dev = _native.Batch(stream=stream, **cand)
-        ok = dev.init_extended(cwt, jac, cutoff, True, monotonic) if Kc else np.zeros(0, bool)
+        ok = (dev.init_sources(kind if kinds is not None else None, cwt, jac, cutoff, True, monotonic, perc)
+              if Kc else np.zeros(0, bool))
         self.n_failed = int((~ok).sum())
         keep_src = np.nonzero(ok)[0]
         self.kept = np.nonzero(np.bincount(owner[keep_src], minlength=B) > 0)[0]
@@ -268,9 +292,10 @@ class BlendBatch:
         else:
             # sources without a pixel above the noise cut are dropped (source.py:171-173), and with them blends left
             # without a source: rebuild the batch from the surviving candidates
-            morphs = dev.download(morph=True)["morph"]
+            first_out = dev.download(morph=True)
             dev.close()
-            self.host = host_dict(keep_src, self.kept, morphs[keep_src])
+            self.kind = kind[keep_src]
+            self.host = host_dict(keep_src, self.kept, first_out["morph"][keep_src], first_out["sed"])
             self._dev = None
         Bk, K = len(self.kept), len(keep_src)
         self.B, self.K = Bk, K
@@ -297,7 +322,7 @@ class BlendBatch:
 
     def upload(self):
         """Host state -> device (what a fresh `fit` on host-resident blends costs)."""
-        self._dev.upload(**{k: v for k, v in self.host.items() if k not in ("C", "Ny", "Nx")})
+        self._dev.upload(**{k: v for k, v in self.host.items() if k not in ("C", "Ny", "Nx", "ker_half")})
 
     def fit_device(self, max_iter=200, e_rel=1e-2, approximate_L=False, check_every=8, profile=False, serial=False):
         """The loop only, on the state already in HBM; returns the timing dict of _native.Batch.fit.

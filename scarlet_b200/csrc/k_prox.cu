@@ -711,17 +711,19 @@ scl_k_mono_plan(int Ny, int Nx, int pbits, unsigned* __restrict__ npass, const u
 //   monotonic sweep with thresh 0.1                                                      (source.py:165-166)
 //   morph = detect where detect > cutoff[k], else 0; no pixel left -> ok[k] = 0 (SourceInitError, source.py:171-173)
 //   morph /= morph[centre]                                                               (source.py:177-179)
-// and writes the morphology into S[k].  dynamic smem: as scl_k_prox
-extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
-scl_k_init_extended(const float* __restrict__ images, const int* __restrict__ comp_blend,
-                    const int* __restrict__ center, const float* __restrict__ cw, const float* __restrict__ jac,
-                    const float* __restrict__ cutoff, float* __restrict__ S, int* __restrict__ ok,
-                    int C, int Ny, int Nx, int symmetric, int monotonic,
-                    const float* __restrict__ wtab, const double* __restrict__ ctab, SclMonoPlan plan)
+// and writes the morphology into S[k].  list (optional): the components to initialise (grid = their number).
+// dynamic smem: as scl_k_prox; SCENE: the working copy lives at xscratch + blockIdx.x * xstride (HBM / L2).
+template <bool SCENE>
+__device__ __forceinline__ void scl_init_extended_body(
+    const float* __restrict__ images, const int* __restrict__ comp_blend, const int* __restrict__ center,
+    const float* __restrict__ cw, const float* __restrict__ jac, const float* __restrict__ cutoff, float* __restrict__ S,
+    int* __restrict__ ok, int C, int Ny, int Nx, int symmetric, int monotonic, const float* __restrict__ wtab,
+    const double* __restrict__ ctab, SclMonoPlan plan, const int* __restrict__ list, float* xscratch, size_t xstride)
 {
     extern __shared__ __align__(16) float smem_i[];
-    const int k = blockIdx.x, b = comp_blend[k], N = Ny * Nx;
-    float* X = smem_i + ((Nx + 4) & ~3);
+    const int k = list ? list[blockIdx.x] : blockIdx.x, b = comp_blend[k], N = Ny * Nx;
+    float* xbase = SCENE ? xscratch + (size_t)blockIdx.x * xstride : smem_i;
+    float* X = xbase + ((Nx + 4) & ~3);
     float* Z = X + ((N + 3) & ~3);
     __shared__ int any;
     const int cy = center[2 * k], cx = center[2 * k + 1];
@@ -741,7 +743,9 @@ scl_k_init_extended(const float* __restrict__ images, const int* __restrict__ co
     __syncthreads();
     if (symmetric) scl_flip_symmetry(X, Nx, scl_window(Ny, Nx, cy, cx), 1, 0.f);
     if (monotonic) {
-        if (plan.pbits) {
+        if (SCENE) {
+            scl_monotonic_hbm<float, false>(X, Ny, Nx, cy, cx, wtab, ctab, 0.1f);
+        } else if (plan.pbits) {
             if (threadIdx.x < 32) {
                 const unsigned f0 = plan.first[cy * Nx + cx], f1 = plan.first[cy * Nx + cx + 1];
                 scl_monotonic_f32_stream(X, Nx, plan.list + (size_t)f0 * 32, (int)(f1 - f0), plan.pbits, wtab, 0.1f, Z);
@@ -763,6 +767,127 @@ scl_k_init_extended(const float* __restrict__ images, const int* __restrict__ co
     for (int p = threadIdx.x; p < N; p += blockDim.x) {
         const float v = (X[p] > cut) ? X[p] : 0.f;
         out[p] = any ? __fdiv_rn(v, peak) : 0.f;
+    }
+}
+
+#define SCL_INIT_EXT_PARAMS const float* __restrict__ images, const int* __restrict__ comp_blend, const int* __restrict__ center, \
+    const float* __restrict__ cw, const float* __restrict__ jac, const float* __restrict__ cutoff, float* __restrict__ S, \
+    int* __restrict__ ok, int C, int Ny, int Nx, int symmetric, int monotonic, const float* __restrict__ wtab, \
+    const double* __restrict__ ctab, SclMonoPlan plan, const int* __restrict__ list, float* xscratch, size_t xstride
+#define SCL_INIT_EXT_ARGS images, comp_blend, center, cw, jac, cutoff, S, ok, C, Ny, Nx, symmetric, monotonic, wtab, ctab, plan, \
+    list, xscratch, xstride
+extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS)
+scl_k_init_extended(SCL_INIT_EXT_PARAMS) { scl_init_extended_body<false>(SCL_INIT_EXT_ARGS); }
+extern "C" __global__ void __launch_bounds__(SCL_PROX_WIDE, SCL_WIDE_MIN)
+scl_k_init_extended_wide(SCL_INIT_EXT_PARAMS) { scl_init_extended_body<true>(SCL_INIT_EXT_ARGS); }
+
+// N1: init_multicomponent_source (source.py:242-291) after the extended initialisation of the source's first
+// component: the base morphology is cut into K flux layers at the percentile thresholds (each layer peak-normalised)
+// and the K SEDs are the least-squares solution of images = A^T layers (get_best_fit_seds, source.py:74-98).
+// One CTA per multi-component source; msrc [n][2] = (first component, K <= 4); perc [K-1] ascending.
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_init_multi(const float* __restrict__ images, const int* __restrict__ comp_blend, const int* __restrict__ msrc,
+                 const float* __restrict__ perc, float* __restrict__ S, float* __restrict__ A, const int* __restrict__ ok,
+                 int C, int N)
+{
+    __shared__ double red[32];
+    __shared__ float smax[5];
+    __shared__ double sg[4][4], sp[4][SCL_MAX_BANDS];
+    const int k0 = msrc[2 * blockIdx.x], K = msrc[2 * blockIdx.x + 1], b = comp_blend[k0];
+    if (!ok[k0] || K < 2 || K > 4) return;
+    float* base = S + (size_t)k0 * N;
+    const float* img = images + (size_t)b * C * N;
+    float mx = -INFINITY;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) mx = fmaxf(mx, base[p]);
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = (double)mx;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        float v = -INFINITY;
+        for (int w = 0; w < (int)(blockDim.x >> 5); w++) v = fmaxf(v, (float)red[w]);
+        smax[4] = v;
+    }
+    __syncthreads();
+    const float max_flux = smax[4];
+    // perc * max_flux / 100 with an integer percentile and a float32 maximum is float64 arithmetic in numpy, and so are
+    // the comparison and the differences below before they are stored as float32 (source.py:263-270)
+    double t[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int k = 1; k < K; k++) t[k] = (double)perc[k - 1] * (double)max_flux / 100.0;
+    // layers (source.py:263-270), written in place: component k0 + k holds layer k
+    float lmax[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        const float v = base[p];
+        float out[4] = {v, 0.f, 0.f, 0.f};
+        for (int k = 1; k < K; k++)
+            if ((double)v > t[k]) { out[k - 1] = (float)(t[k] - t[k - 1]); out[k] = (float)((double)v - t[k]); }
+        for (int k = 0; k < K; k++) { S[(size_t)(k0 + k) * N + p] = out[k]; lmax[k] = fmaxf(lmax[k], out[k]); }
+    }
+    for (int k = 0; k < K; k++) {
+        const float v = warp_max(lmax[k]);
+        __syncthreads();
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = (double)v;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float m = -INFINITY;
+            for (int w = 0; w < (int)(blockDim.x >> 5); w++) m = fmaxf(m, (float)red[w]);
+            smax[k] = m;
+        }
+    }
+    __syncthreads();
+    // peak-normalise (source.py:273-277) and accumulate the normal equations
+    double g[4][4], pr[4][SCL_MAX_BANDS];
+    for (int i = 0; i < 4; i++) { for (int j = 0; j < 4; j++) g[i][j] = 0.0; for (int c = 0; c < SCL_MAX_BANDS; c++) pr[i][c] = 0.0; }
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        float l[4] = {0.f, 0.f, 0.f, 0.f};
+        for (int k = 0; k < K; k++) {
+            l[k] = __fdiv_rn(S[(size_t)(k0 + k) * N + p], smax[k]);
+            S[(size_t)(k0 + k) * N + p] = l[k];
+        }
+        for (int i = 0; i < K; i++) {
+            for (int j = i; j < K; j++) g[i][j] += (double)l[i] * (double)l[j];
+            for (int c = 0; c < C; c++) pr[i][c] += (double)l[i] * (double)img[(size_t)c * N + p];
+        }
+    }
+    for (int i = 0; i < K; i++) {
+        for (int j = i; j < K; j++) { const double v = block_sum<double>(g[i][j], red); if (threadIdx.x == 0) { sg[i][j] = v; sg[j][i] = v; } }
+        for (int c = 0; c < C; c++) { const double v = block_sum<double>(pr[i][c], red); if (threadIdx.x == 0) sp[i][c] = v; }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        // seds = inv(G) P by Gauss-Jordan elimination with partial pivoting (K <= 4, float64)
+        double a[4][4 + SCL_MAX_BANDS];
+        for (int i = 0; i < K; i++) { for (int j = 0; j < K; j++) a[i][j] = sg[i][j]; for (int c = 0; c < C; c++) a[i][K + c] = sp[i][c]; }
+        for (int col = 0; col < K; col++) {
+            int piv = col;
+            for (int r = col + 1; r < K; r++) if (fabs(a[r][col]) > fabs(a[piv][col])) piv = r;
+            for (int j = 0; j < K + C; j++) { const double tmp = a[col][j]; a[col][j] = a[piv][j]; a[piv][j] = tmp; }
+            const double d = a[col][col];
+            for (int j = 0; j < K + C; j++) a[col][j] /= d;
+            for (int r = 0; r < K; r++) {
+                if (r == col) continue;
+                const double f = a[r][col];
+                for (int j = 0; j < K + C; j++) a[r][j] -= f * a[col][j];
+            }
+        }
+        for (int i = 0; i < K; i++) for (int c = 0; c < C; c++) A[(size_t)(k0 + i) * C + c] = (float)a[i][K + c];
+    }
+}
+
+// N1: PointSource.__init__ (source.py:355-375): the model PSF image projected onto the frame around the source's
+// pixel (interpolation.get_projection_slices).  One CTA per listed component.
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_init_point(const int* __restrict__ list, const int* __restrict__ comp_blend, const int* __restrict__ center,
+                 const float* __restrict__ cw, const int* __restrict__ cw_idx, int ph, int pw, float* __restrict__ S,
+                 int Ny, int Nx)
+{
+    const int k = list[blockIdx.x], b = comp_blend[k], N = Ny * Nx;
+    const float* psf = cw + (size_t)cw_idx[b] * ph * pw;
+    const int py = center[2 * k], px = center[2 * k + 1];
+    const int bottom = py - (Ny - 1) / 2 - (ph - 1) / 2 + (Ny >> 1), left = px - (Nx - 1) / 2 - (pw - 1) / 2 + (Nx >> 1);
+    float* out = S + (size_t)k * N;
+    for (int p = threadIdx.x; p < N; p += blockDim.x) {
+        const int y = p / Nx, x = p - y * Nx, iy = y - bottom, ix = x - left;
+        out[p] = (iy >= 0 && iy < ph && ix >= 0 && ix < pw) ? psf[iy * pw + ix] : 0.f;
     }
 }
 

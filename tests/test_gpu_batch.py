@@ -36,6 +36,58 @@ def test_init_matches_oracle_sources(batch6):
             assert_allclose(bb.host["morph"][k], s.morph, rtol=0, atol=REL)
 
 
+def _oracle_sources(d, i, kinds, dtype=np.float32):
+    """Oracle sources of blend i of a synth.make_blends dict, one per catalogue row, of the given kinds."""
+    from oracle import ref_blend as rb
+    frame = rb.Frame(d["images"][i].shape, psfs=d["model_psf"], dtype=dtype)
+    obs = rb.Observation(d["images"][i], psfs=d["psfs"], weights=d["weights"][i]).match(frame)
+    srcs = []
+    for (y, x), kd in zip(d["centers"][i], kinds):
+        if kd == 0:
+            srcs.append(rb.ExtendedSource(frame, (int(y), int(x)), obs, d["bg_rms"]))
+        elif kd == 1:
+            srcs.append(rb.MultiComponentSource(frame, (int(y), int(x)), obs, d["bg_rms"]))
+        else:
+            srcs.append(rb.PointSource(frame, (int(y), int(x)), obs))
+    return frame, obs, srcs
+
+
+@pytest.mark.parametrize("shape", [(64, 64), (150, 140)])
+def test_init_of_every_source_kind_matches_oracle(shape):
+    """ExtendedSource, MultiComponentSource (flux layers + least-squares SEDs, source.py:74-98,242-291)
+    and PointSource (source.py:355-375) initialised on the device, then the construction-time update(); against the
+    oracle's objects.  (150, 140): the same in scene mode (working copies in the HBM scratch), then three iterations of
+    the mixed batch in lock step."""
+    from scarlet_b200 import synth
+    from scarlet_b200.batch import BlendBatch
+    from scarlet_b200 import _native as nat
+    from oracle import ref_blend as rb
+    n = 4 if shape == (64, 64) else 1
+    d = synth.make_blends(range(20, 20 + n), Ny=shape[0], Nx=shape[1], kmin=4, kmax=6, device="cpu")
+    kinds = [np.arange(len(c)) % 3 for c in d["centers"]]
+    bb = BlendBatch(d["images"], d["psfs"], d["model_psf"], d["centers"], d["bg_rms"], weights=d["weights"], kinds=kinds)
+    assert bb.n_failed == 0
+    off = bb.host["comp_off"]
+    blends = []
+    for i in range(n):
+        frame, obs, srcs = _oracle_sources(d, i, kinds[i])
+        k = off[i]
+        for s in srcs:
+            for c in s.components:
+                assert_array_equal(bb.host["center"][k], s.pixel_center)
+                assert_allclose(bb.host["shift"][k], s.shift, rtol=0, atol=5e-6)
+                assert_allclose(bb.host["sed"][k], c.sed, rtol=2e-4, atol=2e-5 * np.abs(c.sed).max())
+                assert_allclose(bb.host["morph"][k], c.morph, rtol=0, atol=REL)
+                k += 1
+        assert k == off[i + 1]
+        blends.append(rb.Blend(srcs, obs))
+    # the loop on the mixed batch, from the oracle's own initial state, three iterations
+    import test_gpu_fit
+    for bl in blends[:2]:
+        test_gpu_fit._lockstep(nat, bl, 3)
+    bb.close()
+
+
 def test_fit_matches_oracle(batch6):
     """Free-running fit(30, e_rel=0) of the batch vs the oracle blend by blend."""
     d, bb = batch6
