@@ -15,12 +15,27 @@ def mk_shifter(shape, real=False):
 def sinc_interp(images, coord_hr, coord_lr, angle=None, padding=3):
     """Samples of `images` (pixels at coord_lr) at the positions coord_hr by separable sinc interpolation
     (interpolation.py:342-372).  Like the reference, each image enters transposed (interpolation.py:370)."""
-    if angle is not None:
-        raise NotImplementedError("rotated frames are not supported")
     y_hr, x_hr = coord_hr
     y_lr, x_lr = coord_lr
     hy, hx = np.abs(y_lr[1] - y_lr[0]), np.abs(x_lr[1] - x_lr[0])
     assert hy != 0 and hx != 0
+    if angle is not None:
+        # Rotated grids (interpolation.py:374-404), angle = (cos, sin).  For every high-resolution row a the images are
+        # moved by (-y_a cos / hy, -y_a sin / hx) pixels with a Fourier phase ramp on the zero-padded box, then
+        # sample (a, b) is the double sinc sum over the moved image at (-x_b sin, x_b cos).
+        from . import fft as sfft
+        cos, sin = angle
+        images = np.asarray(images)
+        box = sfft._get_fft_shape(images, images, padding=padding, axes=[1, 2])
+        spec = sfft.Fourier(images).fft(box, (1, 2))                                     # [C, Fy, Fx/2+1]
+        ramp_y, ramp_x = mk_shifter(box)
+        move = (ramp_y[None, :, None] ** (-np.asarray(y_hr, dtype=np.float64) * cos / hy)[:, None, None] *
+                ramp_x[None, None, :] ** (-np.asarray(y_hr, dtype=np.float64) * sin / hx)[:, None, None])
+        moved = sfft.Fourier.from_fft(spec[:, None] * move[None], box,
+                                      (len(images), len(y_hr)) + images.shape[1:], [2, 3]).image    # [C, a, p, q]
+        wy = np.sinc((np.asarray(y_lr)[None, :] + np.asarray(x_hr)[:, None] * sin) / hy)            # [b, p]
+        wx = np.sinc((np.asarray(x_lr)[None, :] - np.asarray(x_hr)[:, None] * cos) / hx)            # [b, q]
+        return np.einsum("capq,bp,bq->cab", moved, wy, wx)
     wy = np.sinc((y_lr[None, :] - y_hr[:, None]) / hy)
     wx = np.sinc((x_lr[:, None] - x_hr[None, :]) / hx)
     return np.array([wy @ img.T @ wx for img in images])

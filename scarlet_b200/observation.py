@@ -158,8 +158,9 @@ class LowResObservation(Observation):
     sinc-shifted to every low-resolution row (`_resconv_op`, as the reference stores it) -- and then folds the
     reference's whole `_render` (pad, FFT along x, per-column phase shift + its "sinc" mask, inverse FFT, contraction
     with `_resconv_op`, final flip) into one matrix per band, `_lr_op[c]`: [n_lr, Ny*Nx].  `_render`, `get_loss` and
-    the loop apply that matrix on the device (scl_lowres_render_f32 / scl_k_lowres).  Unrotated square frames only,
-    the geometry on which the reference's own code runs (resampling.py:90-92).
+    the loop apply that matrix on the device (scl_lowres_render_f32 / scl_k_lowres).  Unrotated frames must be square
+    (the reference multiplies per-row and per-column masks, resampling.py:90-92); rotated frames (`_match_rotated`) must
+    lie inside the model frame, as in the reference (observation.py:486-489).
     """
 
     def __init__(self, images, wcs=None, psfs=None, weights=None, channels=None, padding=3, operator='exact'):
@@ -240,19 +241,21 @@ class LowResObservation(Observation):
         sv, mv = np.sum(sa, axis=0)[:2] / self_pix, np.sum(ma, axis=0)[:2] / model_pix
         sv, mv = sv / np.sum(sv ** 2) ** .5, mv / np.sum(mv ** 2) ** .5
         self.sin_rot, self.cos_rot = sv[0] * mv[1] - sv[1] * mv[0], np.dot(sv, mv)
-        self.isrot = np.abs(self.sin_rot) ** 2 > np.finfo(float).eps
-        if self.isrot:
-            raise NotImplementedError("rotated low-resolution frames are not supported (see the class docstring)")
-        self.sin_rot, self.cos_rot = 0, 1
+        self.isrot = bool(np.abs(self.sin_rot) ** 2 > np.finfo(float).eps)
+        if not self.isrot:
+            self.sin_rot, self.cos_rot = 0, 1
+        angle = (self.cos_rot, self.sin_rot) if self.isrot else None
         coord_lr, coord_hr, _ = resampling.match_patches(model_frame.shape, self.frame.shape, model_frame.wcs,
-                                                        self.frame.wcs, isrot=False)
+                                                        self.frame.wcs, isrot=self.isrot)
         self.lr_shape = (int(coord_lr[0].max() - coord_lr[0].min() + 1), int(coord_lr[1].max() - coord_lr[1].min() + 1))
         self._coord_lr, self._coord_hr = coord_lr, coord_hr
         self.frame_coord = (np.arange(model_frame.Ny), np.arange(model_frame.Nx))
         center_y = (coord_hr[0].max() - coord_hr[0].min() + 1) / 2
         center_x = (coord_hr[1].max() - coord_hr[1].min() + 1) / 2
-        diff_psf = self.build_diffkernel(model_frame, None)
+        diff_psf = self.build_diffkernel(model_frame, angle)
         self.small_axis = self.frame.Nx <= self.frame.Ny          # always True on square frames
+        if self.isrot:
+            return self._match_rotated(model_frame, diff_psf, coord_hr, center_y, center_x, (self_pix / model_pix) ** 2)
         self._fft_shape = fft._get_fft_shape(model_frame.psfs, np.zeros(model_frame.shape), padding=3,
                                              axes=[-2, -1], max=True)
         Fy, Fx = self._fft_shape
@@ -278,6 +281,58 @@ class LowResObservation(Observation):
         C_lr, n_y, n_x = op.shape[:3]
         assert (n_y, n_x) == self.lr_shape
         self._lr_op = np.ascontiguousarray(op.reshape(C_lr, n_y * n_x, Ny * Nx), dtype=np.float32)
+        return self
+
+    def _shift2(self, imgs, shifts, masked_axis):
+        """The reference's two-axis "sinc shift" (observation.py:345-403 with axes = (1, 2)) of a stack imgs [n, Fy, Fx]
+        already on the FFT box: for every entry k of the shift lists the stack moved by (shifts[0][k], shifts[1][k])
+        pixels with Fourier phase ramps (full transform along y, real transform along x), the ramp of `masked_axis`
+        low-passed by zeroing its entries [m//4, -m//4).  Returns [n, K, Fy, Fx]."""
+        from . import interpolation
+        Fy, Fx = self._fft_shape
+        spec = np.fft.rfftn(np.fft.ifftshift(imgs, axes=(1, 2)), axes=(1, 2))
+        ramps = interpolation.mk_shifter((Fy, Fx))
+        phase = [ramps[ax][None, :] ** np.asarray(shifts[ax], dtype=np.float64)[:, None] for ax in (0, 1)]
+        m = phase[masked_axis].shape[1]
+        phase[masked_axis][:, m // 4:-m // 4] = 0
+        spec = spec[:, None] * phase[0][None, :, :, None] * phase[1][None, :, None, :]
+        return np.fft.fftshift(np.fft.irfftn(spec, (Fy, Fx), axes=(2, 3)), axes=(2, 3))
+
+    def _match_rotated(self, model_frame, diff_psf, coord_hr, center_y, center_x, flux_scale):
+        """The rotated branch of `match` (observation.py:483-503): the low-resolution grid is described by its
+        un-rotated rows Y and columns X; row j sees the difference kernel moved by (Y_j cos, Y_j sin), column i the
+        model moved by (-X_i sin, X_i cos), and pixel (j, i) is the product of the two summed over the FFT box
+        (`_render`, observation.py:524-558).  Both factors are circular convolutions on the box, so the whole map is one
+        matrix per band,  op[c, (j, i'), (y, x)] = (R_cj correlated with h_i)[y, x],  h_i = the moved unit model pixel:
+        built with one FFT product per (band, row, column) and handed to the device like the unrotated operator."""
+        if not self.small_axis:
+            raise NotImplementedError("rotated low-resolution frames wider than tall are not supported")
+        n_y, n_x = self.lr_shape
+        if len(coord_hr[0]) != n_y * n_x:
+            raise NotImplementedError("a rotated low-resolution frame must lie entirely inside the model frame "
+                                      "(the reference reshapes its pixel list to the frame, observation.py:486-489)")
+        Yu = ((coord_hr[0] - center_y) * self.cos_rot + (coord_hr[1] - center_x) * self.sin_rot).reshape(n_y, n_x)[:, 0]
+        Xu = ((coord_hr[1] - center_x) * self.cos_rot - (coord_hr[0] - center_y) * self.sin_rot).reshape(n_y, n_x)[0, :]
+        self.Y_unrot, self.X_unrot = Yu, Xu
+        self.shifts = [Yu * self.cos_rot, Yu * self.sin_rot]
+        self.other_shifts = [-self.sin_rot * Xu, self.cos_rot * Xu]
+        self._fft_shape = fft._get_fft_shape(model_frame.psfs, np.zeros(model_frame.shape), padding=3,
+                                             axes=[-2, -1], max=True)
+        Fy, Fx = self._fft_shape
+        Ny, Nx = model_frame.Ny, model_frame.Nx
+        dpad = fft._pad(np.asarray(diff_psf.image, dtype=np.float64), self._fft_shape, axes=(1, 2))
+        R = self._shift2(dpad, self.shifts, 0) * flux_scale                         # [C, n_y, Fy, Fx]
+        self._resconv_op = R.reshape(R.shape[0], n_y, -1).astype(self.frame.dtype)
+        unit = np.zeros((1, Ny, Nx))
+        unit[0, 0, 0] = 1
+        h = self._shift2(fft._pad(unit, self._fft_shape, axes=(1, 2)), self.other_shifts, 1)[0]     # [n_x, Fy, Fx]
+        hf = np.conj(np.fft.rfft2(h[::-1]))                                         # column order flipped (i' = n_x-1-i)
+        C_lr = R.shape[0]
+        op = np.empty((C_lr, n_y, n_x, Ny, Nx), np.float32)
+        for c in range(C_lr):
+            rf = np.fft.rfft2(R[c])                                                 # [n_y, Fy, Fx/2+1]
+            op[c] = np.fft.irfft2(rf[:, None] * hf[None], (Fy, Fx))[:, :, :Ny, :Nx]
+        self._lr_op = np.ascontiguousarray(op.reshape(C_lr, n_y * n_x, Ny * Nx))
         return self
 
     def _window(self):

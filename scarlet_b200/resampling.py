@@ -24,15 +24,29 @@ def match_patches(shape_hr, shape_lr, wcs_hr, wcs_lr, isrot=True, perimeter='ove
     """
     assert perimeter in ['overlap', 'union'], 'perimeter should be either overlap or union.'
     assert wcs_hr is not None and wcs_lr is not None
-    if isrot:
-        raise NotImplementedError("rotated frames are not supported (the reference's rotated branch only runs when "
-                                  "the whole low-resolution frame lies inside the high-resolution one)")
     if np.size(shape_hr) not in (2, 3):
         raise ValueError('Wrong dimensions for reference image')
     if np.size(shape_lr) not in (2, 3):
         raise ValueError('Wrong dimensions for low resolution image')
     Ny_hr, Nx_hr = shape_hr[-2:]
     Ny_lr, Nx_lr = shape_lr[-2:]
+    if isrot:
+        # rotated frames: every low-resolution pixel is a point of its own (resampling.py:53-60), listed row-major
+        rows_lr, cols_lr = [g.ravel() for g in np.indices((Ny_lr, Nx_lr))]
+        rows_hr, cols_hr = np.arange(Ny_hr), np.arange(Nx_hr)
+        ra_lr, dec_lr = _pix2world(wcs_lr, cols_lr, rows_lr)
+        ra_hr, dec_hr = _pix2world(wcs_hr, cols_hr, rows_hr)
+        cols_lr_in_hr, rows_lr_in_hr = _world2pix(wcs_hr, ra_lr, dec_lr)
+        cols_hr_in_lr, rows_hr_in_lr = _world2pix(wcs_lr, ra_hr, dec_hr)
+        inside_lr = ((cols_lr_in_hr >= 0) & (cols_lr_in_hr < Nx_hr + 1) & (rows_lr_in_hr >= 0) & (rows_lr_in_hr < Ny_hr + 1))
+        inside_hr = ((cols_hr_in_lr >= 0) & (cols_hr_in_lr < Nx_lr + 1) & (rows_hr_in_lr >= 0) & (rows_hr_in_lr < Ny_lr + 1))
+        if not inside_lr.any():
+            raise SourceInitError
+        coordhr_hr = (rows_hr[inside_hr], cols_hr[inside_hr])
+        if perimeter == 'overlap':
+            return ((rows_lr[inside_lr], cols_lr[inside_lr]),
+                    (rows_lr_in_hr[inside_lr], cols_lr_in_hr[inside_lr]), coordhr_hr)
+        return (rows_lr, cols_lr), (rows_lr_in_hr, cols_lr_in_hr), coordhr_hr
     if Ny_hr != Nx_hr or Ny_lr != Nx_lr:
         raise NotImplementedError("unrotated multi-resolution matching needs square frames (resampling.py:90-92)")
     rows_hr, cols_hr = np.arange(Ny_hr), np.arange(Nx_hr)

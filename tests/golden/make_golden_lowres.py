@@ -7,8 +7,9 @@ described by the affine WCS stand-in wcs_stub.py (astropy is absent here).  Run 
 
 Extra compat patch (besides ref_shims): numpy >= 1.24 refuses `np.array((a, b))` for arrays of different length
 (observation.py:374 wraps the two 1-D shifters like that); the stand-in returns the object array old numpy made.
-The reference's rotated branch is not exercised: it needs every low-resolution pixel inside the high-resolution
-frame (observation.py:486-489 reshape) and trips over mk_shifter's cache key (interpolation.py:319).
+Case R exercises the reference's rotated branch (10 degrees): it needs every low-resolution pixel inside the
+high-resolution frame (observation.py:486-489 reshape) and a cold operator cache (mk_shifter's cache key ignores
+`real`, interpolation.py:319; repro_rotated_lowres.py shows both outcomes).
 
 `autograd.grad` stand-in for the low-resolution observation: the adjoint of the reference's own linear `_render`,
 taken from its dense matrix (one `_render` call per model pixel).
@@ -45,12 +46,12 @@ psf = scarlet.psf
 CH = ["h0", "h1", "h2", "l0", "l1", "l2", "l3", "l4"]
 
 
-def scene(hr_shape, lr_shape, seed, offset=(0.3, -0.2)):
+def scene(hr_shape, lr_shape, seed, offset=(0.3, -0.2), angle=0.0):
     """frame, hr observation, lr observation, true model, true centres"""
     Cache._cache.clear()
     rng = np.random.default_rng(seed)
     (HY, HX), (LY, LX) = hr_shape, lr_shape
-    whr, wlr = make_pair(hr_shape, lr_shape, scale=4.0, lr_offset=offset)
+    whr, wlr = make_pair(hr_shape, lr_shape, scale=4.0, angle_deg=angle, lr_offset=offset)
     mpsf = psf.generate_psf_image(psf.gaussian, (15, 15), sigma=.9).image.astype(np.float32)
     frame = scarlet.Frame((8, HY, HX), wcs=whr, psfs=mpsf[None], channels=CH)
     hr_psfs = np.array([psf.generate_psf_image(psf.gaussian, (15, 15), sigma=1.2 + .15 * b).image
@@ -82,7 +83,8 @@ def scene(hr_shape, lr_shape, seed, offset=(0.3, -0.2)):
     olr = scarlet.LowResObservation(lr_img, wcs=wlr, psfs=lr_psfs, weights=w_lr, channels=CH[3:])
     olr.match(frame)
     return frame, ohr, olr, model, centers, dict(hr_psfs=hr_psfs, lr_psfs=lr_psfs, mpsf=mpsf, hr_img=hr_img,
-                                                 lr_img=lr_img, w_lr=w_lr, offset=np.array(offset))
+                                                 lr_img=lr_img, w_lr=w_lr, offset=np.array(offset),
+                                                 angle=np.float64(angle))
 
 
 def dump_match(tag, olr, out):
@@ -194,5 +196,26 @@ out["B_model"] = model
 out["B_render"] = olr._render(model)
 out["B_loss"] = np.float64(olr.get_loss(model))
 print("B: fft", olr._fft_shape, "lr", olr.lr_shape, "small_axis", olr.small_axis, "loss", out["B_loss"])
+
+# ---- case R: the low-resolution frame rotated by 10 degrees and entirely inside the high-resolution one (the
+# reference's rotated branch, observation.py:443-454,483-503; it runs with a cold operator cache, see
+# repro_rotated_lowres.py): match + render + loss + adjoint
+frame, ohr, olr, truth, centers, inp = scene((64, 64), (10, 10), seed=13, offset=(0.25, -0.1), angle=10.0)
+assert olr.isrot
+for k, v in inp.items():
+    out["R_" + k] = v
+dump_match("R_", olr, out)
+out["R_diff_psf"] = olr.build_diffkernel(frame, (olr.cos_rot, olr.sin_rot)).image.astype(np.float32)
+model = (truth * rng.uniform(.8, 1.2, truth.shape)).astype(np.float32)
+out["R_model"] = model
+out["R_render"] = olr._render(model)
+out["R_loss"] = np.float64(olr.get_loss(model))
+L = dense_operator(olr, frame)
+y0, x0 = int(olr._coord_lr[0].min()), int(olr._coord_lr[1].min())
+ny, nx = olr.lr_shape
+sub = olr.images[:, y0:y0 + ny, x0:x0 + nx]
+r = (olr.weights ** 2 * (olr._render(model) - sub)).reshape(5, -1).astype(np.float64)
+out["R_grad"] = np.einsum("cq,cqp->cp", r, L).reshape(5, 64, 64)
+print("R: fft", olr._fft_shape, "lr", olr.lr_shape, "small_axis", olr.small_axis, "loss", out["R_loss"])
 np.savez_compressed(os.path.join(HERE, "ref_golden_lowres.npz"), **out)
 print(os.path.getsize(os.path.join(HERE, "ref_golden_lowres.npz")) / 1e6, "MB")

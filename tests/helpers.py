@@ -112,7 +112,9 @@ def lowres_scene(gold, tag, dtype=np.float32):
     from wcs_stub import make_pair
     from oracle import ref_lowres as rl
     hr_img, lr_img = gold[tag + "hr_img"], gold[tag + "lr_img"]
-    whr, wlr = make_pair(hr_img.shape[1:], lr_img.shape[1:], scale=4.0, lr_offset=tuple(gold[tag + "offset"]))
+    angle = float(gold[tag + "angle"]) if tag + "angle" in gold else 0.0
+    whr, wlr = make_pair(hr_img.shape[1:], lr_img.shape[1:], scale=4.0, angle_deg=angle,
+                         lr_offset=tuple(gold[tag + "offset"]))
     chan = ["h0", "h1", "h2", "l0", "l1", "l2", "l3", "l4"]
     frame = rb.Frame((8,) + hr_img.shape[1:], psfs=gold[tag + "mpsf"][None], channels=chan, dtype=dtype)
     frame.wcs = whr

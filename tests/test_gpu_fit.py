@@ -89,6 +89,17 @@ def test_multiple_observations_approximate_L(nat):
     assert_allclose(out["logL"][0, :10], blend.mse, rtol=2e-4)
 
 
+def test_lockstep_rotated_low_resolution_observation(nat):
+    """The same with the low-resolution frame rotated by 10 degrees against the model frame (observation.py:443-454,
+    483-503; fixture R_ of a run of the reference): every iteration against the oracle's restated rotated `_render`."""
+    import os
+    gold = np.load(os.path.join(helpers.GOLD, "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "R_")
+    assert olr.isrot
+    srcs, blend = helpers.lowres_blend(gold, frame, ohr, olr)
+    _lockstep(nat, blend, 6, e_rel=1e-9)
+
+
 def test_lockstep_low_resolution_observation(nat):
     """A high-resolution Observation + a LowResObservation of other bands (observation.py:242-599, row A14): the
     low-resolution planes go through scl_k_lowres (resample-and-convolve operator, residual, transpose), every
