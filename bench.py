@@ -163,17 +163,43 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
-def alg_bytes(comp_off, n_iter=None):
+def alg_bytes(comp_off, n_iter=None, weight_planes=1):
     """Algorithmic bytes per launch of each kernel, summed over the blends of one batch.
     With n_iter: summed over the iterations each blend actually ran (launches differ in active blends)."""
     K = np.diff(comp_off).astype(np.float64)
     N = NY * NX
     w = np.ones_like(K) if n_iter is None else n_iter.astype(np.float64)
-    k1 = 4 * N * (K + 3 * C) + 4 * C * PSF * PSF + 8 * K * C          # S, images, weights in; G out; diff kernel; A, dA
+    Cw = C * weight_planes                                            # 0 when the weights are the scalar 1 (SURVEY 8(d) C_w)
+    k1 = 4 * N * (K + 2 * C + Cw) + 4 * C * PSF * PSF + 8 * K * C     # S, images, weights in; G out; diff kernel; A, dA
     k2 = 12 * K * C + 8 * K * K + 8 * C + 16                          # A, dA in; A out; Gram, loss parts in; logL, L out
     k3 = 4 * N * (2 * K + C) + 8 * K * C                              # S in/out, G in; A in/out
-    it = 4 * N * (2 * K + 2 * C) + 4 * C * PSF * PSF + 8 * K * C      # fused-iteration figure B_iter
+    it = 4 * N * (2 * K + C + Cw) + 4 * C * PSF * PSF + 8 * K * C     # fused-iteration figure B_iter
     return [float((k1 * w).sum()), float((k2 * w).sum()), float((k3 * w).sum())], float((it * w).sum())
+
+
+def bind_near_gpu(local):
+    """Restrict this rank (and the chunk threads it spawns) to the host cores on the GPU's own NUMA node
+    (/sys/bus/pci/devices/<bus id>/local_cpulist), so that the staging buffers allocated afterwards are first touched
+    there and eight ranks do not all stage through node 0.  Returns a description for the bench line."""
+    try:
+        bus = subprocess.check_output(["nvidia-smi", "-i", str(local), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                                      text=True).strip().lower()
+        bus = bus[-12:] if len(bus) > 12 else bus                      # sysfs uses a 4-digit PCI domain
+        base = "/sys/bus/pci/devices/" + bus
+        node = int(open(base + "/numa_node").read())
+        cpus = set()
+        for part in open(base + "/local_cpulist").read().strip().split(","):
+            if part:
+                lo, _, hi = part.partition("-")
+                cpus.update(range(int(lo), int(hi or lo) + 1))
+        have = os.sched_getaffinity(0)
+        use = cpus & have
+        if node < 0 or not use or use == have:
+            return "gpu %d: numa node %d, local cpus %d, allowed %d: affinity left as is" % (local, node, len(cpus), len(have))
+        os.sched_setaffinity(0, use)
+        return "gpu %d: bound to %d cores of numa node %d" % (local, len(use), node)
+    except (OSError, ValueError, subprocess.SubprocessError) as e:
+        return "affinity left as is (%s)" % type(e).__name__
 
 
 def run_b200(args):
@@ -183,6 +209,7 @@ def run_b200(args):
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
+    binding = bind_near_gpu(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     peaks = {}
@@ -275,10 +302,23 @@ def run_b200(args):
     if args.e2e_streams != args.streams:
         bbe = BlendBatch(data["images"], psfs, data["model_psf"], data["centers"], data["bg_rms"],
                          weights=data["weights"], streams=args.e2e_streams)
-    res = bbe._dev.alloc_results(MAX_ITER, morph=True)
-    for a in list(bbe.host.values()) + list(res.values()):
-        if isinstance(a, np.ndarray) and a.nbytes >= 4096:
-            cudart.cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+    # staging buffers allocated page-locked (cudaHostAlloc through torch) AFTER the rank was bound near its GPU, instead
+    # of page-locking whatever pages the allocator had handed out before
+    keep_pinned = []
+
+    def pinned(a):
+        if not isinstance(a, np.ndarray) or a.nbytes < 4096:
+            return a
+        t = torch.empty(a.nbytes, dtype=torch.uint8, pin_memory=True)            # any numpy dtype: a byte buffer, re-viewed
+        v = t.numpy().view(a.dtype).reshape(a.shape)
+        v[...] = a
+        keep_pinned.append(t)
+        return v
+    res = {k: pinned(v) for k, v in bbe._dev.alloc_results(MAX_ITER, morph=True).items()}
+    for k in list(bbe.host.keys()):
+        if k == "psfs":
+            continue
+        bbe.host[k] = pinned(bbe.host[k])
     def e2e_step():
         _, o = bbe.fit_host(MAX_ITER, E_REL, check_every=args.check_every, out=res, morph=True)
         # per-blend result records gathered over NCCL (north_star: NCCL only for results)
@@ -328,7 +368,7 @@ def run_b200(args):
     bb.fit_device(8, 0.0, check_every=1000, serial=True)
     bb.restore()
     fx = bb.fit_device(args.roofline_iters, 0.0, check_every=1000, profile=True, serial=True)
-    per_launch, it_bytes = alg_bytes(comp_off)
+    per_launch, it_bytes = alg_bytes(comp_off, weight_planes=0 if bb.uniform_weights else 1)
     names = ["scl_k_forward_adjoint", "scl_k_lipschitz", "scl_k_prox", "scl_k_converge"]
     kernels = []
     for j in range(3):
@@ -365,9 +405,13 @@ def run_b200(args):
                                 max_iter=MAX_ITER, e_rel=E_REL, mean_iters_per_blend=iters_total / blends_total,
                                 l2="inputs per GPU (%.1f GB) exceed the 126 MB L2" % (bb.h2d_bytes / 1e9),
                                 streams_per_gpu=args.streams,
+                                weights=("an array of ones: recognised at construction as the reference's weights=None "
+                                         "(observation.py:148-151), not stored or uploaded; algorithmic bytes with C_w = 0")
+                                if bb.uniform_weights else "per-pixel array",
                                 psfs="one set per blend, matched on the device" if args.per_blend_psfs else "one shared set",
                                 sharding="blend-parallel, rank r owns blends [r*B,(r+1)*B), no data-path collective",
-                                input_gen_s=t_gen, source_init_s=t_init, failed_sources=bb.n_failed),
+                                input_gen_s=t_gen, source_init_s=t_init, failed_sources=bb.n_failed,
+                                host_binding=binding),
                     pgm_iters_per_sec=iters_total * args.steps / (ms / 1e3),
                     e2e=e2e, gpu_launches=int(launches), roofline=roofline, clocks=clocks)
         if cpu is not None:
@@ -544,9 +588,9 @@ def run_scene(args):
 
 
 # ------------------------------------------------------------------------------------------ config 5 (multi-resolution)
-MULTIRES_WORKLOAD = ("config5: joint fit of a 3-band 128x128 observation (41x41 PSFs) and a 5-band 34x34 LowResObservation "
-                     "(pixel scale 4, 15x15 PSFs, sub-pixel offset, unrotated), %d CombinedExtendedSources, "
-                     "Blend.fit(200, e_rel=1e-2) through the Python surface")
+MULTIRES_WORKLOAD = ("config5: joint fits of a 3-band 128x128 observation (41x41 PSFs) and a 5-band 34x34 LowResObservation "
+                     "(pixel scale 4, 15x15 PSFs, sub-pixel offset, unrotated), %d CombinedExtendedSources per blend, "
+                     "Blend.fit(200, e_rel=1e-2), a batch of blends of one geometry through scarlet.fit_many")
 
 
 def run_multires(args):
@@ -601,47 +645,115 @@ def run_multires(args):
     olr = scarlet.LowResObservation(lr_img, wcs=wlr, psfs=lr_psfs, channels=chan[3:]).match(frame)
     t_match = time.perf_counter() - t1
     bg = [np.ones(3, np.float32), np.ones(5, np.float32)]
-    srcs0 = [scarlet.CombinedExtendedSource(frame, (round(c[0]) - HY / 2, round(c[1]) - HX / 2), [ohr, olr], bg, obs_idx=0)
-             for c in centers]
+    # B blends of one geometry: every blend has its own scene and images; the observations of all blends share the
+    # matched difference kernels and the ONE resample-and-convolve operator of the geometry (335 MB), so the batch runs
+    # its low-resolution planes as matrix products over the blends (csrc/k_lowres.cu: scl_k_lowres_gemm)
+    B = max(1, args.multires_blends)
+
+    def scene(i):
+        r = np.random.default_rng(20260411 + 500 + i)
+        cs = []
+        while len(cs) < ns:
+            c = r.uniform(24, HY - 24, 2)
+            if all(np.hypot(*(c - o)) >= 14 for o in cs):
+                cs.append(c)
+        tr = np.zeros((8, HY, HX), np.float32)
+        for c in cs:
+            re, q, pa = r.uniform(2, 4), r.uniform(.6, 1), r.uniform(0, np.pi)
+            u = (xx - c[1]) * np.cos(pa) + (yy - c[0]) * np.sin(pa)
+            v = (-(xx - c[1]) * np.sin(pa) + (yy - c[0]) * np.cos(pa)) / q
+            sed = r.dirichlet(np.ones(8)) * 10 ** r.uniform(3, 4)
+            tr += (sed[:, None, None] * np.exp(-np.hypot(u, v) / re)[None]).astype(np.float32)
+        o_hr, o_lr = copy.copy(ohr), copy.copy(olr)
+        o_hr.images = (ohr.render(tr) + r.normal(0, 1, (3, HY, HX))).astype(np.float32)
+        li = r.normal(0, 1, (5, LY, LX)).astype(np.float32)
+        li[:, ys, xs] += olr._render(tr)
+        o_lr.images = li
+        return cs, o_hr, o_lr
+
+    blends0 = []
+    for i in range(B):
+        cs, o_hr, o_lr = (centers, ohr, olr) if i == 0 else scene(i)
+        srcs = [scarlet.CombinedExtendedSource(frame, (round(c[0]) - HY / 2, round(c[1]) - HX / 2), [o_hr, o_lr], bg, obs_idx=0)
+                for c in cs]
+        blends0.append((srcs, [o_hr, o_lr]))
     t_setup = time.perf_counter() - t0
     from scarlet_b200.blend import pack_blends
     ms_list, its, launches = [], [], 0
     e2e_list = []
     for i in range(args.warmup + args.steps):
-        srcs = [copy.copy(s) for s in srcs0]
-        for s, s0 in zip(srcs, srcs0):
-            s._sed, s._morph = s0._sed.copy(), s0._morph.copy()
-        blend = scarlet.Blend(srcs, [ohr, olr])
+        blends = []
+        for srcs0, obs in blends0:
+            srcs = [copy.copy(s) for s in srcs0]
+            for s, s0 in zip(srcs, srcs0):
+                s._sed, s._morph = s0._sed.copy(), s0._morph.copy()
+            blends.append(scarlet.Blend(srcs, obs))
         t0 = time.perf_counter()
-        infos = scarlet.fit_many([blend], MAX_ITER, E_REL)
+        infos = scarlet.fit_many(blends, MAX_ITER, E_REL)
         dt = time.perf_counter() - t0
         if i >= args.warmup:
-            ms_list.append(infos[0]["device_ms"]); its.append(blend.it); launches += infos[0]["launches"]
+            ms_list.append(sum(f["device_ms"] for f in infos)); its.append(float(np.mean([b.it for b in blends])))
+            launches += sum(f["launches"] for f in infos)
             e2e_list.append(dt)
-    packed = pack_blends([blend])
+    blend = blends[0]
+    packed = pack_blends(blends)
     h2d = sum(v.nbytes for v in packed.values() if isinstance(v, np.ndarray)) + sum(
         v.nbytes for v in (packed["lr"] or {}).values() if isinstance(v, np.ndarray))
     ms = float(np.mean(ms_list))
-    K = len(srcs0)
-    print(json.dumps(dict(
-        metric=METRIC, value=1e3 / ms, unit=UNIT, n_gpus=1, steps=args.steps, warmup=args.warmup, ms_per_step=ms,
+    K = sum(len(s) for s, _ in blends0)
+    line = dict(
+        metric=METRIC, value=B * 1e3 / ms, unit=UNIT, n_gpus=1, steps=args.steps, warmup=args.warmup, ms_per_step=ms,
         higher_is_better=True, scaling="weak", vs_baseline=None, dtype="f32", data="synthetic",
-        config=dict(workload=MULTIRES_WORKLOAD % K, components=K, max_iter=MAX_ITER, e_rel=E_REL,
+        config=dict(workload=MULTIRES_WORKLOAD % ns, blends=B, components=K, max_iter=MAX_ITER, e_rel=E_REL,
                     iters_per_fit=float(np.mean(its)), lr_operator_bytes=int(olr._lr_op.nbytes),
                     lowres_match_s=t_match, setup_s=t_setup,
-                    note="scene mode (128x128 frame + 41x41 PSF exceeds one convolution tile); the low-resolution "
-                         "operator (335 MB) is streamed twice per plane and iteration"),
-        pgm_iters_per_sec=float(np.mean(its)) / (ms / 1e3),
-        e2e=dict(value=1.0 / float(np.mean(e2e_list)), unit=UNIT, h2d_bytes_per_step=int(h2d),
-                 d2h_bytes_per_step=int(4 * K * (HY * HX + 8)), ms_per_step=1e3 * float(np.mean(e2e_list))),
-        gpu_launches=int(launches), logL_first_last=[float(blend.mse[0]), float(blend.mse[-1])],
-        cpu_baseline=None, cpu_baseline_note="the oracle's adjoint of the low-resolution render needs its dense matrix "
-        "(16384 renders at this size); parity at fixture size is tests/test_gpu_fit.py::test_low_resolution_*")))
+                    note="scene mode (128x128 frame + 41x41 PSF exceeds one convolution tile); the blends share one "
+                         "geometry: the low-resolution operator is applied as a matrix product over the blends"),
+        pgm_iters_per_sec=B * float(np.mean(its)) / (ms / 1e3),
+        e2e=dict(value=B / float(np.mean(e2e_list)), unit=UNIT, h2d_bytes_per_step=int(h2d),
+                 d2h_bytes_per_step=int(4 * K * (HY * HX + 8)), ms_per_step=1e3 * float(np.mean(e2e_list)),
+                 note="through the Python surface: pack (host), upload incl. the operator, fit, download, unpack"),
+        gpu_launches=int(launches), logL_first_last=[float(blend.mse[0]), float(blend.mse[-1])])
+    if not args.no_cpu:
+        line["cpu_baseline"] = multires_cpu_baseline()
+    print(json.dumps(line))
+
+
+def multires_cpu_baseline(n_gpu=64):
+    """The CPU oracle on a multi-resolution fit, timed at the size at which its adjoint is tractable (the fixture of
+    tests/golden/make_golden_lowres.py: 3-band 40x40 + 5-band 12x12, 3 CombinedExtendedSources; the oracle needs the
+    dense matrix of `_render`, 1600 renders at that size, 16384 at 128x128), next to the device on the same scene, as
+    a batch of `n_gpu` copies: a like-for-like ratio at that size, stated as such."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import helpers
+    from scarlet_b200 import _native as nat
+    gold = np.load(os.path.join(ROOT, "tests", "golden", "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "A_")
+    srcs, blend = helpers.lowres_blend(gold, frame, ohr, olr)
+    olr.dense_operator(frame.shape)                       # one-off, not timed (the reference gets it from autograd)
+    packs = helpers.pack([blend] * n_gpu)
+    t0 = time.perf_counter()
+    blend.fit(MAX_ITER, E_REL)
+    t_cpu = time.perf_counter() - t0
+    bt = nat.Batch(**packs)
+    bt.snapshot()
+    bt.fit(MAX_ITER, E_REL)                               # warm-up
+    bt.restore()
+    info = bt.fit(MAX_ITER, E_REL)
+    out = bt.download()
+    bt.close()
+    return dict(value=1.0 / t_cpu, unit=UNIT, cores=1, kind="port",
+                sample="ONE fit of the fixture-size scene (3-band 40x40 + 5-band 12x12, 3 sources, %d iterations) with the "
+                       "CPU oracle on one core: %.2f s; NOT the 128x128 workload of this line" % (blend.it, t_cpu),
+                same_size_device=dict(value=n_gpu / (info["device_ms"] / 1e3), unit=UNIT, blends=n_gpu,
+                                      iterations=int(out["n_iter"][0]),
+                                      note="the same scene as a batch of %d copies on the device" % n_gpu))
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--multires-sources", type=int, default=6)
+    ap.add_argument("--multires-blends", type=int, default=128, help="config5: blends of one geometry in the batch")
     ap.add_argument("--workload", default="config3", choices=["config3", "config4", "config5"])
     ap.add_argument("--scene-size", type=int, default=512)
     ap.add_argument("--scene-sources", type=int, default=200)

@@ -315,10 +315,16 @@ int scl_batch_render_components(scl_batch* batch, int k0, int nk, float* out, vo
  * CTAs: 0 gradient step, 1 centre + symmetry, 2 level list, 3 monotonic sweep, 4 normalise/write-back) to a device
  * counter; the call returns the sums so far in out8 (may be NULL) and clears them. */
 int scl_batch_phase_clocks(scl_batch* batch, int enable, unsigned long long* out8);
+/* How the host waits for the batch's stream (polls of the active count, end of fit, copies): 0 (default) spins on
+ * the stream -- lowest latency for one batch driven by one thread; 1 sleeps on a blocking-sync event, for hosts where
+ * many ranks and chunk threads share the cores (a spinning waiter per stream starves the staging copies). */
+int scl_batch_wait_mode(scl_batch* batch, int blocking);
 /* Test switches (no counterpart in the reference).  bit 0: the scene-mode monotonic sweep visits every level instead of
  * stopping at the first three consecutive levels without a positive pixel (the results are bit-identical; the
  * tests compare the two).  bit 1: scene mode forms S S^T by the dense tiled contraction instead of per pair of
- * overlapping footprint boxes (same products; the sums differ in their last bits). */
+ * overlapping footprint boxes (same products; the sums differ in their last bits).  bit 2 / bit 3: low-resolution planes
+ * always by the per-blend kernels / always by the kernels blocked over 64 blends (default: blocked from 16 blends of
+ * one geometry on). */
 int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
 

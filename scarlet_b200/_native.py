@@ -688,6 +688,10 @@ class Batch:
         _check(lib().scl_batch_phase_clocks(self._h, int(bool(enable)), out))
         return [int(v) for v in out]
 
+    def wait_mode(self, blocking):
+        """Host waits sleep on a blocking-sync event (True) instead of spinning on the stream (False, default)."""
+        _check(lib().scl_batch_wait_mode(self._h, int(bool(blocking))))
+
     def debug_flags(self, flags):
         """Test switches (include/scarlet_b200.h: scl_batch_debug_flags)."""
         _check(lib().scl_batch_debug_flags(self._h, int(flags)))

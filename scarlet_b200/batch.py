@@ -40,6 +40,8 @@ class _Chunks:
         self._psf_slices = {}
         self.streams = [_native.stream_create() for _ in range(len(self.bounds) - 1)]
         self.parts = [_native.Batch(stream=s, **self._slice(host, i)) for i, s in enumerate(self.streams)]
+        for part in self.parts:
+            part.wait_mode(True)            # several host threads per GPU (and several ranks per host): sleep, do not spin
         # the CUDA device is a per-thread setting: the worker threads adopt the device of the thread that built the batch
         self.pool = ThreadPoolExecutor(len(self.parts), initializer=_native.device_set, initargs=(_native.device_get(),))
         self.B, self.K = B, int(off[-1])
@@ -254,6 +256,11 @@ class BlendBatch:
             flags &= ~np.uint32(_native.F_MONOTONIC)
         self.kind = kind
         wts = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
+        # A weight array that is 1 everywhere is the reference's `weights=None` (observation.py:148-151: W = 1), bit for
+        # bit: checked once here, and then neither stored on the device nor uploaded with every fit
+        self.uniform_weights = wts is not None and wts.size > 0 and float(wts.min()) == 1.0 and float(wts.max()) == 1.0
+        if self.uniform_weights:
+            wts = None
 
         def host_dict(keep_src, kept, morph, sed=sed):
             cnt = np.bincount(owner[keep_src], minlength=B)[kept]

@@ -127,3 +127,130 @@ scl_k_lowres_render(const float* __restrict__ model, const float* __restrict__ o
     acc = block_sum<float>(acc, red);
     if (threadIdx.x == 0) out[((size_t)n * C + c) * n_lr + q] = acc;
 }
+
+// ---- blocked over blends ----------------------------------------------------------------------------------------------
+// Many blends that share one geometry share the operator: R[q][b] = sum_p L[q][p] M[p][b] and
+// G[p][b] = sum_q L[q][p] r[q][b] are matrix products with the blends as their third dimension, so an operator tile
+// fetched once serves 64 blends (the per-blend kernels above stream the whole operator for every blend: 379 GB per
+// iteration for 1000 blends of config 5).  Plain fp32 FMA on 64 x 64 x 16 tiles, 4 x 4 outputs per thread (fp32 parity:
+// no reduced-precision tensor path); k ascending inside a tile, so results do not depend on scheduling.
+//   ADJ = false: m = low-resolution pixel q, k = model pixel p;  epilogue: d = W (R - I), r = W d, d2 = d^2
+//   ADJ = true:  m = model pixel p, k = low-resolution pixel q;  epilogue: G[b][P0 + c][p]
+// grid: (ceil(M / 64), Plr, ceil(nB / 64)), 256 threads.  lr_op: ONE geometry [Plr][n_lr][N].
+template <bool ADJ>
+__global__ void __launch_bounds__(256)
+scl_k_lowres_gemm(const float* __restrict__ lr_op, const float* __restrict__ X, int x_planes, int x_is_model,
+                  const float* __restrict__ lr_images, const float* __restrict__ lr_weights,
+                  const int* __restrict__ active, const int* __restrict__ blend_list, int nB,
+                  float* __restrict__ r_lr, float* __restrict__ d2_lr, float* __restrict__ G,
+                  SclPlanes pl, int P0, int Plr, int PG, int N, int n_lr)
+{
+    __shared__ __align__(16) float As[16][64 + 4];
+    __shared__ __align__(16) float Bs[16][64 + 4];
+    __shared__ int sb[64];
+    const int c = blockIdx.y, m0 = blockIdx.x * 64, n0 = blockIdx.z * 64;
+    const int Mdim = ADJ ? N : n_lr, Kdim = ADJ ? n_lr : N;
+    const float* L = lr_op + (size_t)c * n_lr * N;
+    if (threadIdx.x < 64) sb[threadIdx.x] = (n0 + threadIdx.x < nB) ? blend_list[n0 + threadIdx.x] : -1;
+    __syncthreads();
+    // the operand that carries the blends: forward the model plane of LR band c, adjoint the residual r
+    const int xp = ADJ ? c : (x_is_model ? scl_lr_band(pl, P0 + c) : c);
+    const size_t xlen = ADJ ? (size_t)n_lr : (size_t)N;              // length of one blend's vector along k
+    const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) acc[i][j] = 0.f;
+    // loaders: 64 x 16 elements per tile and operand, 4 per thread
+    const int lr_ = threadIdx.x >> 2, lc = (threadIdx.x & 3) * 4;     // (row 0..63, k offset 0,4,8,12): rows contiguous in k
+    const int ar = threadIdx.x >> 4, ac = (threadIdx.x & 15) * 4;     // adjoint operator tile: (k 0..15, m offset): contiguous in m
+    const bool vec = (N & 3) == 0;                                    // 16-byte operator loads
+    for (int k0 = 0; k0 < Kdim; k0 += 16) {
+        if (!ADJ) {
+            // As[k][m] = L[m0 + m][k0 + k]
+            const int q = m0 + lr_, k = k0 + lc;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (q < n_lr) {
+                if (vec && k + 3 < N) v = *reinterpret_cast<const float4*>(L + (size_t)q * N + k);
+                else {
+                    if (k < N) v.x = L[(size_t)q * N + k];
+                    if (k + 1 < N) v.y = L[(size_t)q * N + k + 1];
+                    if (k + 2 < N) v.z = L[(size_t)q * N + k + 2];
+                    if (k + 3 < N) v.w = L[(size_t)q * N + k + 3];
+                }
+            }
+            As[lc][lr_] = v.x; As[lc + 1][lr_] = v.y; As[lc + 2][lr_] = v.z; As[lc + 3][lr_] = v.w;
+        } else {
+            // As[k][m] = L[k0 + k][m0 + m]
+            const int q = k0 + ar, p = m0 + ac;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (q < n_lr) {
+                if (vec && p + 3 < N) v = *reinterpret_cast<const float4*>(L + (size_t)q * N + p);
+                else {
+                    if (p < N) v.x = L[(size_t)q * N + p];
+                    if (p + 1 < N) v.y = L[(size_t)q * N + p + 1];
+                    if (p + 2 < N) v.z = L[(size_t)q * N + p + 2];
+                    if (p + 3 < N) v.w = L[(size_t)q * N + p + 3];
+                }
+            }
+            *reinterpret_cast<float4*>(&As[ar][ac]) = v;
+        }
+        {
+            // Bs[k][n] = x_b[k0 + k] of blend sb[n]
+            const int b = sb[lr_];
+            const float* xb = b >= 0 ? X + ((size_t)b * x_planes + xp) * xlen : nullptr;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const int k = k0 + lc + u;
+                Bs[lc + u][lr_] = (xb && k < Kdim) ? xb[k] : 0.f;
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+            const float4 bq = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {bq.x, bq.y, bq.z, bq.w};
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+#pragma unroll
+                for (int j = 0; j < 4; j++) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int b = sb[tx * 4 + j];
+        if (b < 0 || !active[b]) continue;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int m = m0 + ty * 4 + i;
+            if (m >= Mdim) continue;
+            if (!ADJ) {
+                const size_t idx = ((size_t)b * Plr + c) * n_lr + m;
+                const float w = lr_weights ? lr_weights[idx] : 1.f;
+                const float d = w * (acc[i][j] - lr_images[idx]);
+                r_lr[idx] = w * d;
+                d2_lr[idx] = d * d;
+            } else {
+                G[((size_t)b * PG + P0 + c) * N + m] = acc[i][j];
+            }
+        }
+    }
+}
+
+// loss of every (blend, LR plane): 0.5 sum_q d2, q ascending per thread, fixed combination.  grid (Plr, nB)
+extern "C" __global__ void __launch_bounds__(256)
+scl_k_lowres_loss(const float* __restrict__ d2_lr, const int* __restrict__ active, const int* __restrict__ blend_list,
+                  double* __restrict__ loss_out, int Plr, int n_lr, int loss_stride, int loss_off)
+{
+    __shared__ double red[32];
+    const int c = blockIdx.x, b = blend_list[blockIdx.y];
+    if (!active[b]) return;
+    const float* d2 = d2_lr + ((size_t)b * Plr + c) * n_lr;
+    double loss = 0.0;
+    for (int q = threadIdx.x; q < n_lr; q += blockDim.x) loss += (double)d2[q];
+    loss = block_sum<double>(loss, red);
+    if (threadIdx.x == 0) loss_out[(size_t)b * loss_stride + loss_off + c] = 0.5 * loss;
+}

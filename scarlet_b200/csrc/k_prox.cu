@@ -522,6 +522,7 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
 
 extern "C" __global__ void __launch_bounds__(SCL_PROX_THREADS, 6)
 scl_k_prox(SclProxArgs a) { scl_prox_body<SCL_PROX_THREADS>(a); }
+
 // scene mode (working set in HBM, hundreds of thousands of pixels per component): wider CTAs
 extern "C" __global__ void __launch_bounds__(SCL_PROX_WIDE, SCL_WIDE_MIN)
 scl_k_prox_wide(SclProxArgs a) { scl_prox_body<SCL_PROX_WIDE>(a); }

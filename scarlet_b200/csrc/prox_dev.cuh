@@ -479,9 +479,12 @@ __device__ void scl_mono_build(const SclMonoWork& wk, int Ny, int Nx, int cy, in
 // (Processing the passes of one level two at a time -- two pixels per lane -- was measured and is not faster: the
 // warp is bound by its instruction count, not by the number of dependent steps.)
 #define SCL_MONO_IDLE 0xffffffffu
+// R: weight-ring depth (passes of look-ahead), RL: entry-ring depth (power of two, multiple of 4, > R + 4); scratch =
+// R * 1024 + RL * 128 bytes.
+template <int R = SCL_MONO_RING, int RL = SCL_MONO_ENTRIES>
 __device__ SCL_STREAM_INLINE void scl_monotonic_f32_stream(float* X, int Nx, const unsigned* __restrict__ passes, int npass,
                                                       int pbits, const float* __restrict__ wt9, float thresh, void* scratch) {
-    constexpr int R = SCL_MONO_RING, RL = SCL_MONO_ENTRIES;
+    static_assert((RL & (RL - 1)) == 0 && RL % 4 == 0 && RL > R + 4, "entry ring too small");
     const float omt = 1.f - thresh;
     const int lane = threadIdx.x & 31;
     const unsigned pmask = (1u << pbits) - 1u;

@@ -122,6 +122,37 @@ def test_scene_lockstep_low_resolution(nat, approx):
     _lockstep(nat, blend, 6, e_rel=1e-9, approximate_L=approx, scene_mode=1)
 
 
+@pytest.mark.parametrize("scene", [0, 1])
+def test_low_resolution_planes_blocked_over_blends(nat, scene):
+    """Blends that share a geometry: the low-resolution planes as matrix products over the blends (operator tiles
+    reused by 64 blends, scl_k_lowres_gemm) against the per-blend kernels, and against the oracle."""
+    import os
+    gold = np.load(os.path.join(helpers.GOLD, "ref_golden_lowres.npz"))
+    frame, ohr, olr = helpers.lowres_scene(gold, "A_")
+    blends = []
+    for i in range(3):
+        srcs, bl = helpers.lowres_blend(gold, frame, ohr, olr)
+        for c in bl.components:                    # three different states of the same scene
+            c.sed = (c.sed * (1 + .05 * i)).astype(c.sed.dtype)
+        blends.append(bl)
+    packs = helpers.pack(blends)
+    outs = []
+    for flags in (4, 8):
+        bt = nat.Batch(scene_mode=scene, **packs)
+        bt.debug_flags(flags)
+        bt.fit(6, 1e-9)
+        outs.append(bt.download())
+        bt.close()
+    a, b = outs
+    assert_allclose(b["logL"], a["logL"], rtol=5e-6)
+    assert_array_equal(b["center"], a["center"])
+    assert_allclose(b["morph"], a["morph"], rtol=0, atol=1e-5)
+    for i, bl in enumerate(blends):
+        for _ in range(6):
+            bl.step(1e-9)
+        assert_allclose(b["logL"][i, :6], bl.mse, rtol=1e-4)
+
+
 def test_low_resolution_free_running_vs_reference(nat):
     """The same scene free-running against the reference's own 12 iterations (make_golden_lowres.py)."""
     import os
