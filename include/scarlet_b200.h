@@ -120,6 +120,18 @@ int scl_threshold_f32(float* x, int n, int Ny, int Nx, int apply, double* thresh
  * tap sits at window offset (y0, x0).  x, out float32 [n][Ny][Nx]. */
 int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const double* ky, const int32_t* y0, int Ly,
                      const double* kx, const int32_t* x0, int Lx, void* stream);
+/* The same operators on caller-owned DEVICE arrays (SURVEY 8(b) "Ownership": no hidden host<->device copies): every
+ * pointer is a device pointer, the call is ordered on `stream` and returns without synchronising.  Centres cannot be
+ * validated on the host; an image whose centre lies outside the frame is left untouched.  Single-tile frames for the
+ * convolution (Ny, Nx <= 128 - ker_half); the kernel spectra are the device copy of what scl_convolve_f32 takes. */
+int scl_prox_weighted_monotonic_f32_dev(float* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev, float thresh, void* stream);
+int scl_prox_weighted_monotonic_f64_dev(double* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev, double thresh, void* stream);
+int scl_measure_f32_dev(const float* x_dev, int n, int Ny, int Nx, int32_t* centers_dev, double* shifts_dev,
+                        const float* psf_dev, int ph, int pw, int do_max_pixel, int do_centroid, void* stream);
+int scl_convolve_f32_dev(const float* model_dev, float* out_dev, int n, int C, int Ny, int Nx, const float* spec_dev,
+                         int n_ker, const int32_t* ker_idx_dev, int adjoint, void* stream);
+/* (the symmetry operator on device arrays: scl_prox_symmetry_noalloc_f32 below) */
+
 /* No counterpart in the reference: added for callers that may not allocate
  * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).
  * scl_prox_symmetry_f32 on caller-owned DEVICE arrays, stream-ordered, no host<->device copy, no synchronisation and no

@@ -220,20 +220,33 @@ int check_shape(int Ny, int Nx, bool allow_big = false) {
 }
 
 
+// device core: x [n][Ny][Nx] and centers [n][2] are DEVICE arrays; stream-ordered, no copies, no synchronisation
+template <typename T, bool NEAREST>
+static int launch_monotonic(T* dx, int n, int Ny, int Nx, const int32_t* dcenters, T thresh, cudaStream_t s) {
+    int rc = check_shape(Ny, Nx, true);
+    if (rc) return rc;
+    if ((rc = ensure_globals())) return rc;
+    const size_t msm = (size_t)Ny * Nx * sizeof(T) + (Nx + 1) * sizeof(T) + 32 + SCL_MONO_STREAM_BYTES;
+    const int in_place = msm > 200 * 1024;
+    Tables t;
+    if ((rc = get_tables(Ny, Nx, &t))) return rc;
+    if (in_place)
+        scl_k_monotonic<T, NEAREST><<<n, SCL_THREADS, 0, s>>>(dx, dcenters, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 1);
+    else
+        scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, msm, s>>>(dx, dcenters, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 0);
+    CK(cudaGetLastError());
+    return SCL_OK;
+}
+
 template <typename T, bool NEAREST>
 static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T thresh, void* stream) {
     if (n == 0) return SCL_OK;
     if (!x || !centers || n < 0) return fail(SCL_E_ARG, "bad argument%s%s");
     int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
-    if ((rc = ensure_globals())) return rc;
     for (int i = 0; i < n; i++)
         if (centers[2 * i] < 0 || centers[2 * i] >= Ny || centers[2 * i + 1] < 0 || centers[2 * i + 1] >= Nx)
             return fail(SCL_E_ARG, "center outside the image%s%s");
-    const size_t msm = (size_t)Ny * Nx * sizeof(T) + (Nx + 1) * sizeof(T) + 32 + SCL_MONO_STREAM_BYTES;
-    const int in_place = msm > 200 * 1024;
-    Tables t;
-    if ((rc = get_tables(Ny, Nx, &t))) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     size_t N = (size_t)Ny * Nx;
     DevBuf<T> dx;
@@ -242,11 +255,7 @@ static int run_monotonic(T* x, int n, int Ny, int Nx, const int32_t* centers, T 
     CK(dc.alloc(2 * (size_t)n));
     CK(dx.up(x, s));
     CK(dc.up(centers, s));
-    if (in_place)
-        scl_k_monotonic<T, NEAREST><<<n, SCL_THREADS, 0, s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 1);
-    else
-        scl_k_monotonic<T, NEAREST><<<n, SCL_PROX_THREADS, msm, s>>>(dx.p, dc.p, Ny, Nx, thresh, t.wtab, t.ctab, t.plan(), 0);
-    CK(cudaGetLastError());
+    if ((rc = launch_monotonic<T, NEAREST>(dx.p, n, Ny, Nx, dc.p, thresh, s))) return rc;
     CK(dx.down(x, s));
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
@@ -592,6 +601,56 @@ int scl_resample_f32(const float* x, float* out, int n, int Ny, int Nx, const do
     CK(cudaStreamSynchronize(s));
     return SCL_OK;
 }
+
+// ---- the array-level operators on caller-owned DEVICE arrays: stream-ordered, no host<->device copies, no
+// synchronisation (SURVEY 8(b) "Ownership").  Centres live on the device and cannot be validated here: the kernels
+// leave an image whose centre is outside the frame untouched.
+extern "C" {
+
+int scl_prox_weighted_monotonic_f32_dev(float* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev, float thresh, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x_dev || !centers_dev || n < 0) return fail(SCL_E_ARG, "bad argument%s%s");
+    return launch_monotonic<float, false>(x_dev, n, Ny, Nx, centers_dev, thresh, (cudaStream_t)stream);
+}
+int scl_prox_weighted_monotonic_f64_dev(double* x_dev, int n, int Ny, int Nx, const int32_t* centers_dev, double thresh, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x_dev || !centers_dev || n < 0) return fail(SCL_E_ARG, "bad argument%s%s");
+    return launch_monotonic<double, false>(x_dev, n, Ny, Nx, centers_dev, thresh, (cudaStream_t)stream);
+}
+
+int scl_measure_f32_dev(const float* x_dev, int n, int Ny, int Nx, int32_t* centers_dev, double* shifts_dev,
+                        const float* psf_dev, int ph, int pw, int do_max, int do_centroid, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!x_dev || !centers_dev || !shifts_dev || n < 0 || (do_centroid && (!psf_dev || ph < 1 || pw < 1)))
+        return fail(SCL_E_ARG, "bad argument%s%s");
+    int rc = check_shape(Ny, Nx, true);
+    if (rc) return rc;
+    if ((rc = ensure_globals())) return rc;
+    const size_t N = (size_t)Ny * Nx;
+    const int in_place = N * sizeof(float) > 200 * 1024;
+    scl_k_measure<<<n, SCL_THREADS, in_place ? 0 : N * sizeof(float), (cudaStream_t)stream>>>(
+        x_dev, centers_dev, shifts_dev, Ny, Nx, psf_dev, ph, pw, do_max, do_centroid, in_place);
+    CK(cudaGetLastError());
+    return SCL_OK;
+}
+
+int scl_convolve_f32_dev(const float* model_dev, float* out_dev, int n, int C, int Ny, int Nx, const float* spec_dev,
+                         int n_ker, const int32_t* ker_idx_dev, int adjoint, void* stream) {
+    if (n == 0) return SCL_OK;
+    if (!model_dev || !out_dev || !ker_idx_dev || n < 0 || C < 1 || (n_ker > 0 && !spec_dev))
+        return fail(SCL_E_ARG, "bad argument%s%s");
+    if (C > SCL_MAX_BANDS) return fail(SCL_E_LIMIT, "1 <= C <= 8 bands supported%s%s");
+    if (Ny > SCL_FFT || Nx > SCL_FFT)
+        return fail(SCL_E_LIMIT, "frame larger than the 128x128 convolution tile: use scl_convolve_f32 with ker_half%s%s");
+    int rc = ensure_globals();
+    if (rc) return rc;
+    scl_k_convolve<<<dim3(C, n), SCL_THREADS, kFwdSmem, (cudaStream_t)stream>>>(
+        model_dev, reinterpret_cast<const float2*>(spec_dev), ker_idx_dev, out_dev, C, Ny, Nx, adjoint);
+    CK(cudaGetLastError());
+    return SCL_OK;
+}
+
+}  // extern "C"
 
 #include "api_batch.inc"
 #include "api_noalloc.inc"

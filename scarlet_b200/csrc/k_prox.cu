@@ -660,6 +660,10 @@ scl_k_monotonic(T* __restrict__ imgs, const int* __restrict__ centers, int Ny, i
     const int N = Ny * Nx;
     const size_t pad = (((size_t)Nx + 1) * sizeof(T) + 15) & ~(size_t)15;
     T* g = imgs + (size_t)blockIdx.x * N;
+    {   // the device-pointer entry points cannot validate centres on the host: an image with a centre outside stays as is
+        const int cy_ = centers[2 * blockIdx.x], cx_ = centers[2 * blockIdx.x + 1];
+        if (cy_ < 0 || cy_ >= Ny || cx_ < 0 || cx_ >= Nx) return;
+    }
     if (in_place) {
         // images beyond the shared-memory limit: the level loop works on the image where it lies (HBM / L2)
         scl_monotonic_hbm<T, NEAREST>(g, Ny, Nx, centers[2 * blockIdx.x], centers[2 * blockIdx.x + 1], wtab, ctab, thresh);
@@ -930,6 +934,7 @@ scl_k_measure(const float* __restrict__ imgs, int* __restrict__ centers, double*
     if (!in_place) for (int p = threadIdx.x; p < N; p += blockDim.x) smem_f[p] = g[p];
     if (threadIdx.x == 0) { sc[0] = centers[2 * blockIdx.x]; sc[1] = centers[2 * blockIdx.x + 1]; ss[0] = ss[1] = 0.0; }
     __syncthreads();
+    if (sc[0] < 0 || sc[0] >= Ny || sc[1] < 0 || sc[1] >= Nx) return;       // see scl_k_monotonic
     if (do_max) { scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc); __syncthreads(); }
     if (do_centroid) { int cy = sc[0], cx = sc[1]; __syncthreads(); scl_centroid(X, Ny, Nx, psf, ph, pw, cy, cx, sc, ss, red); }
     if (threadIdx.x == 0) {

@@ -89,3 +89,52 @@ def test_noalloc_rejects_what_the_static_array_cannot_hold(nat):
     torch.cuda.synchronize()
     with pytest.raises(ValueError):
         nat.prox_symmetry_noalloc(dx.data_ptr(), 4, 64, 64, dc.data_ptr(), None, "kspace")
+
+
+def test_device_pointer_operators_match_host_pointer_ones(nat):
+    """scl_*_dev (SURVEY 8(b) "Ownership": caller-owned device buffers, no hidden copies): monotonic sweep (bit-exact),
+    max_pixel / centroid (exact centres) and the single-tile convolution on torch device tensors against the
+    host-pointer entry points."""
+    import ctypes
+    import torch
+    dev = torch.device("cuda:0")
+    L = nat.lib()
+    rng = np.random.default_rng(31)
+    n, Ny, Nx = 6, 64, 64
+    x = rng.random((n, Ny, Nx)).astype(np.float32)
+    centers = np.stack([rng.integers(3, 61, n), rng.integers(3, 61, n)], axis=1).astype(np.int32)
+    want = x.copy()
+    nat.prox_weighted_monotonic(want, centers, 0.1)
+    dx, dc = torch.from_numpy(x.copy()).to(dev), torch.from_numpy(centers).to(dev)
+    p = lambda t: ctypes.c_void_p(t.data_ptr())          # noqa: E731
+    nat._check(L.scl_prox_weighted_monotonic_f32_dev(p(dx), n, Ny, Nx, p(dc), ctypes.c_float(0.1), None))
+    torch.cuda.synchronize()
+    assert_array_equal(dx.cpu().numpy(), want)
+    x64 = x.astype(np.float64)
+    want64 = x64.copy()
+    nat.prox_weighted_monotonic(want64, centers, 0.0)
+    dx64 = torch.from_numpy(x64).to(dev)
+    nat._check(L.scl_prox_weighted_monotonic_f64_dev(p(dx64), n, Ny, Nx, p(dc), ctypes.c_double(0.0), None))
+    torch.cuda.synchronize()
+    assert_array_equal(dx64.cpu().numpy(), want64)
+    # measure
+    psf = np.exp(-((np.arange(15) - 7)[:, None] ** 2 + (np.arange(15) - 7)[None, :] ** 2) / 4.0).astype(np.float32)
+    c_want, s_want = nat.measure(x, centers, psf, True, True)
+    dc2, ds = torch.from_numpy(centers.copy()).to(dev), torch.zeros((n, 2), dtype=torch.float64, device=dev)
+    dxm, dpsf = torch.from_numpy(x).to(dev), torch.from_numpy(psf).to(dev)
+    nat._check(L.scl_measure_f32_dev(p(dxm), n, Ny, Nx, p(dc2), p(ds), p(dpsf), 15, 15, 1, 1, None))
+    torch.cuda.synchronize()
+    assert_array_equal(dc2.cpu().numpy(), c_want)
+    assert_allclose(ds.cpu().numpy(), s_want, rtol=0, atol=1e-12)
+    # convolution
+    ker = rng.random((2, 15, 15)).astype(np.float32)
+    spec = nat.kernel_spectrum(ker, Ny, Nx)
+    model = rng.random((3, 2, Ny, Nx)).astype(np.float32)
+    idx = np.tile(np.arange(2, dtype=np.int32), 3)
+    w = nat.convolve(model, spec, idx)
+    dm, dout = torch.from_numpy(model).to(dev), torch.zeros((3, 2, Ny, Nx), dtype=torch.float32, device=dev)
+    dspec = torch.from_numpy(np.ascontiguousarray(spec).view(np.float32)).to(dev)
+    didx = torch.from_numpy(idx).to(dev)
+    nat._check(L.scl_convolve_f32_dev(p(dm), p(dout), 3, 2, Ny, Nx, p(dspec), 2, p(didx), 0, None))
+    torch.cuda.synchronize()
+    assert_array_equal(dout.cpu().numpy(), w)
