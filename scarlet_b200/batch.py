@@ -180,7 +180,8 @@ class BlendBatch:
     """
 
     def __init__(self, images, psfs, model_psf, centers, bg_rms, weights=None, thresh=1.0,
-                 symmetric=True, monotonic=True, stream=None, streams=1, kinds=None, flux_percentiles=(25,)):
+                 symmetric=True, monotonic=True, stream=None, streams=1, kinds=None, flux_percentiles=(25,),
+                 detect_unit_weights=False):
         """kinds: list of B integer arrays [K_b] aligned with `centers` -- 0 ExtendedSource (default), 1
         MultiComponentSource (len(flux_percentiles) + 1 components, source.py:242-291,537-641), 2 PointSource
         (source.py:323-440); all of them initialised on the device (scl_batch_init_sources)."""
@@ -257,8 +258,10 @@ class BlendBatch:
         self.kind = kind
         wts = None if weights is None else np.ascontiguousarray(weights, dtype=np.float32)
         # A weight array that is 1 everywhere is the reference's `weights=None` (observation.py:148-151: W = 1), bit for
-        # bit: checked once here, and then neither stored on the device nor uploaded with every fit
-        self.uniform_weights = wts is not None and wts.size > 0 and float(wts.min()) == 1.0 and float(wts.max()) == 1.0
+        # bit: with detect_unit_weights=True checked once here, and then neither stored on the device nor uploaded
+        # (opt-in: the bench keeps the per-pixel array its workload names)
+        self.uniform_weights = bool(detect_unit_weights and wts is not None and wts.size > 0 and
+                                    float(wts.min()) == 1.0 and float(wts.max()) == 1.0)
         if self.uniform_weights:
             wts = None
 
