@@ -347,7 +347,7 @@ def run_b200(args):
     strong = None
     if world > 1 and args.strong_blends > 0:
         Ks = np.array([len(synth.draw_scene(i, C, NY, NX)[0]["re"]) for i in range(args.strong_blends)])
-        mine = np.argsort(Ks, kind="stable")[rank::world]
+        mine = shard.deal_sorted(Ks, rank, world)
         ds = synth.make_blends(mine, C, NY, NX, psf_size=PSF)
         bs = BlendBatch(ds["images"], ds["psfs"], ds["model_psf"], ds["centers"], ds["bg_rms"], weights=ds["weights"])
         bs.snapshot()

@@ -16,6 +16,13 @@ def shard_range(n_total, rank, world):
     return range(start, start + base + (1 if rank < extra else 0))
 
 
+def deal_sorted(sizes, rank, world):
+    """Strong-scaling layout: unit indices sorted by size (stable) and dealt round-robin, so every rank
+    gets the same mix of small and large units; rank r owns sorted[r::world]."""
+    order = np.argsort(np.asarray(sizes), kind="stable")
+    return order[int(rank)::int(world)]
+
+
 def weak_range(per_rank, rank):
     """Weak-scaling layout used by bench.py: rank r owns blends [r*B, (r+1)*B)."""
     return range(rank * int(per_rank), (rank + 1) * int(per_rank))

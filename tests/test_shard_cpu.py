@@ -52,3 +52,16 @@ def test_gather_records_gloo_world2():
         assert p.exitcode == 0
     expect = [[[i, 1, 0.5 * i, 2] for i in shard.shard_range(7, r, 2)] for r in range(2)]
     assert res[0] == expect and res[1] == expect          # ragged shards (4 + 3 blends), same view on both ranks
+
+
+def test_deal_sorted_partitions_and_balances():
+    """Strong scaling: units sorted by size and dealt round-robin -- a partition, with per-rank totals within one
+    largest unit of each other."""
+    from scarlet_b200 import shard
+    rng = np.random.default_rng(0)
+    sizes = rng.integers(2, 9, 1000)
+    parts = [shard.deal_sorted(sizes, r, 8) for r in range(8)]
+    assert sorted(np.concatenate(parts).tolist()) == list(range(1000))
+    tot = [int(sizes[p].sum()) for p in parts]
+    assert max(tot) - min(tot) <= 8
+    assert max(len(p) for p in parts) - min(len(p) for p in parts) <= 1
