@@ -325,7 +325,8 @@ int scl_batch_products(scl_batch* batch, float min_value, float* flux, int32_t* 
 int scl_batch_render_components(scl_batch* batch, int k0, int nk, float* out, void* stream);
 /* Profiling aid: while enabled, the constraint kernel adds the clock64 ticks each of its phases took (summed over
  * CTAs: 0 gradient step, 1 centre + symmetry, 2 level list, 3 monotonic sweep, 4 normalise/write-back) to a device
- * counter; the call returns the sums so far in out8 (may be NULL) and clears them. */
+ * counter; slots 5, 6, 7 hold the longest symmetry phase, sweep and CTA seen; the call returns the values so far in
+ * out8 (may be NULL) and clears them. */
 int scl_batch_phase_clocks(scl_batch* batch, int enable, unsigned long long* out8);
 /* How the host waits for the batch's stream (polls of the active count, end of fit, copies): 0 (default) spins on
  * the stream -- lowest latency for one batch driven by one thread; 1 sleeps on a blocking-sync event, for hosts where
@@ -336,7 +337,8 @@ int scl_batch_wait_mode(scl_batch* batch, int blocking);
  * tests compare the two).  bit 1: scene mode forms S S^T by the dense tiled contraction instead of per pair of
  * overlapping footprint boxes (same products; the sums differ in their last bits).  bit 2 / bit 3: low-resolution planes
  * always by the per-blend kernels / always by the kernels blocked over 64 blends (default: blocked from 16 blends of
- * one geometry on). */
+ * one geometry on).  bit 4: scene mode runs a component's whole constraint schedule in one CTA instead of the chain of
+ * kernels that spreads its k-space symmetry products over the GPU (csrc/k_prox_split.cu). */
 int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
 

@@ -5,7 +5,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 SRC = os.path.join(HERE, "csrc", "api.cu")
 LIB = os.path.join(HERE, "lib", "libscarlet_b200.so")
-SOURCES = ["api.cu", "api_batch.inc", "api_noalloc.inc", "api_pybind.inc", "api_f64.inc", "k_f64.cu", "k_forward.cu", "k_grad.cu", "k_prox.cu", "k_lowres.cu", "k_scene.cu", "k_psf.cu", "k_products.cu", "k_update.cu", "prox_dev.cuh", "fft_smem.cuh",
+SOURCES = ["api.cu", "api_batch.inc", "api_noalloc.inc", "api_pybind.inc", "api_f64.inc", "k_f64.cu", "k_forward.cu", "k_grad.cu", "k_prox.cu", "k_prox_split.cu", "k_lowres.cu", "k_scene.cu", "k_psf.cu", "k_products.cu", "k_update.cu", "prox_dev.cuh", "fft_smem.cuh",
            "fft_reg.cuh", "common.cuh"]
 
 

@@ -13,6 +13,7 @@
 #include "k_grad.cu"
 #include "k_update.cu"
 #include "k_prox.cu"
+#include "k_prox_split.cu"
 #include "k_lowres.cu"
 #include "k_scene.cu"
 #include "k_psf.cu"

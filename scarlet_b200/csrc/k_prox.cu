@@ -10,6 +10,7 @@
 //   Blend._check_convergence                     blend.py:141-184
 #include "prox_dev.cuh"
 
+struct SclWideRec;
 struct SclProxArgs {
     const float* G;           // [B, P, N]  adjoint image of every plane (K1); nullptr: no gradient step (construction pass)
     const float* lips;        // [B, 2]     (L_sed, L_morph) (K2)
@@ -34,7 +35,7 @@ struct SclProxArgs {
     SclPlanes pl;             // image planes -> model bands (d loss / d model[c] = sum of G over the planes of band c)
     int it_override;          // >= 0: the iteration number update() sees (0 = source construction)
     double e_rel2;
-    unsigned long long* phase_clk;   // optional [8]: summed clock64 per phase over all CTAs (profiling; nullptr = off)
+    unsigned long long* phase_clk;   // optional [8]: clock64 per phase, [0..4] summed over all CTAs, [5..7] maxima (profiling; nullptr = off)
     // Frames too large for shared memory (scene mode, DESIGN "large frames"): the working copy X and the symmetry
     // scratch Z of CTA i live at xscratch + i * xstride in HBM/L2 (same layout as the shared-memory one); only the
     // symmetry tables stay in shared memory.  nullptr: everything in shared memory.
@@ -50,6 +51,24 @@ struct SclProxArgs {
     const float* prior_b_sed; // [Ktot][C]
     const int* prior_idx;     // [Ktot] row of prior_b_morph, -1 = none
     const float* prior_b_morph;   // [n][N]
+    // Scene mode in stages (k_prox_split.cu): one record per scratch slot carries a component from the step kernel to
+    // the finishing one; waux + i * waux_stride: the symmetry tables of slot i; slot_of[k]: the slot of component k.
+    SclWideRec* wrec;
+    float* waux;
+    size_t waux_stride;
+    int* slot_of;
+};
+
+// What the stages of an iteration hand to each other about the component in one scratch slot.
+struct SclWideRec {
+    int k;                    // component, -1: nothing to do in this slot (blend no longer active)
+    int mode;                 // symmetry the component takes: 0 none, 1 k-space operator, 2 mirror pairs
+    int cy, cx;               // pixel_center after max_pixel / centroid
+    int y0, x0, ny, nx;       // window of the symmetry (scl_window)
+    int nyq, oy;              // k-space operator: Nyquist row term present, row parity offset
+    double dy, dx;            // shift
+    float step;               // 1 / L_morph of the component
+    float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
 };
 
 #define SCL_SCHED_MAX 16
@@ -285,7 +304,9 @@ __device__ void scl_run_schedule(const SclProxArgs& a, int k, int b, float* X, f
     }
 }
 
-template <int THREADS>
+// STAGE 0: the whole update of a component.  STAGE 2 (scene mode in stages): the component arrives stepped, centred and
+// made symmetric by the kernels of k_prox_split.cu (record a.wrec[slot]); only mirror-pair symmetry is left to do here.
+template <int THREADS, int STAGE = 0>
 __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
 {
     extern __shared__ __align__(16) float smem_f[];
@@ -307,24 +328,36 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     if (threadIdx.x == 0) sexit = 0x7fffffff;
     const unsigned fl = a.cflags[k];
     long long tprev = a.phase_clk ? clock64() : 0;
+    const long long tstart = tprev;
+    // slots 0..4: clocks summed over CTAs per phase; 5, 6, 7: the longest symmetry phase, sweep and CTA of the launch
 #define SCL_PHASE(i) do { if (a.phase_clk && threadIdx.x == 0) { long long t_ = clock64(); \
-        atomicAdd(a.phase_clk + (i), (unsigned long long)(t_ - tprev)); tprev = t_; } } while (0)
+        const unsigned long long d_ = (unsigned long long)(t_ - tprev); atomicAdd(a.phase_clk + (i), d_); \
+        if ((i) == 1) atomicMax(a.phase_clk + 5, d_); \
+        if ((i) == 3) atomicMax(a.phase_clk + 6, d_); \
+        if ((i) == 4) atomicMax(a.phase_clk + 7, (unsigned long long)(t_ - tstart)); \
+        tprev = t_; } } while (0)
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;   // Blend.it seen by update()
 
     // gradient steps of this component
     __shared__ double sdA[THREADS / 32][SCL_MAX_BANDS];
     __shared__ float sAnew[SCL_MAX_BANDS], sAold[SCL_MAX_BANDS];
     __shared__ float sstep;
-    scl_component_step<SCENE>(a, k, b, fl, X, sdA, sAnew, sAold, SCENE ? &sstep : nullptr);
-    if (threadIdx.x == 0) {
-        sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
-        ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
+    if (STAGE == 0) {
+        scl_component_step<SCENE>(a, k, b, fl, X, sdA, sAnew, sAold, SCENE ? &sstep : nullptr);
+        if (threadIdx.x == 0) {
+            sc[0] = a.center[2 * k]; sc[1] = a.center[2 * k + 1];
+            ss[0] = a.shift[2 * k]; ss[1] = a.shift[2 * k + 1];
+        }
+    } else {
+        const SclWideRec& r = a.wrec[blockIdx.x];
+        if (threadIdx.x == 0) { sc[0] = r.cy; sc[1] = r.cx; ss[0] = r.dy; ss[1] = r.dx; }
+        if (threadIdx.x < SCL_MAX_BANDS) { sAnew[threadIdx.x] = r.sAnew[threadIdx.x]; sAold[threadIdx.x] = r.sAold[threadIdx.x]; }
     }
     __syncthreads();
     SCL_PHASE(0);      // gradient step
 
     bool scheduled = false;
-    if (SCENE && (fl & SCL_F_SCHEDULE)) {
+    if (STAGE == 0 && SCENE && (fl & SCL_F_SCHEDULE)) {
         scheduled = true;
         scl_run_schedule(a, k, b, X, Z, tab, sAnew, sc, ss, red, sstep);
         if (threadIdx.x == 0) sm = 1.f;
@@ -333,6 +366,14 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
         // components of a multi-component source: centre and shift were measured on the source's combined
         // morphology by scl_k_source_center just before this launch
         const bool own_center = !(fl & SCL_F_SHARED_CENTER);
+        if (STAGE == 2) {
+            const SclWideRec& r = a.wrec[blockIdx.x];
+            if (r.mode == 2) {
+                SclWindow w;
+                w.y0 = r.y0; w.x0 = r.x0; w.ny = r.ny; w.nx = r.nx; w.centered = false;
+                scl_flip_symmetry(X, Nx, w, 0, 1.0f);
+            }
+        } else {
         if (own_center) scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
         __syncthreads();
         if (fl & SCL_F_SYMMETRIC) {
@@ -349,6 +390,7 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
             } else {
                 scl_flip_symmetry(X, Nx, w, 0, 1.0f);
             }
+        }
         }
         SCL_PHASE(1);  // max_pixel, centroid, symmetry
         if (fl & SCL_F_MONOTONIC) {
@@ -369,8 +411,7 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                 }
                 __syncthreads();
             } else if (SCENE) {
-                scl_monotonic_hbm<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f,
-                                                a.no_early_exit ? nullptr : &sexit);
+                scl_monotonic_wide_f32(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f, a.no_early_exit ? nullptr : &sexit);
                 __syncthreads();
             } else {
                 scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);

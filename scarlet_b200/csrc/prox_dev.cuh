@@ -689,7 +689,12 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
     const T omt = (T)1 - thresh;
     const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
     const int vmax = 2 * max(ay, ax) + min(ay, ax);       // v = level + 1 = 2a + b
-    const int slot = threadIdx.x >> 3, oct = threadIdx.x & 7;
+    // An octant per warp (blocks of a multiple of eight warps): of a source near the frame edge whole octants lie
+    // outside the frame on the far levels, and their warps then issue nothing; with the octants spread over the lanes
+    // of every warp each warp ran the full pixel path for one or two live lanes.
+    const bool by_warp = (blockDim.x & 255) == 0;
+    const int oct = by_warp ? ((threadIdx.x >> 5) & 7) : (threadIdx.x & 7);
+    const int slot = by_warp ? ((threadIdx.x & 31) | ((threadIdx.x >> 8) << 5)) : (threadIdx.x >> 3);
     const int nslot = blockDim.x >> 3;
     const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
     __syncthreads();
@@ -702,9 +707,15 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
     // The pixels of a level are independent: each thread takes up to MONO_ILP of them per round and computes all
     // their values before storing any, so their loads overlap (with X in HBM/L2 a round is one memory round trip).
     constexpr int MONO_ILP = 2;
+    // This thread's octant reaches the frame edge after Ba steps along its long axis and Bb along its short one: of a
+    // level's offsets (a, v - 2a) only a in [(v - Bb + 1) / 2, Ba] lie inside the frame.  Far levels of a source near
+    // an edge are mostly outside; enumerating only the inside keeps their cost proportional to what they update (the
+    // sweep of one component runs on one SM and is bound by the instructions it issues).
+    const int Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);
+    const int Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);
     int dry = 0, vlast = 0x7fffffff;    // consecutive levels without a positive pixel (block-uniform); last level done
     for (int v = 1; v <= vmax; v++) {
-        const int amin = (v + 2) / 3, amax = v / 2;
+        const int amin = max((v + 2) / 3, (v - Bb + 1) >> 1), amax = min(v / 2, Ba);
         int anypos = 0;
         for (int a0 = amin + slot; a0 <= amax; a0 += MONO_ILP * nslot) {
             T val[MONO_ILP];
@@ -720,7 +731,6 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
                 const int pa = sa ? -a : a, pb = sb ? -bb : bb;
                 const int Yo = sw ? pb : pa, Xo = sw ? pa : pb;
                 const int y = cy + Yo, x = cx + Xo;
-                if (y < 0 || y >= Ny || x < 0 || x >= Nx) continue;
                 pos[u] = y * Nx + x;
                 val[u] = scl_mono_pixel_value_hbm<T, NEAREST>(X, Ny, Nx, y, x, Yo, Xo, wtab, ctab, omt);
             }
@@ -730,6 +740,111 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
         }
         if (exit_level) {
             // the level barrier doubles as the vote (a level without pixels inside the frame counts as dry)
+            dry = __syncthreads_or(anypos) ? 0 : dry + 1;
+            if (dry >= 3 && v >= 3) { vlast = v; break; }
+        } else {
+            __syncthreads();
+        }
+    }
+    if (exit_level && threadIdx.x == 0) *exit_level = vlast;
+}
+
+// ---- the float32 weighted sweep of scene mode, written for its instruction count.
+// One component's sweep runs on one SM, a level after the other, and a frame-sized component has ~1000 pixels on each
+// of ~1000 levels: measured, the generic loop above spent ~450 instructions on a pixel (sign/swap selects, 64-bit
+// address arithmetic and in-frame tests per tap, a branch per weight) and a level took 1.7 us with every load removed.
+// Here the octant is a property of the warp (blocks of a multiple of 8 warps), pixel and table indices are affine in
+// (a, v - 2a) with per-thread constant steps, interior pixels read their eight neighbours at fixed offsets, and the
+// weights select instead of branch.  Same operations on the same values in the same order as scl_mono_pixel_value_hbm
+// (products rounded, added in tap order, taps of weight 0 skipped), hence the same bits.
+__device__ __forceinline__ float scl_mono_ref8(const float (&n)[8], const float4 w0, const float4 w1) {
+    float ref = 0.f;
+    ref = (w0.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n[0], w0.x)) : ref;
+    ref = (w0.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n[1], w0.y)) : ref;
+    ref = (w0.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n[2], w0.z)) : ref;
+    ref = (w0.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n[3], w0.w)) : ref;
+    ref = (w1.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n[4], w1.x)) : ref;
+    ref = (w1.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n[5], w1.y)) : ref;
+    ref = (w1.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n[6], w1.z)) : ref;
+    ref = (w1.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n[7], w1.w)) : ref;
+    return ref;
+}
+
+__device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
+                                       const float* __restrict__ wtab, const double* __restrict__ ctab, float thresh,
+                                       int* exit_level = nullptr) {
+    if ((blockDim.x & 255) != 0 || Ny < 2 || Nx < 2) {
+        scl_monotonic_hbm<float, false>(X, Ny, Nx, cy, cx, wtab, ctab, thresh, exit_level);
+        return;
+    }
+    const float omt = 1.f - thresh;
+    const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
+    const int vmax = 2 * max(ay, ax) + min(ay, ax);
+    const int oct = (threadIdx.x >> 5) & 7;
+    const int slot = (threadIdx.x & 31) | ((threadIdx.x >> 8) << 5), nslot = blockDim.x >> 3;
+    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
+    // offset (Yo, Xo) = a (ya, xa) + bb (yb, xb)
+    const int ya = sw ? 0 : (sa ? -1 : 1), xa = sw ? (sa ? -1 : 1) : 0;
+    const int yb = sw ? (sb ? -1 : 1) : 0, xb = sw ? 0 : (sb ? -1 : 1);
+    const int Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);      // steps to the frame edge, long axis
+    const int Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);      // ... short axis
+    const int W2 = 2 * Nx - 1;
+    const int pA = ya * Nx + xa, pB = yb * Nx + xb;      // steps of the pixel index per unit of a / bb
+    const int tA = ya * W2 + xa, tB = yb * W2 + xb;      // steps of the table entry
+    const int p0 = cy * Nx + cx, t0 = (Ny - 1) * W2 + (Nx - 1);
+    const size_t tsize = (size_t)(2 * Ny - 1) * (size_t)W2 * 8;
+    __syncthreads();
+    constexpr int ILP = 2;
+    int dry = 0, vlast = 0x7fffffff;
+    for (int v = 1; v <= vmax; v++) {
+        const int amin = max((v + 2) / 3, (v - Bb + 1) >> 1), amax = min(v >> 1, Ba);
+        int anypos = 0;
+        for (int a0 = amin + slot; a0 <= amax; a0 += ILP * nslot) {
+            float val[ILP];
+            int pos[ILP];
+#pragma unroll
+            for (int u = 0; u < ILP; u++) {
+                const int a = a0 + u * nslot, bb = v - 2 * a;
+                pos[u] = -1;
+                // beyond the level, or a duplicate image of a pixel on an octant boundary
+                if (a > amax || (bb == 0 && sb) || (a == bb && sw)) continue;
+                const int p = p0 + a * pA + bb * pB;
+                const float* xr = X + p;
+                const float* wt = wtab + (size_t)(t0 + a * tA + bb * tB) * 8;
+                float n[8];
+                pos[u] = p;
+                if (a == Ba || bb == Bb) {
+                    // on the frame edge: the table of the border type; taps outside the frame (weight 0 there) read
+                    // the pixel itself
+                    const int y = cy + ya * a + yb * bb, x = cx + xa * a + xb * bb;
+                    const bool up = y > 0, dn = y < Ny - 1, lf = x > 0, rt = x < Nx - 1;
+                    wt += (size_t)((up ? (dn ? 0 : 2) : 1) * 3 + (lf ? (rt ? 0 : 2) : 1)) * tsize;
+                    n[0] = xr[(up && lf) ? -Nx - 1 : 0];
+                    n[1] = xr[up ? -Nx : 0];
+                    n[2] = xr[(up && rt) ? -Nx + 1 : 0];
+                    n[3] = xr[lf ? -1 : 0];
+                    n[4] = xr[rt ? 1 : 0];
+                    n[5] = xr[(dn && lf) ? Nx - 1 : 0];
+                    n[6] = xr[dn ? Nx : 0];
+                    n[7] = xr[(dn && rt) ? Nx + 1 : 0];
+                } else {
+                    const float* xu = xr - Nx;
+                    const float* xd = xr + Nx;
+                    n[0] = xu[-1]; n[1] = xu[0]; n[2] = xu[1];
+                    n[3] = xr[-1]; n[4] = xr[1];
+                    n[5] = xd[-1]; n[6] = xd[0]; n[7] = xd[1];
+                }
+                const float4 w0 = *reinterpret_cast<const float4*>(wt);
+                const float4 w1 = *reinterpret_cast<const float4*>(wt + 4);
+                const float cur = xr[0];
+                const float r = __fmul_rn(scl_mono_ref8(n, w0, w1), omt);
+                val[u] = (r < cur) ? r : cur;
+            }
+#pragma unroll
+            for (int u = 0; u < ILP; u++)
+                if (pos[u] >= 0) { X[pos[u]] = val[u]; anypos |= !(val[u] <= 0.f); }
+        }
+        if (exit_level) {
             dry = __syncthreads_or(anypos) ? 0 : dry + 1;
             if (dry >= 3 && v >= 3) { vlast = v; break; }
         } else {

@@ -25,12 +25,16 @@ def main():
     ap.add_argument("--bands", type=int, default=6)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--approx", action="store_true")
+    ap.add_argument("--drop", default="", help="experiment: clear a constraint flag on every component (symmetric, monotonic, kspace)")
     a = ap.parse_args()
     C, Ny, Nx, ns = a.bands, a.size, a.size, a.sources
     t0 = time.time()
     nat.require_device()
     batch, _ = synth.scene_arrays(a.size, a.sources, a.bands)
     K = len(batch["sed"])
+    if a.drop:
+        bit = {"symmetric": nat.F_SYMMETRIC, "monotonic": nat.F_MONOTONIC, "kspace": nat.F_KSPACE}[a.drop]
+        batch["cflags"] = [f & ~bit for f in batch["cflags"]]
     t_gen = time.time() - t0
     t0 = time.time()
     bt = nat.Batch(**batch)
@@ -45,6 +49,8 @@ def main():
     tot = float(sum(clk[:5])) or 1.0
     phases = dict(zip(["gradient_step", "centre_symmetry", "level_list", "monotonic", "normalise_writeback"],
                       [round(c / tot, 3) for c in clk[:5]]))
+    # slots 5..7: longest symmetry phase / sweep / CTA of a launch (max over the three launches), in ms at 1.9 GHz
+    longest = dict(zip(["symmetry_ms", "sweep_ms", "cta_ms"], [round(float(c) / 1.9e6, 3) for c in clk[5:8]]))
     bt.close()
     N = Ny * Nx
     alg = 4 * N * (2 * K + 2 * C) + 4 * C * 41 * 41 + 8 * K * C         # DESIGN.md B_iter
@@ -53,7 +59,7 @@ def main():
     print(json.dumps(dict(workload="config4-like scene", C=C, Ny=Ny, Nx=Nx, sources=ns, components=K,
                           approximate_L=a.approx, iters=info["steps"], ms_per_iter=ms,
                           kernel_ms=dict(render_conv_adjoint=km[0], lipschitz=km[1], constraints=km[2], converge=km[3]),
-                          constraint_phase_share=phases, alg_bytes_per_iter=alg, gbs=alg / ms / 1e6, launches=info["launches"],
+                          constraint_phase_share=phases, constraint_longest=longest, alg_bytes_per_iter=alg, gbs=alg / ms / 1e6, launches=info["launches"],
                           logL=[float(v) for v in out["logL"][0, :info["steps"]]],
                           gen_s=t_gen, tables_upload_s=t_up)))
 
