@@ -338,7 +338,9 @@ int scl_batch_wait_mode(scl_batch* batch, int blocking);
  * overlapping footprint boxes (same products; the sums differ in their last bits).  bit 2 / bit 3: low-resolution planes
  * always by the per-blend kernels / always by the kernels blocked over 64 blends (default: blocked from 16 blends of
  * one geometry on).  bit 4: scene mode runs a component's whole constraint schedule in one CTA instead of the chain of
- * kernels that spreads its k-space symmetry products over the GPU (csrc/k_prox_split.cu). */
+ * kernels that spreads its k-space symmetry products over the GPU (csrc/k_prox_split.cu).  bit 5: the scene-mode sweep
+ * reads every pixel's eight weights from the offset-indexed table instead of the four that can be non-zero from the
+ * level-ordered copy (bit-identical results; the tests compare the two). */
 int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
 

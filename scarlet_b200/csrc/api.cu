@@ -61,9 +61,12 @@ struct Tables {
     unsigned* plist = nullptr;   // sweep plans of every centre (prox_dev.cuh), 32 entries per pass
     unsigned* pfirst = nullptr;  // [N + 1] first pass of each centre
     int pbits = 0;               // 0: no plan (shape too large): generic monotonic path
+    float4* wlev = nullptr;      // [8][wlevE] level-ordered four-tap weights of the wide sweep (prox_dev.cuh); nullptr: none
+    int wlevE = 0;
     SclMonoPlan plan() const { SclMonoPlan p; p.list = plist; p.first = pfirst; p.pbits = pbits; return p; }
-    void release() { cudaFree(wtab); cudaFree(ctab); cudaFree(plist); cudaFree(pfirst); }
+    void release() { cudaFree(wtab); cudaFree(ctab); cudaFree(plist); cudaFree(pfirst); cudaFree(wlev); }
 };
+constexpr size_t kWlevBudget = (size_t)128 << 20;    // bytes of level-ordered weights per shape
 constexpr size_t kPlanBudget = (size_t)768 << 20;    // bytes of sweep plans per shape
 constexpr int kNflN = 4096;
 constexpr int kMaxDev = 64;
@@ -295,6 +298,32 @@ int scl_stream_destroy(void* stream) {
     return SCL_OK;
 }
 
+// Level-ordered four-tap weights of the wide float32 sweep (prox_dev.cuh: scl_k_build_wlev), derived on the device
+// from the interior table just uploaded.  Left out (the sweep then reads the eight-tap table) when they would exceed
+// kWlevBudget or when the table carries weight outside an octant's four candidate taps.
+static int build_wlev(int Ny, int Nx, Tables* t) {
+    const int amax_tab = (Ny > Nx ? Ny : Nx) - 1;
+    if (amax_tab < 1) return SCL_OK;
+    const int nv = 3 * amax_tab;
+    std::vector<int> start(nv + 2, 0);
+    for (int v = 1; v <= nv; v++) start[v + 1] = start[v] + scl_wlev_count(v, amax_tab);
+    const int E = start[nv + 1];
+    if ((size_t)E * 8 * sizeof(float4) > kWlevBudget) return SCL_OK;
+    DevBuf<int> dstart, dbad;
+    CK(dstart.alloc(start.size()));
+    CK(dbad.alloc(1));
+    CK(cudaMemcpy(dstart.p, start.data(), start.size() * sizeof(int), cudaMemcpyHostToDevice));
+    CK(cudaMemset(dbad.p, 0, sizeof(int)));
+    CK(cudaMalloc(&t->wlev, (size_t)E * 8 * sizeof(float4)));
+    scl_k_build_wlev<<<dim3((amax_tab + 128) / 128, nv, 8), 128>>>(t->wtab, dstart.p, t->wlev, E, Ny, Nx, amax_tab, dbad.p);
+    CK(cudaGetLastError());
+    int bad = 0;
+    CK(cudaMemcpy(&bad, dbad.p, sizeof(int), cudaMemcpyDeviceToHost));
+    if (bad) { cudaFree(t->wlev); t->wlev = nullptr; return SCL_OK; }
+    t->wlevE = E;
+    return SCL_OK;
+}
+
 int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ctab) {
     int rc = check_shape(Ny, Nx, true);
     if (rc) return rc;
@@ -308,6 +337,7 @@ int scl_set_monotonic_tables(int Ny, int Nx, const float* wtab, const double* ct
     CK(cudaMemcpy(t.wtab, wtab, 9 * n * sizeof(float), cudaMemcpyHostToDevice));
     CK(cudaMemcpy(t.ctab, ctab, n * sizeof(double), cudaMemcpyHostToDevice));
     if ((rc = build_plans(Ny, Nx, &t))) { t.release(); return rc; }
+    if ((rc = build_wlev(Ny, Nx, &t))) { t.release(); return rc; }
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = st->tables.find({Ny, Nx});
     if (it != st->tables.end()) it->second.release();

@@ -29,6 +29,8 @@ struct SclProxArgs {
     const float* wtab;        // monotonic tables (see prox_dev.cuh)
     const double* ctab;
     SclMonoPlan plan;         // per-centre sweep plans of this shape (pbits == 0: none)
+    const float4* wlev;       // level-ordered four-tap weights of the wide sweep (nullptr: none), wlevE entries per octant
+    int wlevE;
     const int* nfl;           // next_fast_len tables
     const int* nfl_even;
     int C, Ny, Nx, ph, pw, step;
@@ -411,7 +413,8 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                 }
                 __syncthreads();
             } else if (SCENE) {
-                scl_monotonic_wide_f32(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f, a.no_early_exit ? nullptr : &sexit);
+                scl_monotonic_wide_f32(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f, a.no_early_exit ? nullptr : &sexit,
+                                       a.wlev, a.wlevE);
                 __syncthreads();
             } else {
                 scl_monotonic<float, false>(X, Ny, Nx, sc[0], sc[1], a.wtab, a.ctab, 0.f);

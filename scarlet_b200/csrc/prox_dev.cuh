@@ -770,9 +770,80 @@ __device__ __forceinline__ float scl_mono_ref8(const float (&n)[8], const float4
     return ref;
 }
 
+// Level-ordered weights of the wide sweep.  Of the eight taps of a pixel at offset a (ya, xa) + bb (yb, xb), a >= bb >= 0,
+// only four can be strictly closer to the peak: the three one step back along the long axis and the one a step back
+// along the short axis; the others always carry weight 0 (the builder checks it on the table it is given).  wlev holds,
+// per octant, those four weights of every offset in the order the sweep visits them -- level v = 2a + bb after level,
+// a ascending inside a level -- so that the lanes of a warp (consecutive a) read consecutive 16-byte entries instead
+// of 32-byte rows scattered over a table of (2Ny-1)(2Nx-1) offsets.  Component j of an entry is the weight of the
+// octant's j-th candidate tap in ascending tap index (the order the reference adds them in, operators_pybind11.cc:38-44).
+struct SclOctant {
+    int ya, xa, yb, xb;      // offset (Yo, Xo) = a (ya, xa) + bb (yb, xb)
+    int tap[4];              // the candidate taps (index into the 3x3 neighbourhood without its centre), ascending
+    int oy[4], ox[4];        // their steps
+};
+__host__ __device__ inline int scl_tap_index(int oy, int ox) {
+    const int i = (oy + 1) * 3 + (ox + 1);
+    return i > 4 ? i - 1 : i;
+}
+__host__ __device__ inline SclOctant scl_octant(int oct) {
+    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
+    SclOctant o;
+    o.ya = sw ? 0 : (sa ? -1 : 1); o.xa = sw ? (sa ? -1 : 1) : 0;
+    o.yb = sw ? (sb ? -1 : 1) : 0; o.xb = sw ? 0 : (sb ? -1 : 1);
+    const int da[4] = {-1, -1, -1, 0}, db[4] = {-1, 0, 1, -1};
+    for (int j = 0; j < 4; j++) {
+        o.oy[j] = da[j] * o.ya + db[j] * o.yb;
+        o.ox[j] = da[j] * o.xa + db[j] * o.xb;
+        o.tap[j] = scl_tap_index(o.oy[j], o.ox[j]);
+    }
+    for (int i = 1; i < 4; i++)                   // insertion sort by tap index
+        for (int j = i; j > 0 && o.tap[j - 1] > o.tap[j]; j--) {
+            int t;
+            t = o.tap[j]; o.tap[j] = o.tap[j - 1]; o.tap[j - 1] = t;
+            t = o.oy[j]; o.oy[j] = o.oy[j - 1]; o.oy[j - 1] = t;
+            t = o.ox[j]; o.ox[j] = o.ox[j - 1]; o.ox[j - 1] = t;
+        }
+    return o;
+}
+// entries of level v in a table built for offsets up to amax_tab along the long axis
+__host__ __device__ inline int scl_wlev_count(int v, int amax_tab) {
+    const int lo = (v + 2) / 3, hi = (v >> 1) < amax_tab ? (v >> 1) : amax_tab;
+    return hi >= lo ? hi - lo + 1 : 0;
+}
+
+// grid (ceil((amax_tab + 1) / 128), 3 * amax_tab, 8 octants); start[v]: first entry of level v; bad: count of offsets
+// with a non-zero weight on a tap outside the octant's four (must stay 0 for the table to be used)
+__global__ void scl_k_build_wlev(const float* __restrict__ wtab, const int* __restrict__ start, float4* __restrict__ wlev,
+                                 int E, int Ny, int Nx, int amax_tab, int* __restrict__ bad) {
+    const int v = blockIdx.y + 1, oct = blockIdx.z;
+    const int ai = blockIdx.x * blockDim.x + threadIdx.x;
+    if (ai >= scl_wlev_count(v, amax_tab)) return;
+    const int a = (v + 2) / 3 + ai, bb = v - 2 * a;
+    const SclOctant o = scl_octant(oct);
+    const int Yo = a * o.ya + bb * o.yb, Xo = a * o.xa + bb * o.xb;
+    float4 out = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (abs(Yo) <= Ny - 1 && abs(Xo) <= Nx - 1) {
+        const float* w = wtab + ((size_t)(Yo + Ny - 1) * (2 * Nx - 1) + (Xo + Nx - 1)) * 8;
+        out = make_float4(w[o.tap[0]], w[o.tap[1]], w[o.tap[2]], w[o.tap[3]]);
+        int extra = 0;
+        for (int i = 0; i < 8; i++)
+            if (i != o.tap[0] && i != o.tap[1] && i != o.tap[2] && i != o.tap[3] && w[i] != 0.f) extra++;
+        if (extra) atomicAdd(bad, 1);
+    }
+    wlev[(size_t)oct * E + start[v] + ai] = out;
+}
+
+// in-frame range of a on level v for an octant that reaches the frame edge after Ba steps along its long axis and Bb
+// along its short one
+__device__ __forceinline__ void scl_wide_range(int v, int Ba, int Bb, int& amin, int& amax) {
+    amin = max((v + 2) / 3, (v - Bb + 1) >> 1);
+    amax = min(v >> 1, Ba);
+}
+
 __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                                        const float* __restrict__ wtab, const double* __restrict__ ctab, float thresh,
-                                       int* exit_level = nullptr) {
+                                       int* exit_level = nullptr, const float4* __restrict__ wlev = nullptr, int wlevE = 0) {
     if ((blockDim.x & 255) != 0 || Ny < 2 || Nx < 2) {
         scl_monotonic_hbm<float, false>(X, Ny, Nx, cy, cx, wtab, ctab, thresh, exit_level);
         return;
@@ -780,24 +851,85 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
     const float omt = 1.f - thresh;
     const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
     const int vmax = 2 * max(ay, ax) + min(ay, ax);
-    const int oct = (threadIdx.x >> 5) & 7;
-    const int slot = (threadIdx.x & 31) | ((threadIdx.x >> 8) << 5), nslot = blockDim.x >> 3;
-    const bool sb = oct & 1, sa = (oct >> 1) & 1, sw = (oct >> 2) & 1;
-    // offset (Yo, Xo) = a (ya, xa) + bb (yb, xb)
-    const int ya = sw ? 0 : (sa ? -1 : 1), xa = sw ? (sa ? -1 : 1) : 0;
-    const int yb = sw ? (sb ? -1 : 1) : 0, xb = sw ? 0 : (sb ? -1 : 1);
-    const int Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);      // steps to the frame edge, long axis
-    const int Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);      // ... short axis
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     const int W2 = 2 * Nx - 1;
-    const int pA = ya * Nx + xa, pB = yb * Nx + xb;      // steps of the pixel index per unit of a / bb
-    const int tA = ya * W2 + xa, tB = yb * W2 + xb;      // steps of the table entry
     const int p0 = cy * Nx + cx, t0 = (Ny - 1) * W2 + (Nx - 1);
     const size_t tsize = (size_t)(2 * Ny - 1) * (size_t)W2 * 8;
+    const int amax_tab = max(Ny, Nx) - 1;
+    // A level ends when its slowest warp does, and a source near an edge has one or two octants that reach across the
+    // frame and six that left it: with a fixed octant per warp two warps ran two or three rounds per level while
+    // fourteen waited (measured per warp with clock64: 1067 rounds against 27).  Every SCL_WIDE_CHUNK levels the warps
+    // are dealt to the octants in proportion to the pixels they hold over those levels (at least one warp per octant
+    // that holds any).
+    constexpr int SCL_WIDE_CHUNK = 32;
+    __shared__ int s_pre[9], s_cnt[8];
+    // per-octant values of this warp (set at every deal)
+    int oct = -1, slot = 0, nslot = 32;
+    bool sb = false, sw = false;
+    int ya = 0, xa = 0, yb = 0, xb = 0, Ba = -1, Bb = -1, pA = 0, pB = 0, tA = 0, tB = 0;
+    int d4[4] = {0, 0, 0, 0};
+    const float4* wl = nullptr;
+    int estart = 0;          // first level-ordered entry of the current level
     __syncthreads();
     constexpr int ILP = 2;
     int dry = 0, vlast = 0x7fffffff;
     for (int v = 1; v <= vmax; v++) {
-        const int amin = max((v + 2) / 3, (v - Bb + 1) >> 1), amax = min(v >> 1, Ba);
+        if (((v - 1) % SCL_WIDE_CHUNK) == 0) {
+            // (every thread is past the barrier that ended level v - 1)
+            if (warp == 0) {
+                int n = 0;
+                if (lane < 8) {
+                    const bool qb = lane & 1, qa = (lane >> 1) & 1, qw = (lane >> 2) & 1;
+                    const int qBa = qw ? (qa ? cx : Nx - 1 - cx) : (qa ? cy : Ny - 1 - cy);
+                    const int qBb = qw ? (qb ? cy : Ny - 1 - cy) : (qb ? cx : Nx - 1 - cx);
+                    const int ve = min(v + SCL_WIDE_CHUNK - 1, vmax);
+                    for (int u = v; u <= ve; u++) {
+                        int lo, hi;
+                        scl_wide_range(u, qBa, qBb, lo, hi);
+                        n += max(hi - lo + 1, 0);
+                    }
+                }
+                int tot = n;
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                const int nz = __popc(__ballot_sync(0xffffffffu, n > 0));
+                int w = 0;
+                if (n > 0) w = 1 + (int)(((long long)(nw - nz) * n) / tot);
+                int incl = w;
+#pragma unroll
+                for (int o = 1; o < 8; o <<= 1) {
+                    const int t = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o) incl += t;
+                }
+                if (lane < 8) { s_pre[lane] = incl - w; s_cnt[lane] = w; }
+                if (lane == 7) s_pre[8] = incl;
+            }
+            __syncthreads();
+            oct = -1;
+#pragma unroll
+            for (int o = 0; o < 8; o++)
+                if (warp >= s_pre[o] && warp < s_pre[o] + s_cnt[o]) oct = o;
+            Ba = -1; Bb = -1;
+            if (oct >= 0) {
+                const bool sa = (oct >> 1) & 1;
+                sb = oct & 1; sw = (oct >> 2) & 1;
+                slot = (warp - s_pre[oct]) * 32 + lane;
+                nslot = s_cnt[oct] * 32;
+                ya = sw ? 0 : (sa ? -1 : 1); xa = sw ? (sa ? -1 : 1) : 0;
+                yb = sw ? (sb ? -1 : 1) : 0; xb = sw ? 0 : (sb ? -1 : 1);
+                Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);      // steps to the frame edge, long axis
+                Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);      // ... short axis
+                pA = ya * Nx + xa; pB = yb * Nx + xb;      // steps of the pixel index per unit of a / bb
+                tA = ya * W2 + xa; tB = yb * W2 + xb;      // steps of the table entry
+                wl = wlev ? wlev + (size_t)oct * wlevE : nullptr;
+                const SclOctant o = scl_octant(oct);
+#pragma unroll
+                for (int j = 0; j < 4; j++) d4[j] = o.oy[j] * Nx + o.ox[j];
+            }
+        }
+        const int amin0 = (v + 2) / 3;
+        int amin, amax;
+        scl_wide_range(v, Ba, Bb, amin, amax);
         int anypos = 0;
         for (int a0 = amin + slot; a0 <= amax; a0 += ILP * nslot) {
             float val[ILP];
@@ -810,9 +942,22 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                 if (a > amax || (bb == 0 && sb) || (a == bb && sw)) continue;
                 const int p = p0 + a * pA + bb * pB;
                 const float* xr = X + p;
+                pos[u] = p;
+                if (wl && a != Ba && bb != Bb) {
+                    // interior pixel: its four candidate taps, one coalesced 16-byte entry of weights
+                    const float4 w = wl[estart + (a - amin0)];
+                    const float n0 = xr[d4[0]], n1 = xr[d4[1]], n2 = xr[d4[2]], n3 = xr[d4[3]], cur = xr[0];
+                    float ref = 0.f;
+                    ref = (w.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n0, w.x)) : ref;
+                    ref = (w.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n1, w.y)) : ref;
+                    ref = (w.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n2, w.z)) : ref;
+                    ref = (w.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n3, w.w)) : ref;
+                    const float r = __fmul_rn(ref, omt);
+                    val[u] = (r < cur) ? r : cur;
+                    continue;
+                }
                 const float* wt = wtab + (size_t)(t0 + a * tA + bb * tB) * 8;
                 float n[8];
-                pos[u] = p;
                 if (a == Ba || bb == Bb) {
                     // on the frame edge: the table of the border type; taps outside the frame (weight 0 there) read
                     // the pixel itself
@@ -844,6 +989,7 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
             for (int u = 0; u < ILP; u++)
                 if (pos[u] >= 0) { X[pos[u]] = val[u]; anypos |= !(val[u] <= 0.f); }
         }
+        estart += scl_wlev_count(v, amax_tab);
         if (exit_level) {
             dry = __syncthreads_or(anypos) ? 0 : dry + 1;
             if (dry >= 3 && v >= 3) { vlast = v; break; }

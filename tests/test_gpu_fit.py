@@ -255,6 +255,30 @@ def test_scene_early_exit_is_bit_identical(nat, case):
         assert (a["morph"] == 0).mean() > 0.2       # there was something to skip
 
 
+@pytest.mark.parametrize("case", ["scene160", "ragged", "blends64"])
+def test_scene_sweep_level_ordered_weights_are_bit_identical(nat, case):
+    """The scene-mode sweep takes an interior pixel's weights from a level-ordered copy of the table that keeps the
+    four taps that can be strictly closer to the peak (prox_dev.cuh: scl_k_build_wlev); debug flag 32 makes it read
+    all eight from the offset-indexed table (operator.py:540-621).  Same products in the same order: identical bits,
+    early exit or not, square or ragged frames."""
+    if case == "scene160":
+        kw = dict(helpers.scene_blend(160, 24)[0])
+    elif case == "ragged":
+        kw = dict(helpers.pack([helpers.synthetic_blend(21, Ny=150, Nx=140, kmin=10, kmax=12)[3]]))
+    else:
+        kw = dict(helpers.pack([helpers.synthetic_blend(s, kmin=3, kmax=6)[3] for s in (11, 12, 13)]), scene_mode=1)
+    outs = []
+    for flags in (0, 32, 33):
+        bt = nat.Batch(**kw)
+        bt.debug_flags(flags)
+        bt.fit(6, 0.0, approximate_L=True)
+        outs.append(bt.download())
+        bt.close()
+    for b in outs[1:]:
+        for key in ("sed", "morph", "center", "shift", "conv", "logL", "lipschitz"):
+            assert_array_equal(outs[0][key], b[key])
+
+
 @pytest.mark.parametrize("case", ["scene160", "blends64", "multi"])
 def test_scene_constraints_in_stages_equal_one_cta_kernel(nat, case):
     """Scene mode runs the constraint schedule as a chain of kernels (k_prox_split.cu: steps, source centres, symmetry
