@@ -55,6 +55,8 @@ struct SclProxArgs {
     const float* prior_b_morph;   // [n][N]
     // Scene mode in stages (k_prox_split.cu): one record per scratch slot carries a component from the step kernel to
     // the finishing one; waux + i * waux_stride: the symmetry tables of slot i; slot_of[k]: the slot of component k.
+    int* box;                 // [Ktot][4] scene mode: footprint box (y0, y1, x0, x1) of the morphology written back, for the
+                              // next iteration's Gram matrix (k_scene.cu: scl_k_scene_gram_boxes); nullptr: not wanted
     SclWideRec* wrec;
     float* waux;
     size_t waux_stride;
@@ -484,6 +486,11 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     // write back + convergence sums (blend.py:160-174)
     double d2 = 0.0, n2 = 0.0;
     float* Sout = a.S + (size_t)k * N;
+    // scene mode: the footprint box of what is written (scl_k_scene_bbox spent a pass over every morphology on it)
+    const bool want_box = SCENE && a.box != nullptr;
+    int by0 = Ny, by1 = -1, bx0 = Nx, bx1 = -1;
+#define SCL_BOX_ADD(p_, v_) do { if (want_box && (v_) != 0.f) { const int y_ = (p_) / Nx, x_ = (p_) - y_ * Nx; \
+        by0 = min(by0, y_); by1 = max(by1, y_); bx0 = min(bx0, x_); bx1 = max(bx1, x_); } } while (0)
     if (SCENE && (N & 3) == 0) {
         const int n4 = N >> 2, nt = blockDim.x;
         const float4* X4 = reinterpret_cast<const float4*>(X);
@@ -505,6 +512,14 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                     const double df = (double)oe[j] - (double)e[j];
                     d2 += df * df;
                     n2 += (double)e[j] * (double)e[j];
+                    if ((Nx & 3) != 0) SCL_BOX_ADD(((i0 + u * nt) << 2) + j, e[j]);
+                }
+                if (want_box && (Nx & 3) == 0 && (e[0] != 0.f || e[1] != 0.f || e[2] != 0.f || e[3] != 0.f)) {
+                    // the four pixels share a row: one division for the vector
+                    const int p_ = (i0 + u * nt) << 2, y_ = p_ / Nx, x_ = p_ - y_ * Nx;
+                    const int jf = e[0] != 0.f ? 0 : (e[1] != 0.f ? 1 : (e[2] != 0.f ? 2 : 3));
+                    const int jl = e[3] != 0.f ? 3 : (e[2] != 0.f ? 2 : (e[1] != 0.f ? 1 : 0));
+                    by0 = min(by0, y_); by1 = max(by1, y_); bx0 = min(bx0, x_ + jf); bx1 = max(bx1, x_ + jl);
                 }
                 S4[i0 + u * nt] = v[u];
             }
@@ -523,7 +538,28 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
                 d2 += df * df;
                 n2 += (double)v * (double)v;
                 Sout[p] = v;
+                SCL_BOX_ADD(p, v);
             }
+        }
+    }
+#undef SCL_BOX_ADD
+    if (want_box) {
+        __shared__ int sbox[4][32];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            by0 = min(by0, __shfl_xor_sync(0xffffffffu, by0, o)); by1 = max(by1, __shfl_xor_sync(0xffffffffu, by1, o));
+            bx0 = min(bx0, __shfl_xor_sync(0xffffffffu, bx0, o)); bx1 = max(bx1, __shfl_xor_sync(0xffffffffu, bx1, o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            sbox[0][threadIdx.x >> 5] = by0; sbox[1][threadIdx.x >> 5] = by1;
+            sbox[2][threadIdx.x >> 5] = bx0; sbox[3][threadIdx.x >> 5] = bx1;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            for (int i = 1; i < (int)(blockDim.x >> 5); i++) {
+                by0 = min(by0, sbox[0][i]); by1 = max(by1, sbox[1][i]); bx0 = min(bx0, sbox[2][i]); bx1 = max(bx1, sbox[3][i]);
+            }
+            a.box[4 * k] = by0; a.box[4 * k + 1] = by1; a.box[4 * k + 2] = bx0; a.box[4 * k + 3] = bx1;
         }
     }
     d2 = block_sum<double>(d2, red);

@@ -315,13 +315,25 @@ scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const 
     const float* A = in + (size_t)b * Kp * Kp;
     const int i0 = blockIdx.y * 32, j0 = blockIdx.x * 32, tx = threadIdx.x, ty = threadIdx.y;
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    // the next pair of tiles is fetched into registers while this one is multiplied: the kernel is 11 dependent steps
+    // of a matrix that sits in L2, and paid one L2 round trip per step (21 us a launch, 16 launches per iteration)
+    float ra[4], rb[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        ra[u] = A[(size_t)(i0 + ty + 8 * u) * Kp + tx];
+        rb[u] = A[(size_t)(ty + 8 * u) * Kp + j0 + tx];
+    }
     for (int l0 = 0; l0 < Kp; l0 += 32) {
 #pragma unroll
-        for (int u = 0; u < 4; u++) {
-            ta[ty + 8 * u][tx] = A[(size_t)(i0 + ty + 8 * u) * Kp + l0 + tx];
-            tb[ty + 8 * u][tx] = A[(size_t)(l0 + ty + 8 * u) * Kp + j0 + tx];
-        }
+        for (int u = 0; u < 4; u++) { ta[ty + 8 * u][tx] = ra[u]; tb[ty + 8 * u][tx] = rb[u]; }
         __syncthreads();
+        if (l0 + 32 < Kp) {
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                ra[u] = A[(size_t)(i0 + ty + 8 * u) * Kp + l0 + 32 + tx];
+                rb[u] = A[(size_t)(l0 + 32 + ty + 8 * u) * Kp + j0 + tx];
+            }
+        }
 #pragma unroll
         for (int l = 0; l < 32; l++) {
             const float bv = tb[l][tx];
@@ -351,8 +363,8 @@ scl_k_scene_square(const float* __restrict__ in, float* __restrict__ out, const 
 }
 
 // Rayleigh quotient of the heaviest column of the squared matrix against the float64 Gram matrix -> lambda_max(S S^T);
-// lambda_max(A^T A) (C x C, float64 squarings by one thread); loss sum; lips.  grid: B, block 256
-extern "C" __global__ void __launch_bounds__(256)
+// lambda_max(A^T A) (C x C, float64 squarings by one warp); loss sum; lips.  grid: B, block: a power of two <= 1024
+extern "C" __global__ void __launch_bounds__(1024)
 scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ gram, const float* __restrict__ A,
                        const int* __restrict__ comp_off, const double* __restrict__ loss_tile,
                        const int* __restrict__ active, double* __restrict__ logL, float* __restrict__ lips,
@@ -368,8 +380,8 @@ scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ g
     const double* g = gram + (size_t)b * Kp * Kp;
     {
         // heaviest column: largest diagonal entry, lowest index on ties (block-wide arg-max)
-        __shared__ float sval[256];
-        __shared__ int sidx[256];
+        __shared__ float sval[1024];
+        __shared__ int sidx[1024];
         float bv = -1.f; int bi = 0;
         for (int i = threadIdx.x; i < K; i += blockDim.x) {
             const float v = m[(size_t)i * Kp + i];
@@ -377,7 +389,7 @@ scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ g
         }
         sval[threadIdx.x] = bv; sidx[threadIdx.x] = bi;
         __syncthreads();
-        for (int o = 128; o > 0; o >>= 1) {
+        for (int o = blockDim.x >> 1; o > 0; o >>= 1) {
             if (threadIdx.x < o) {
                 const float v = sval[threadIdx.x + o]; const int i = sidx[threadIdx.x + o];
                 if (v > sval[threadIdx.x] || (v == sval[threadIdx.x] && i < sidx[threadIdx.x])) {
@@ -398,47 +410,70 @@ scl_k_scene_eig_finish(const float* __restrict__ M, const double* __restrict__ g
         sATA[i][j] = s;
     }
     __syncthreads();
-    if (threadIdx.x == 32) {
-        // lambda_max(A^T A): C x C, normalised squarings in float64, Rayleigh quotient of the heaviest column
-        double T[SCL_MAX_BANDS][SCL_MAX_BANDS], Q[SCL_MAX_BANDS][SCL_MAX_BANDS], G0[SCL_MAX_BANDS][SCL_MAX_BANDS];
-        for (int i = 0; i < C; i++)
-            for (int j = 0; j < C; j++) G0[i][j] = T[i][j] = sATA[i][j];
+    if ((threadIdx.x >> 5) == 1) {
+        // lambda_max(A^T A): C x C, normalised squarings in float64, Rayleigh quotient of the heaviest column.  One
+        // warp, an entry or two per lane (the serial version by one thread cost 0.1 ms of dependent DFMAs per
+        // iteration); every sum runs in the order the serial loops had.
+        __shared__ double sT[SCL_MAX_BANDS][SCL_MAX_BANDS], sQ[SCL_MAX_BANDS][SCL_MAX_BANDS];
+        const int lane = threadIdx.x & 31;
+        for (int e = lane; e < SCL_MAX_BANDS * SCL_MAX_BANDS; e += 32)
+            sT[e / SCL_MAX_BANDS][e % SCL_MAX_BANDS] = sATA[e / SCL_MAX_BANDS][e % SCL_MAX_BANDS];
         for (int it = 0; it < 24; it++) {
-            double tr = 0.0;
-            for (int i = 0; i < C; i++)
-                for (int j = 0; j < C; j++) {
+            __syncwarp();
+            for (int e = lane; e < SCL_MAX_BANDS * SCL_MAX_BANDS; e += 32) {
+                const int i = e / SCL_MAX_BANDS, j = e % SCL_MAX_BANDS;
+                if (i < C && j < C) {
                     double s = 0.0;
-                    for (int l = 0; l < C; l++) s += T[i][l] * T[l][j];
-                    Q[i][j] = s;
-                    if (i == j) tr += s;
+                    for (int l = 0; l < C; l++) s += sT[i][l] * sT[l][j];
+                    sQ[i][j] = s;
                 }
+            }
+            __syncwarp();
+            double tr = 0.0;
+            for (int i = 0; i < C; i++) tr += sQ[i][i];
             const double sc = tr > 0.0 ? 1.0 / tr : 0.0;
-            for (int i = 0; i < C; i++) for (int j = 0; j < C; j++) T[i][j] = Q[i][j] * sc;
+            for (int e = lane; e < SCL_MAX_BANDS * SCL_MAX_BANDS; e += 32) {
+                const int i = e / SCL_MAX_BANDS, j = e % SCL_MAX_BANDS;
+                if (i < C && j < C) sT[i][j] = sQ[i][j] * sc;
+            }
         }
-        int bc = 0;
-        for (int i = 1; i < C; i++) if (T[i][i] > T[bc][bc]) bc = i;
-        double num = 0.0, den = 0.0;
-        for (int i = 0; i < C; i++) {
-            double w = 0.0;
-            for (int j = 0; j < C; j++) w += G0[i][j] * T[j][bc];
-            num += T[i][bc] * w; den += T[i][bc] * T[i][bc];
+        __syncwarp();
+        if (lane == 0) {
+            int bc = 0;
+            for (int i = 1; i < C; i++) if (sT[i][i] > sT[bc][bc]) bc = i;
+            double num = 0.0, den = 0.0;
+            for (int i = 0; i < C; i++) {
+                double w = 0.0;
+                for (int j = 0; j < C; j++) w += sATA[i][j] * sT[j][bc];
+                num += sT[i][bc] * w; den += sT[i][bc] * sT[i][bc];
+            }
+            sLS = den > 0.0 ? num / den : 0.0;
         }
-        sLS = den > 0.0 ? num / den : 0.0;
     }
     __syncthreads();
     const int best = sbest;
     double num = 0.0, den = 0.0;
     for (int i = threadIdx.x; i < K; i += blockDim.x) {
         double w = 0.0;
-        for (int j = 0; j < K; j++) w += g[(size_t)i * Kp + j] * (double)m[(size_t)j * Kp + best];
+        // (the Gram matrix is symmetric bit for bit: read column i, consecutive threads on consecutive addresses)
+#pragma unroll 8
+        for (int j = 0; j < K; j++) w += g[(size_t)j * Kp + i] * (double)m[(size_t)j * Kp + best];
         const double vi = (double)m[(size_t)i * Kp + best];
         num += vi * w; den += vi * vi;
     }
     num = block_sum<double>(num, red);
     den = block_sum<double>(den, red);
+    // loss of the iteration: the tile losses added in (plane, tile) order by one thread, fetched by all of them
+    __shared__ double sloss[512];
+    double total = 0.0;
+    for (int i0 = 0; i0 < n_loss; i0 += 512) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < 512 && i0 + i < n_loss; i += blockDim.x) sloss[i] = loss_tile[(size_t)b * n_loss + i0 + i];
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int i = 0; i < 512 && i0 + i < n_loss; i++) total += sloss[i];
+    }
     if (threadIdx.x == 0) {
-        double total = 0.0;
-        for (int i = 0; i < n_loss; i++) total += loss_tile[(size_t)b * n_loss + i];
         if (step < logL_cap) logL[(size_t)b * logL_cap + step] = total;
         const double LA = den > 0.0 ? num / den : 0.0;
         lips[2 * b] = (float)(LA * n_obs);
@@ -498,6 +533,9 @@ scl_k_scene_bbox(const float* __restrict__ S, const int* __restrict__ comp_blend
     }
 }
 
+#ifndef SCL_GRAM_SPLIT
+#define SCL_GRAM_SPLIT 128
+#endif
 // gram[b][i][j] = gram[b][j][i] = sum over box_i ^ box_j of S_i S_j for j = i + blockIdx.y, i + blockIdx.y + gridDim.y, ...
 // grid: (Kmax, SPLIT, B); one warp per row of the intersection, lanes along x; float products and per-thread float
 // sums, combined in a fixed order in float64.
