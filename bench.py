@@ -561,10 +561,13 @@ def run_scene(args):
     km = [v / fx["steps"] for v in fx["kernel_ms"]]
     alg_k3 = 4.0 * N * (2 + Cb) * K
     alg_it = 4.0 * N * (2 * K + 2 * Cb) + 4 * Cb * PSF * PSF + 8 * K * Cb
-    roofline = dict(bound="hbm", kernel="scl_k_prox_wide", achieved=alg_k3 / (km[2] * 1e-3) / 1e9, peak=hbm_peak,
+    roofline = dict(bound="hbm", kernel="scene constraint chain (scl_k_wide_step, _source_center, _prep, _sym_rows, "
+                                        "_sym_cols, _finish)",
+                    achieved=alg_k3 / (km[2] * 1e-3) / 1e9, peak=hbm_peak,
                     unit="GB/s", frac=alg_k3 / (km[2] * 1e-3) / 1e9 / hbm_peak, traffic=None,
-                    how="CUDA events around each kernel group, %d fixed iterations (e_rel=0); latency-bound on the "
-                        "dependent levels of the monotonic sweep, see DESIGN.md scene mode" % fx["steps"],
+                    how="CUDA events around each kernel group, %d fixed iterations (e_rel=0); the chain ends when the "
+                        "longest monotonic sweep does (~1000 dependent levels of a frame-sized component on one SM), "
+                        "see DESIGN.md scene mode" % fx["steps"],
                     iteration=dict(ms=fx["device_ms"] / fx["steps"], alg_bytes=alg_it,
                                    gbs=alg_it / (fx["device_ms"] / fx["steps"] * 1e-3) / 1e9),
                     kernel_ms=dict(render_conv_adjoint=km[0], lipschitz=km[1], constraints=km[2], converge=km[3]))
