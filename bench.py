@@ -423,6 +423,19 @@ def run_b200(args):
             line["cpu_baseline"] = cpu
         if strong is not None:
             line["config"]["strong_scaling"] = strong
+        if world == 1 and args.config4_steps > 0:
+            # the other single-GPU configuration with a bench line of its own (bench.py --workload config4), short
+            try:
+                bb.close()
+                c4 = scene_line(args, args.config4_steps, 1, False)
+                line["config4"] = dict(workload=c4["config"]["workload"], value=c4["value"], unit=c4["unit"],
+                                       steps=c4["steps"], ms_per_step=c4["ms_per_step"],
+                                       iters_per_fit=c4["config"]["iters_per_fit"], components=c4["config"]["components"],
+                                       e2e=c4["e2e"], gpu_launches=c4["gpu_launches"],
+                                       ms_per_iteration=c4["roofline"]["iteration"]["ms"],
+                                       kernel_ms=c4["roofline"]["kernel_ms"], roofline_frac=c4["roofline"]["frac"])
+            except Exception as exc:        # the headline line must not depend on the secondary workload
+                line["config4"] = dict(error="%s: %s" % (type(exc).__name__, exc))
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
@@ -504,9 +517,18 @@ def run_scene(args):
     rank = int(os.environ.get("RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
     torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", 0)))
+    dist = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0))))
+    line = scene_line(args, args.steps, args.warmup, not args.no_cpu, world, rank, dist)
+    if line is not None:
+        print(json.dumps(line))
+
+
+def scene_line(args, steps, warmup, with_cpu, world=1, rank=0, dist=None):
+    """The config-4 measurement (run_scene's line; also the `config4` entry of the default line at N = 1)."""
+    import torch
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -527,8 +549,8 @@ def run_scene(args):
     bt.snapshot()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     iters, launches = 0, 0
-    for i in range(args.warmup + args.steps):
-        if i == args.warmup:
+    for i in range(warmup + steps):
+        if i == warmup:
             torch.cuda.synchronize()
             if world > 1:
                 dist.barrier()
@@ -549,11 +571,11 @@ def run_scene(args):
     # end to end: host arrays -> upload -> fit -> download of the fitted scene
     up = {k: v for k, v in batch.items() if k not in ("C", "Ny", "Nx", "ker_half")}
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         bt.upload(**up)
         bt.fit(MAX_ITER, E_REL, check_every=args.check_every)
         res = bt.download()
-    e2e_s = (time.perf_counter() - t0) / args.steps
+    e2e_s = (time.perf_counter() - t0) / steps
     d2h = sum(v.nbytes for v in res.values() if isinstance(v, np.ndarray))
     # per-kernel time of a fixed-iteration pass
     bt.restore()
@@ -573,26 +595,26 @@ def run_scene(args):
                     kernel_ms=dict(render_conv_adjoint=km[0], lipschitz=km[1], constraints=km[2], converge=km[3]))
     bt.close()
     if rank != 0:
-        return
-    line = dict(metric=METRIC, value=world * args.steps / (ms / 1e3), unit=UNIT, n_gpus=world, steps=args.steps,
-                warmup=args.warmup, ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None,
+        return None
+    line = dict(metric=METRIC, value=world * steps / (ms / 1e3), unit=UNIT, n_gpus=world, steps=steps,
+                warmup=warmup, ms_per_step=ms / steps, higher_is_better=True, scaling="weak", vs_baseline=None,
                 dtype="f32", data="synthetic",
                 config=dict(workload=SCENE_WORKLOAD, size=args.scene_size, sources=args.scene_sources, components=K,
-                            max_iter=MAX_ITER, e_rel=E_REL, iters_per_fit=iters / args.steps,
+                            max_iter=MAX_ITER, e_rel=E_REL, iters_per_fit=iters / steps,
                             l2="state per iteration (%.0f MB of morphologies) exceeds the 126 MB L2" % (4e-6 * N * K),
                             sharding="replicas only: one scene is one unit", input_gen_s=t_gen),
                 pgm_iters_per_sec=world * iters / (ms / 1e3),
                 e2e=dict(value=world / e2e_s, unit=UNIT, h2d_bytes_per_step=int(bt.h2d_bytes), d2h_bytes_per_step=int(d2h),
                          ms_per_step=e2e_s * 1e3),
                 gpu_launches=int(launches), roofline=roofline)
-    if not args.no_cpu:
+    if with_cpu:
         t_it, _ = scene_oracle_step_seconds(batch, extra)
-        per_fit = iters / args.steps
+        per_fit = iters / steps
         line["cpu_baseline"] = dict(value=1.0 / (t_it * per_fit), unit=UNIT, cores=1, kind="port",
                                     sample="1 iteration of the same scene with the CPU oracle (%.1f s), scaled to the "
                                            "%.0f iterations the GPU fit took" % (t_it, per_fit),
                                     iters_per_sec=1.0 / t_it)
-    print(json.dumps(line))
+    return line
 
 
 # ------------------------------------------------------------------------------------------ config 5 (multi-resolution)
@@ -780,6 +802,8 @@ def main():
     ap.add_argument("--ref-per-worker", type=int, default=0,
                     help="--impl reference: blends per worker process and step (0 = sized from --steps / --warmup)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--config4-steps", type=int, default=3,
+                    help="N = 1: fits of the config-4 scene reported as `config4` in the default line (0 = skip)")
     ap.add_argument("--per-blend-psfs", action="store_true",
                     help="config 3 with one observed PSF set per blend (B x C kernel spectra matched on the device and "
                          "kept in HBM) instead of one shared set")
