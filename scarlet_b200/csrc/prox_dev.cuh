@@ -834,47 +834,85 @@ __global__ void scl_k_build_wlev(const float* __restrict__ wtab, const int* __re
     wlev[(size_t)oct * E + start[v] + ai] = out;
 }
 
-// in-frame range of a on level v for an octant that reaches the frame edge after Ba steps along its long axis and Bb
-// along its short one
-__device__ __forceinline__ void scl_wide_range(int v, int Ba, int Bb, int& amin, int& amax) {
-    amin = max((v + 2) / 3, (v - Bb + 1) >> 1);
-    amax = min(v >> 1, Ba);
+// The pixels of level v in one octant, after dropping the duplicate images on the octant boundaries (bb == 0 belongs to
+// the octants with sb == 0, a == bb to those with sw == 0) and what lies outside the frame: a in [lo, hi].
+// a3 = (v + 2) / 3, v3 = v % 3, vh = v / 2 are carried along the level loop (no divisions per level).
+__device__ __forceinline__ void scl_wide_range(int v, int a3, int v3, int vh, int Ba, int Bb, bool sb, bool sw,
+                                               int& lo, int& hi) {
+    const int lo0 = a3 + ((sw && v3 == 0) ? 1 : 0);
+    const int hi0 = vh - ((sb && !(v & 1)) ? 1 : 0);
+    lo = max(lo0, (v - Bb + 1) >> 1);
+    hi = min(hi0, Ba);
 }
 
 __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                                        const float* __restrict__ wtab, const double* __restrict__ ctab, float thresh,
                                        int* exit_level = nullptr, const float4* __restrict__ wlev = nullptr, int wlevE = 0) {
-    if ((blockDim.x & 255) != 0 || Ny < 2 || Nx < 2) {
+    if ((blockDim.x & 511) != 0 || Ny < 2 || Nx < 2 || !wlev) {
         scl_monotonic_hbm<float, false>(X, Ny, Nx, cy, cx, wtab, ctab, thresh, exit_level);
         return;
     }
     const float omt = 1.f - thresh;
+    const bool early = exit_level != nullptr;    // (tested once: exit_level points to shared memory through a generic pointer)
     const int ay = max(cy, Ny - 1 - cy), ax = max(cx, Nx - 1 - cx);
     const int vmax = 2 * max(ay, ax) + min(ay, ax);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+    const int nwm = nw - 1;                      // warps that take interior pixels; the last warp takes the frame edge
+    const bool edge_warp = warp == nwm;
     const int W2 = 2 * Nx - 1;
     const int p0 = cy * Nx + cx, t0 = (Ny - 1) * W2 + (Nx - 1);
     const size_t tsize = (size_t)(2 * Ny - 1) * (size_t)W2 * 8;
     const int amax_tab = max(Ny, Nx) - 1;
-    // A level ends when its slowest warp does, and a source near an edge has one or two octants that reach across the
-    // frame and six that left it: with a fixed octant per warp two warps ran two or three rounds per level while
-    // fourteen waited (measured per warp with clock64: 1067 rounds against 27).  Every SCL_WIDE_CHUNK levels the warps
-    // are dealt to the octants in proportion to the pixels they hold over those levels (at least one warp per octant
-    // that holds any).
+    // Measured on the frame-sized sweeps that end the kernel (clock64 per warp): a level takes as long as the warp that
+    // issues the most instructions for it, at ~10 cycles per instruction; waiting for the loads is 7 % of it.  So:
+    // (1) every SCL_WIDE_CHUNK levels the interior warps are dealt to the octants in proportion to the pixels they
+    // hold over those levels (a source near an edge has one or two octants that reach across the frame and six that
+    // left it: with a fixed octant per warp two warps ran 1 067 rounds while others ran 27); (2) the interior loop is
+    // straight-line code over the four candidate taps, its range already stripped of duplicates and edge pixels, the
+    // level counters carried instead of divided; (3) the at most sixteen pixels of a level that sit on the frame edge
+    // (border-type weights, taps to clamp) belong to one warp of their own, a lane each, which runs beside the others.
     constexpr int SCL_WIDE_CHUNK = 32;
     __shared__ int s_pre[9], s_cnt[8];
-    // per-octant values of this warp (set at every deal)
+    // per-octant values of this warp: set at every deal (interior warps), once (a lane pair of the edge warp per octant)
     int oct = -1, slot = 0, nslot = 32;
     bool sb = false, sw = false;
     int ya = 0, xa = 0, yb = 0, xb = 0, Ba = -1, Bb = -1, pA = 0, pB = 0, tA = 0, tB = 0;
-    int d4[4] = {0, 0, 0, 0};
-    const float4* wl = nullptr;
-    int estart = 0;          // first level-ordered entry of the current level
+    int d0 = 0, d1 = 0, d2 = 0, d3 = 0;
+    const float4* wl = wlev;
+    auto set_octant = [&](int o_) {
+        const bool sa = (o_ >> 1) & 1;
+        oct = o_; sb = o_ & 1; sw = (o_ >> 2) & 1;
+        ya = sw ? 0 : (sa ? -1 : 1); xa = sw ? (sa ? -1 : 1) : 0;
+        yb = sw ? (sb ? -1 : 1) : 0; xb = sw ? 0 : (sb ? -1 : 1);
+        Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);      // steps to the frame edge, long axis
+        Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);      // ... short axis
+        pA = ya * Nx + xa; pB = yb * Nx + xb;      // steps of the pixel index per unit of a / bb
+        tA = ya * W2 + xa; tB = yb * W2 + xb;      // steps of the table entry
+    };
+    // edge warp: the four candidate taps of the lane's octant -- offsets in d0..d3, the frame sides each needs (bit 0 up,
+    // 1 down, 2 left, 3 right; four bits per tap) and their indices into a row of the weight table (three bits per tap)
+    int emask = 0, etap = 0;
+    if (edge_warp && lane < 16) {
+        set_octant(lane >> 1);
+        const SclOctant o = scl_octant(lane >> 1);
+        d0 = o.oy[0] * Nx + o.ox[0]; d1 = o.oy[1] * Nx + o.ox[1];
+        d2 = o.oy[2] * Nx + o.ox[2]; d3 = o.oy[3] * Nx + o.ox[3];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int m = (o.oy[j] < 0 ? 1 : 0) | (o.oy[j] > 0 ? 2 : 0) | (o.ox[j] < 0 ? 4 : 0) | (o.ox[j] > 0 ? 8 : 0);
+            emask |= m << (4 * j);
+            etap |= o.tap[j] << (3 * j);
+        }
+    }
+    int estart = 0;                  // first level-ordered entry of the current level
+    int a3 = 0, v3 = 0;              // (v + 2) / 3 and v % 3 of the current level
     __syncthreads();
-    constexpr int ILP = 2;
     int dry = 0, vlast = 0x7fffffff;
     for (int v = 1; v <= vmax; v++) {
-        if (((v - 1) % SCL_WIDE_CHUNK) == 0) {
+        if (++v3 == 3) v3 = 0;
+        if (v3 == 1) a3++;
+        const int vh = v >> 1;
+        if (((v - 1) & (SCL_WIDE_CHUNK - 1)) == 0) {
             // (every thread is past the barrier that ended level v - 1)
             if (warp == 0) {
                 int n = 0;
@@ -885,7 +923,7 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                     const int ve = min(v + SCL_WIDE_CHUNK - 1, vmax);
                     for (int u = v; u <= ve; u++) {
                         int lo, hi;
-                        scl_wide_range(u, qBa, qBb, lo, hi);
+                        scl_wide_range(u, (u + 2) / 3, u % 3, u >> 1, qBa, qBb, qb, qw, lo, hi);
                         n += max(hi - lo + 1, 0);
                     }
                 }
@@ -894,7 +932,7 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                 for (int o = 1; o < 8; o <<= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
                 const int nz = __popc(__ballot_sync(0xffffffffu, n > 0));
                 int w = 0;
-                if (n > 0) w = 1 + (int)(((long long)(nw - nz) * n) / tot);
+                if (n > 0) w = 1 + (int)(((long long)(nwm - nz) * n) / tot);
                 int incl = w;
 #pragma unroll
                 for (int o = 1; o < 8; o <<= 1) {
@@ -905,97 +943,83 @@ __device__ void scl_monotonic_wide_f32(float* X, int Ny, int Nx, int cy, int cx,
                 if (lane == 7) s_pre[8] = incl;
             }
             __syncthreads();
-            oct = -1;
+            if (!edge_warp) {
+                int o_ = -1;
 #pragma unroll
-            for (int o = 0; o < 8; o++)
-                if (warp >= s_pre[o] && warp < s_pre[o] + s_cnt[o]) oct = o;
-            Ba = -1; Bb = -1;
-            if (oct >= 0) {
-                const bool sa = (oct >> 1) & 1;
-                sb = oct & 1; sw = (oct >> 2) & 1;
-                slot = (warp - s_pre[oct]) * 32 + lane;
-                nslot = s_cnt[oct] * 32;
-                ya = sw ? 0 : (sa ? -1 : 1); xa = sw ? (sa ? -1 : 1) : 0;
-                yb = sw ? (sb ? -1 : 1) : 0; xb = sw ? 0 : (sb ? -1 : 1);
-                Ba = sw ? (sa ? cx : Nx - 1 - cx) : (sa ? cy : Ny - 1 - cy);      // steps to the frame edge, long axis
-                Bb = sw ? (sb ? cy : Ny - 1 - cy) : (sb ? cx : Nx - 1 - cx);      // ... short axis
-                pA = ya * Nx + xa; pB = yb * Nx + xb;      // steps of the pixel index per unit of a / bb
-                tA = ya * W2 + xa; tB = yb * W2 + xb;      // steps of the table entry
-                wl = wlev ? wlev + (size_t)oct * wlevE : nullptr;
-                const SclOctant o = scl_octant(oct);
-#pragma unroll
-                for (int j = 0; j < 4; j++) d4[j] = o.oy[j] * Nx + o.ox[j];
+                for (int o = 0; o < 8; o++)
+                    if (warp >= s_pre[o] && warp < s_pre[o] + s_cnt[o]) o_ = o;
+                oct = -1; Ba = -1; Bb = -1;
+                if (o_ >= 0) {
+                    set_octant(o_);
+                    slot = (warp - s_pre[o_]) * 32 + lane;
+                    nslot = s_cnt[o_] * 32;
+                    wl = wlev + (size_t)o_ * wlevE;
+                    const SclOctant o = scl_octant(o_);
+                    d0 = o.oy[0] * Nx + o.ox[0]; d1 = o.oy[1] * Nx + o.ox[1];
+                    d2 = o.oy[2] * Nx + o.ox[2]; d3 = o.oy[3] * Nx + o.ox[3];
+                }
             }
         }
-        const int amin0 = (v + 2) / 3;
-        int amin, amax;
-        scl_wide_range(v, Ba, Bb, amin, amax);
+        int lo, hi;
+        scl_wide_range(v, a3, v3, vh, Ba, Bb, sb, sw, lo, hi);
         int anypos = 0;
-        for (int a0 = amin + slot; a0 <= amax; a0 += ILP * nslot) {
-            float val[ILP];
-            int pos[ILP];
-#pragma unroll
-            for (int u = 0; u < ILP; u++) {
-                const int a = a0 + u * nslot, bb = v - 2 * a;
-                pos[u] = -1;
-                // beyond the level, or a duplicate image of a pixel on an octant boundary
-                if (a > amax || (bb == 0 && sb) || (a == bb && sw)) continue;
-                const int p = p0 + a * pA + bb * pB;
-                const float* xr = X + p;
-                pos[u] = p;
-                if (wl && a != Ba && bb != Bb) {
-                    // interior pixel: its four candidate taps, one coalesced 16-byte entry of weights
-                    const float4 w = wl[estart + (a - amin0)];
-                    const float n0 = xr[d4[0]], n1 = xr[d4[1]], n2 = xr[d4[2]], n3 = xr[d4[3]], cur = xr[0];
-                    float ref = 0.f;
-                    ref = (w.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n0, w.x)) : ref;
-                    ref = (w.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n1, w.y)) : ref;
-                    ref = (w.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n2, w.z)) : ref;
-                    ref = (w.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n3, w.w)) : ref;
-                    const float r = __fmul_rn(ref, omt);
-                    val[u] = (r < cur) ? r : cur;
-                    continue;
-                }
-                const float* wt = wtab + (size_t)(t0 + a * tA + bb * tB) * 8;
-                float n[8];
-                if (a == Ba || bb == Bb) {
-                    // on the frame edge: the table of the border type; taps outside the frame (weight 0 there) read
-                    // the pixel itself
-                    const int y = cy + ya * a + yb * bb, x = cx + xa * a + xb * bb;
-                    const bool up = y > 0, dn = y < Ny - 1, lf = x > 0, rt = x < Nx - 1;
-                    wt += (size_t)((up ? (dn ? 0 : 2) : 1) * 3 + (lf ? (rt ? 0 : 2) : 1)) * tsize;
-                    n[0] = xr[(up && lf) ? -Nx - 1 : 0];
-                    n[1] = xr[up ? -Nx : 0];
-                    n[2] = xr[(up && rt) ? -Nx + 1 : 0];
-                    n[3] = xr[lf ? -1 : 0];
-                    n[4] = xr[rt ? 1 : 0];
-                    n[5] = xr[(dn && lf) ? Nx - 1 : 0];
-                    n[6] = xr[dn ? Nx : 0];
-                    n[7] = xr[(dn && rt) ? Nx + 1 : 0];
-                } else {
-                    const float* xu = xr - Nx;
-                    const float* xd = xr + Nx;
-                    n[0] = xu[-1]; n[1] = xu[0]; n[2] = xu[1];
-                    n[3] = xr[-1]; n[4] = xr[1];
-                    n[5] = xd[-1]; n[6] = xd[0]; n[7] = xd[1];
-                }
-                const float4 w0 = *reinterpret_cast<const float4*>(wt);
-                const float4 w1 = *reinterpret_cast<const float4*>(wt + 4);
-                const float cur = xr[0];
-                const float r = __fmul_rn(scl_mono_ref8(n, w0, w1), omt);
-                val[u] = (r < cur) ? r : cur;
+        if (!edge_warp) {
+            // interior pixels: p = p0 + a pA + (v - 2a) pB; weights at entry estart + a - (v + 2) / 3 of the octant.
+            // The pixels on the frame edge -- a == Ba (then hi == Ba) and bb == Bb (then 2 lo == v - Bb) -- are not ours.
+            const int ilo = lo + ((2 * lo == v - Bb) ? 1 : 0), ihi = hi - ((hi == Ba) ? 1 : 0);
+            float* xv = X + (p0 + v * pB);
+            const int pS = pA - 2 * pB;
+            const float4* wv = wl + (estart - a3);
+            for (int a = ilo + slot; a <= ihi; a += nslot) {
+                float* xr = xv + a * pS;
+                const float4 w = wv[a];
+                const float n0 = xr[d0], n1 = xr[d1], n2 = xr[d2], n3 = xr[d3], cur = xr[0];
+                float r = 0.f;
+                r = (w.x > 0.f) ? __fadd_rn(r, __fmul_rn(n0, w.x)) : r;
+                r = (w.y > 0.f) ? __fadd_rn(r, __fmul_rn(n1, w.y)) : r;
+                r = (w.z > 0.f) ? __fadd_rn(r, __fmul_rn(n2, w.z)) : r;
+                r = (w.w > 0.f) ? __fadd_rn(r, __fmul_rn(n3, w.w)) : r;
+                r = __fmul_rn(r, omt);
+                const float val = (r < cur) ? r : cur;
+                xr[0] = val;
+                anypos |= !(val <= 0.f);
             }
-#pragma unroll
-            for (int u = 0; u < ILP; u++)
-                if (pos[u] >= 0) { X[pos[u]] = val[u]; anypos |= !(val[u] <= 0.f); }
+        } else if (lane < 16) {
+            // the frame edge: even lanes the pixel with a == Ba of their octant, odd lanes the one with bb == Bb
+            const bool isA = !(lane & 1);
+            const bool have = isA ? (hi == Ba && lo <= hi) : (2 * lo == v - Bb && lo <= hi && lo != Ba);
+            if (have) {
+                const int a = isA ? Ba : lo, bb = v - 2 * a;
+                float* xr = X + (p0 + a * pA + bb * pB);
+                const int y = cy + ya * a + yb * bb, x = cx + xa * a + xb * bb;
+                const bool up = y > 0, dn = y < Ny - 1, lf = x > 0, rt = x < Nx - 1;
+                // the table of the border type (out-of-frame taps weigh 0 there and read the pixel itself); of its
+                // eight weights only the octant's four candidates can be non-zero
+                const float* wt = wtab + (size_t)(t0 + a * tA + bb * tB) * 8
+                                  + (size_t)((up ? (dn ? 0 : 2) : 1) * 3 + (lf ? (rt ? 0 : 2) : 1)) * tsize;
+                const int missing = emask & ~((up ? 0x1111 : 0) | (dn ? 0x2222 : 0) | (lf ? 0x4444 : 0) | (rt ? 0x8888 : 0));
+                const float w0 = wt[etap & 7], w1 = wt[(etap >> 3) & 7], w2 = wt[(etap >> 6) & 7], w3 = wt[(etap >> 9) & 7];
+                const float n0 = xr[(missing & 0x000f) ? 0 : d0], n1 = xr[(missing & 0x00f0) ? 0 : d1];
+                const float n2 = xr[(missing & 0x0f00) ? 0 : d2], n3 = xr[(missing & 0xf000) ? 0 : d3];
+                const float cur = xr[0];
+                float r = 0.f;
+                r = (w0 > 0.f) ? __fadd_rn(r, __fmul_rn(n0, w0)) : r;
+                r = (w1 > 0.f) ? __fadd_rn(r, __fmul_rn(n1, w1)) : r;
+                r = (w2 > 0.f) ? __fadd_rn(r, __fmul_rn(n2, w2)) : r;
+                r = (w3 > 0.f) ? __fadd_rn(r, __fmul_rn(n3, w3)) : r;
+                r = __fmul_rn(r, omt);
+                const float val = (r < cur) ? r : cur;
+                xr[0] = val;
+                anypos |= !(val <= 0.f);
+            }
         }
-        estart += scl_wlev_count(v, amax_tab);
-        if (exit_level) {
+        estart += max(min(vh, amax_tab) - a3 + 1, 0);
+        if (early) {
             dry = __syncthreads_or(anypos) ? 0 : dry + 1;
             if (dry >= 3 && v >= 3) { vlast = v; break; }
         } else {
             __syncthreads();
         }
     }
-    if (exit_level && threadIdx.x == 0) *exit_level = vlast;
+    if (early && threadIdx.x == 0) *exit_level = vlast;
 }
