@@ -340,7 +340,9 @@ int scl_batch_wait_mode(scl_batch* batch, int blocking);
  * one geometry on).  bit 4: scene mode runs a component's whole constraint schedule in one CTA instead of the chain of
  * kernels that spreads its k-space symmetry products over the GPU (csrc/k_prox_split.cu).  bit 5: the scene-mode sweep
  * reads every pixel's eight weights from the offset-indexed table instead of the four that can be non-zero from the
- * level-ordered copy (bit-identical results; the tests compare the two). */
+ * level-ordered copy (bit-identical results; the tests compare the two).  bit 6: scene mode with exact constants runs
+ * the Gram chain in line on the caller's stream instead of beside the render / convolution kernels on a stream of the
+ * batch's own. */
 int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
 
