@@ -753,22 +753,10 @@ __device__ void scl_monotonic_hbm(T* X, int Ny, int Nx, int cy, int cx,
 // One component's sweep runs on one SM, a level after the other, and a frame-sized component has ~1000 pixels on each
 // of ~1000 levels: measured, the generic loop above spent ~450 instructions on a pixel (sign/swap selects, 64-bit
 // address arithmetic and in-frame tests per tap, a branch per weight) and a level took 1.7 us with every load removed.
-// Here the octant is a property of the warp (blocks of a multiple of 8 warps), pixel and table indices are affine in
-// (a, v - 2a) with per-thread constant steps, interior pixels read their eight neighbours at fixed offsets, and the
-// weights select instead of branch.  Same operations on the same values in the same order as scl_mono_pixel_value_hbm
-// (products rounded, added in tap order, taps of weight 0 skipped), hence the same bits.
-__device__ __forceinline__ float scl_mono_ref8(const float (&n)[8], const float4 w0, const float4 w1) {
-    float ref = 0.f;
-    ref = (w0.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n[0], w0.x)) : ref;
-    ref = (w0.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n[1], w0.y)) : ref;
-    ref = (w0.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n[2], w0.z)) : ref;
-    ref = (w0.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n[3], w0.w)) : ref;
-    ref = (w1.x > 0.f) ? __fadd_rn(ref, __fmul_rn(n[4], w1.x)) : ref;
-    ref = (w1.y > 0.f) ? __fadd_rn(ref, __fmul_rn(n[5], w1.y)) : ref;
-    ref = (w1.z > 0.f) ? __fadd_rn(ref, __fmul_rn(n[6], w1.z)) : ref;
-    ref = (w1.w > 0.f) ? __fadd_rn(ref, __fmul_rn(n[7], w1.w)) : ref;
-    return ref;
-}
+// Here the octant is a property of the warp, pixel and table indices are affine in (a, v - 2a) with per-warp constant
+// steps, a pixel reads the four taps that can be strictly closer at fixed offsets, and the weights select instead of
+// branch.  Same operations on the same values in the same order as scl_mono_pixel_value_hbm (products rounded, added
+// in tap order, taps of weight 0 skipped), hence the same bits.
 
 // Level-ordered weights of the wide sweep.  Of the eight taps of a pixel at offset a (ya, xa) + bb (yb, xb), a >= bb >= 0,
 // only four can be strictly closer to the peak: the three one step back along the long axis and the one a step back
