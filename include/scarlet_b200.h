@@ -342,7 +342,8 @@ int scl_batch_wait_mode(scl_batch* batch, int blocking);
  * reads every pixel's eight weights from the offset-indexed table instead of the four that can be non-zero from the
  * level-ordered copy (bit-identical results; the tests compare the two).  bit 6: scene mode with exact constants runs
  * the Gram chain in line on the caller's stream instead of beside the render / convolution kernels on a stream of the
- * batch's own. */
+ * batch's own, and the constraint schedule as one chain of kernels instead of two (components with / without the
+ * k-space symmetry). */
 int scl_batch_debug_flags(scl_batch* batch, int flags);
 void scl_batch_destroy(scl_batch* batch);
 

@@ -57,6 +57,8 @@ struct SclProxArgs {
     // the finishing one; waux + i * waux_stride: the symmetry tables of slot i; slot_of[k]: the slot of component k.
     int* box;                 // [Ktot][4] scene mode: footprint box (y0, y1, x0, x1) of the morphology written back, for the
                               // next iteration's Gram matrix (k_scene.cu: scl_k_scene_gram_boxes); nullptr: not wanted
+    int part;                 // staged scene mode: 0 every listed component, 1 only those that take the k-space symmetry,
+                              // 2 only the others (the two groups finish on different streams)
     SclWideRec* wrec;
     float* waux;
     size_t waux_stride;
@@ -66,7 +68,7 @@ struct SclProxArgs {
 // What the stages of an iteration hand to each other about the component in one scratch slot.
 struct SclWideRec {
     int k;                    // component, -1: nothing to do in this slot (blend no longer active)
-    int mode;                 // symmetry the component takes: 0 none, 1 k-space operator, 2 mirror pairs
+    int mode;                 // 1: the k-space operator is applied to the window below by the symmetry kernels; 0: not
     int cy, cx;               // pixel_center after max_pixel / centroid
     int y0, x0, ny, nx;       // window of the symmetry (scl_window)
     int nyq, oy;              // k-space operator: Nyquist row term present, row parity offset
@@ -331,6 +333,10 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
     __shared__ int sexit;               // last level the scene-mode sweep processed (0x7fffffff: not stopped early)
     if (threadIdx.x == 0) sexit = 0x7fffffff;
     const unsigned fl = a.cflags[k];
+    if (STAGE == 2 && a.part) {
+        const unsigned ks = SCL_F_CONSTRAINED | SCL_F_SYMMETRIC | SCL_F_KSPACE;
+        if ((a.part == 1) != ((fl & ks) == ks)) return;
+    }
     long long tprev = a.phase_clk ? clock64() : 0;
     const long long tstart = tprev;
     // slots 0..4: clocks summed over CTAs per phase; 5, 6, 7: the longest symmetry phase, sweep and CTA of the launch
@@ -371,12 +377,10 @@ __device__ __forceinline__ void scl_prox_body(const SclProxArgs& a)
         // morphology by scl_k_source_center just before this launch
         const bool own_center = !(fl & SCL_F_SHARED_CENTER);
         if (STAGE == 2) {
-            const SclWideRec& r = a.wrec[blockIdx.x];
-            if (r.mode == 2) {
-                SclWindow w;
-                w.y0 = r.y0; w.x0 = r.x0; w.ny = r.ny; w.nx = r.nx; w.centered = false;
-                scl_flip_symmetry(X, Nx, w, 0, 1.0f);
-            }
+            // the k-space symmetry was applied by the kernels before this one; mirror pairs are taken here, on the window
+            // of the centre the record carries (a multi-component source's was measured after its components' steps)
+            if ((fl & SCL_F_SYMMETRIC) && !(fl & SCL_F_KSPACE))
+                scl_flip_symmetry(X, Nx, scl_window(Ny, Nx, sc[0], sc[1]), 0, 1.0f);
         } else {
         if (own_center) scl_max_pixel(X, Ny, Nx, sc[0], sc[1], sc);
         __syncthreads();

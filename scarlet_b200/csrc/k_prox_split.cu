@@ -147,11 +147,12 @@ scl_k_wide_prep(SclProxArgs a)
     const int k = r.k;
     if (k < 0) return;
     const unsigned fl = a.cflags[k];
-    if (!(fl & SCL_F_CONSTRAINED) || !(fl & SCL_F_SYMMETRIC) || (fl & SCL_F_SCHEDULE)) return;     // mode stays 0
+    // only the components that take the k-space symmetry (mirror pairs are taken by the finishing kernel); mode stays 0
+    if (!(fl & SCL_F_CONSTRAINED) || !(fl & SCL_F_SYMMETRIC) || !(fl & SCL_F_KSPACE) || (fl & SCL_F_SCHEDULE)) return;
     const int Ny = a.Ny, Nx = a.Nx;
     const SclWindow w = scl_window(Ny, Nx, r.cy, r.cx);
     // update.symmetric discards the return value of the centred case (update.py:193-198)
-    const int mode = (fl & SCL_F_KSPACE) ? (w.centered ? 0 : 1) : 2;
+    const int mode = w.centered ? 0 : 1;
     if (threadIdx.x == 0) { r.mode = mode; r.y0 = w.y0; r.x0 = w.x0; r.ny = w.ny; r.nx = w.nx; }
     if (mode != 1) return;
     const int ny = w.ny, nx = w.nx;
