@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--bands", type=int, default=6)
     ap.add_argument("--iters", type=int, default=10)
     ap.add_argument("--approx", action="store_true")
+    ap.add_argument("--debug-flags", type=int, default=0, help="scl_batch_debug_flags of the batch (experiments)")
     ap.add_argument("--drop", default="", help="experiment: clear a constraint flag on every component (symmetric, monotonic, kspace)")
     a = ap.parse_args()
     C, Ny, Nx, ns = a.bands, a.size, a.size, a.sources
@@ -38,6 +39,8 @@ def main():
     t_gen = time.time() - t0
     t0 = time.time()
     bt = nat.Batch(**batch)
+    if a.debug_flags:
+        bt.debug_flags(a.debug_flags)
     t_up = time.time() - t0
     bt.fit(2, 0.0, approximate_L=a.approx)                       # warm-up
     info = bt.fit(a.iters, 0.0, approximate_L=a.approx, profile=True)
