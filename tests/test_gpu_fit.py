@@ -212,6 +212,28 @@ def test_scene_lockstep_large_frame(nat):
     _lockstep(nat, blend, 4, approximate_L=False)
 
 
+def test_scene_lockstep_tall_frame_near_the_edge_limit(nat):
+    """A 2-band 2040x48 frame, two pixels short of the 2042-pixel edge limit (include/scarlet_b200.h): the symmetry
+    tables of the one-CTA constraint kernel pass 48 KB of dynamic shared memory there (the opt-in of ensure_globals), the
+    level-ordered sweep weights exceed their budget (the sweep falls back to the offset-indexed table) and the
+    offset tables hold 4079 x 95 entries.  Two lock-step iterations against the oracle through the chain of kernels,
+    then one iteration of the one-CTA kernel (debug flag 16) against the chain."""
+    _, _, _, blend = helpers.synthetic_blend(31, C=2, Ny=2040, Nx=48, kmin=2, kmax=2)
+    p = helpers.pack([blend])
+    outs = []
+    for flags in (0, 16):
+        bt = nat.Batch(**p)
+        bt.debug_flags(flags)
+        bt.fit(1, 1e-2)
+        outs.append(bt.download())
+        bt.close()
+    a, b = outs
+    assert_array_equal(a["center"], b["center"])
+    assert_allclose(a["logL"], b["logL"], rtol=1e-6)
+    assert_allclose(a["morph"], b["morph"], rtol=0, atol=2e-6)
+    _lockstep(nat, blend, 2)
+
+
 @pytest.mark.parametrize("approx", [False, True])
 def test_scene_lockstep_config4_class_256(nat, approx):
     """BASELINE config 4's class at a quarter of its area: a 6-band 256x256 scene with 100 sources (70 %
