@@ -86,35 +86,30 @@ scl_k_wide_source_center(SclProxArgs a, const int* __restrict__ msrc)
     const int k0 = msrc[2 * blockIdx.x], n = msrc[2 * blockIdx.x + 1];
     const int b = a.comp_blend[k0];
     if (!a.active[b]) return;
-    const int N = a.Ny * a.Nx, Ny = a.Ny, Nx = a.Nx, C = a.C;
+    const int Ny = a.Ny, Nx = a.Nx, C = a.C;
     __shared__ double red[32];
     __shared__ int sc[2];
     __shared__ double ss[2];
     const int it = a.it_override >= 0 ? a.it_override : a.it0[b] + a.step + 1;
     const unsigned fl0 = a.cflags[k0];
     float* M = scl_wide_z(a, a.slot_of[k0]);
+    // max_pixel looks at the 5x5 pixels around the previous centre and the centroid at a PSF-sized window around the
+    // pixel it finds (measurement.py:3-29,32-94): the summed morphology is needed on that neighbourhood only, not on
+    // the frame (the same products and sums, pixel by pixel; the full-frame pass cost 0.2 ms per iteration)
+    const int rad = a.pw / 2 + 2;
+    const int cy0 = a.center[2 * k0], cx0 = a.center[2 * k0 + 1];
+    const int wy0 = max(cy0 - rad, 0), wy1 = min(cy0 + rad, Ny - 1), wx0 = max(cx0 - rad, 0), wx1 = min(cx0 + rad, Nx - 1);
+    const int wnx = wx1 - wx0 + 1, wn = (wy1 - wy0 + 1) * wnx;
     for (int j = 0; j < n; j++) {
         const int slot = a.slot_of[k0 + j];
         const float* Xk = scl_wide_x(a, slot);
         const SclWideRec& rj = a.wrec[slot];
         float ssum = 0.f;                                    // c.sed.sum(), float32, band order
         for (int c = 0; c < C; c++) ssum = __fadd_rn(ssum, rj.sAnew[c]);
-        if ((N & 3) == 0) {
-            const float4* X4 = reinterpret_cast<const float4*>(Xk);
-            float4* M4 = reinterpret_cast<float4*>(M);
-            for (int i = threadIdx.x; i < (N >> 2); i += blockDim.x) {
-                const float4 x = X4[i];
-                float4 m = (j == 0) ? make_float4(0.f, 0.f, 0.f, 0.f) : M4[i];
-                const float t0 = __fmul_rn(x.x, ssum), t1 = __fmul_rn(x.y, ssum), t2 = __fmul_rn(x.z, ssum), t3 = __fmul_rn(x.w, ssum);
-                m = (j == 0) ? make_float4(t0, t1, t2, t3)
-                             : make_float4(__fadd_rn(m.x, t0), __fadd_rn(m.y, t1), __fadd_rn(m.z, t2), __fadd_rn(m.w, t3));
-                M4[i] = m;
-            }
-        } else {
-            for (int p = threadIdx.x; p < N; p += blockDim.x) {
-                const float t = __fmul_rn(Xk[p], ssum);
-                M[p] = (j == 0) ? t : __fadd_rn(M[p], t);
-            }
+        for (int i = threadIdx.x; i < wn; i += blockDim.x) {
+            const int y = wy0 + i / wnx, x = wx0 + i % wnx, p = y * Nx + x;
+            const float t = __fmul_rn(Xk[p], ssum);
+            M[p] = (j == 0) ? t : __fadd_rn(M[p], t);
         }
         __syncthreads();
     }
@@ -173,6 +168,9 @@ scl_k_wide_prep(SclProxArgs a)
     // b[l] = sum_i (-1)^{p_i} Xw[i][l]
     for (int l = threadIdx.x; l < nx; l += blockDim.x) {
         float s = 0.f;
+        // (same order of additions as the one-CTA kernel; unrolled so that eight loads are in flight: the column is
+        // read from L2 by one thread and the loop was a chain of ny round trips)
+#pragma unroll 8
         for (int i = 0; i < ny; i++) s += (((i + oy) & 1) ? -1.f : 1.f) * Xw[i * Nx + l];
         bvec[l] = s;
     }
@@ -182,6 +180,7 @@ scl_k_wide_prep(SclProxArgs a)
     const float cf = (float)(cphi / Fy), sf = (float)(sphi / Fy);
     for (int j = threadIdx.x; j < nx; j += blockDim.x) {
         float s1 = 0.f, s2 = 0.f;
+#pragma unroll 8
         for (int l = 0; l < nx; l++) { s1 += Tx[j + l] * bvec[l]; s2 += Hx[j + l] * bvec[l]; }
         vvec[j] = cf * s1 + sf * s2;
     }
